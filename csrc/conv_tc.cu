@@ -1,0 +1,464 @@
+// 3x3 / pad-1 convolution forward, data-gradient and weight-gradient as implicit GEMMs on the
+// 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM), operands fetched by 1-D bulk
+// async copies (TMA) from the padded planar-chunk layout described in layout.cuh.
+//
+// Replaces what the reference delegates to cuDNN + ATen for its second convolution:
+//   forward   conv2 + bias + ReLU          reference model.py:11-12   (SURVEY.md K3,K4)
+//   backward  ReLU' + dgrad + wgrad + db   reference train_ddp.py:199 (SURVEY.md K10,K11)
+//
+// Warp roles (192 threads, one CTA per SM, persistent over tiles):
+//   warp 0    bulk-copy producer (one lane)
+//   warp 1    TMEM allocator + MMA issuer (one lane issues tcgen05.mma)
+//   warps 2-5 epilogue: tcgen05.ld the accumulator tile, fuse bias/ReLU/mask, store bf16 planes
+#include "ptx.cuh"
+#include "layout.cuh"
+#include "api_internal.cuh"
+
+namespace ddpb {
+
+constexpr int kConvThreads = 192;
+constexpr uint32_t kRowBytes = 16;
+constexpr uint32_t kStagePlaneBytes = kStageRows * kRowBytes;  // 3328
+
+template <int CI, int CO, int STAGES>
+struct ConvSmem {
+  static constexpr uint32_t KP = CI / 8;
+  static constexpr uint32_t w_tap_bytes = KP * CO * 16;
+  static constexpr uint32_t w_bytes = 9 * w_tap_bytes;
+  static constexpr uint32_t a_stage_bytes = KP * kStagePlaneBytes;
+  static constexpr uint32_t off_a = w_bytes;
+  static constexpr uint32_t off_bias = off_a + STAGES * a_stage_bytes;
+  static constexpr uint32_t off_bar = off_bias + CO * 4;
+  static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 4) * 8;
+  static constexpr uint32_t total = off_tmem + 16;
+};
+
+constexpr uint32_t pow2_cols(uint32_t c) {
+  return c <= 32 ? 32 : c <= 64 ? 64 : c <= 128 ? 128 : c <= 256 ? 256 : 512;
+}
+
+// MODE 0: out = relu(conv(in, w) + bias)                 (GEMM K = CI input channels, N = CO)
+// MODE 1: out = relu'(mask) * conv_transpose(in, w)      (in = grad wrt conv output with CI
+//         channels, w = the layer's weight [CI][CO][3][3], out = grad wrt conv input, CO chans)
+template <int CI, int CO, int MODE, int STAGES>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w,
+                  const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask,
+                  __nv_bfloat16* __restrict__ out, Geom g) {
+  using S = ConvSmem<CI, CO, STAGES>;
+  constexpr uint32_t KP = CI / 8;
+  constexpr uint32_t TMEM_COLS = pow2_cols(2 * CO);
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t s_w = s_base;
+  const uint32_t s_a = s_base + S::off_a;
+  float* s_bias = reinterpret_cast<float*>(smem + S::off_bias);
+  const uint32_t bar_full = s_base + S::off_bar;
+  const uint32_t bar_empty = bar_full + STAGES * 8;
+  const uint32_t bar_tfull = bar_empty + STAGES * 8;
+  const uint32_t bar_tempty = bar_tfull + 16;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+
+  // ---- one-time setup: fp32 master weights -> bf16 UMMA canonical (K-major, no swizzle) tiles
+  // B operand of tap t: rows n (GEMM N), 8-element K chunks; byte offset
+  //   t*w_tap + (k/8)*(CO*16) + n*16 + (k%8)*2        => LBO = CO*16, SBO = 128
+  for (int idx = tid; idx < CI * CO * 9; idx += kConvThreads) {
+    int n, k, tap;
+    if (MODE == 0) {  // w[n=co][k=ci][tap]
+      n = idx / (CI * 9);
+      int rem = idx - n * (CI * 9);
+      k = rem / 9;
+      tap = rem - k * 9;
+    } else {  // w[k=layer out ch][n=layer in ch][tap], taps mirrored
+      k = idx / (CO * 9);
+      int rem = idx - k * (CO * 9);
+      n = rem / 9;
+      tap = 8 - (rem - n * 9);
+    }
+    uint32_t off = tap * S::w_tap_bytes + (k >> 3) * (CO * 16) + n * 16 + (k & 7) * 2;
+    *reinterpret_cast<__nv_bfloat16*>(smem + off) = __float2bfloat16(w[idx]);
+  }
+  if (MODE == 0)
+    for (int i = tid; i < CO; i += kConvThreads) s_bias[i] = bias[i];
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(bar_full + i * 8, 1);
+      mbar_init(bar_empty + i * 8, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_tfull + i * 8, 1);
+      mbar_init(bar_tempty + i * 8, 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(s_tmem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % STAGES;
+        const uint32_t phase = (it / STAGES) & 1;
+        mbar_wait(bar_empty + stage * 8, phase ^ 1);
+        mbar_arrive_expect_tx(bar_full + stage * 8, S::a_stage_bytes);
+        const long long row0 = (long long)kGuard + (long long)t * kTileM - kHalo;
+#pragma unroll
+        for (uint32_t p = 0; p < KP; ++p)
+          bulk_g2s(s_a + stage * S::a_stage_bytes + p * kStagePlaneBytes,
+                   in + ((long long)p * g.plane_rows + row0) * 8, kStagePlaneBytes,
+                   bar_full + stage * 8);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, CO, 0, 0);
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % STAGES;
+        const uint32_t phase = (it / STAGES) & 1;
+        const int acc = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
+        mbar_wait(bar_full + stage * 8, phase);
+        tc_fence_after();
+        const uint32_t a_stage = s_a + stage * S::a_stage_bytes;
+        const uint32_t d_tmem = tmem_base + acc * CO;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const int d = (tap / 3 - 1) * g.PW + (tap % 3 - 1);
+          const uint32_t a_tap = a_stage + (kHalo + d) * kRowBytes;
+          const uint32_t b_tap = s_w + tap * S::w_tap_bytes;
+#pragma unroll
+          for (int kk = 0; kk < CI / 16; ++kk) {
+            const uint64_t adesc =
+                umma_smem_desc(a_tap + kk * 2 * kStagePlaneBytes, kStagePlaneBytes, 128);
+            const uint64_t bdesc = umma_smem_desc(b_tap + kk * 2 * (CO * 16), CO * 16, 128);
+            umma_bf16(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
+          }
+        }
+        umma_commit(bar_empty + stage * 8);
+        umma_commit(bar_tfull + acc * 8);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(bar_tfull + acc * 8, aphase);
+      tc_fence_after();
+      const int rel = t * kTileM + q * 32 + lane;
+      int img, h, wc;
+      const bool valid = decode_row(g, rel, img, h, wc);
+      const long long row = (long long)kGuard + rel;
+#pragma unroll
+      for (int c0 = 0; c0 < CO; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * CO + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const long long off = ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8;
+          uint4 o;
+          uint32_t* op = reinterpret_cast<uint32_t*>(&o);
+          if (MODE == 0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float x0 = __uint_as_float(v[j * 8 + 2 * e]) + s_bias[c0 + j * 8 + 2 * e];
+              float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + s_bias[c0 + j * 8 + 2 * e + 1];
+              x0 = valid ? fmaxf(x0, 0.f) : 0.f;
+              x1 = valid ? fmaxf(x1, 0.f) : 0.f;
+              op[e] = pack_bf16x2(x0, x1);
+            }
+          } else {
+            const uint4 mk = *reinterpret_cast<const uint4*>(mask + off);
+            const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float x0 = __uint_as_float(v[j * 8 + 2 * e]);
+              float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
+              x0 = (valid && bf16_lo(mp[e]) > 0.f) ? x0 : 0.f;
+              x1 = (valid && bf16_hi(mp[e]) > 0.f) ? x1 : 0.f;
+              op[e] = pack_bf16x2(x0, x1);
+            }
+          }
+          *reinterpret_cast<uint4*>(out + off) = o;
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(bar_tempty + acc * 8);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------
+// Weight gradient:  dW[co][ci][tap] = sum_p dout[p][co] * in[p + d(tap)][ci],  db[co] = sum_p dout
+// GEMM per tap: M = CO (dout channels), N = CI (in channels), K = pixels.  Both operands are
+// MN-major views of the planar buffers.  The bias gradient is one more N=8 MMA against a tile of
+// ones.  Each CTA accumulates its share of pixel tiles in TMEM (9*CI + 8 fp32 columns) and writes
+// one partial; wgrad_reduce_kernel sums the partials in a fixed order (deterministic).
+template <int CI, int CO, int STAGES>
+struct WgradSmem {
+  static constexpr uint32_t AP = CO / 8, BP = CI / 8;
+  static constexpr uint32_t a_plane = kTileM * kRowBytes;  // 2048
+  static constexpr uint32_t a_bytes = AP * a_plane;
+  static constexpr uint32_t b_bytes = BP * kStagePlaneBytes;
+  static constexpr uint32_t stage_bytes = a_bytes + b_bytes;
+  static constexpr uint32_t off_ones = STAGES * stage_bytes;
+  static constexpr uint32_t off_bar = off_ones + 256;
+  static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 1) * 8;
+  static constexpr uint32_t total = off_tmem + 16;
+  static constexpr uint32_t ncols = 9 * CI + 8;  // accumulator columns incl. bias block
+};
+
+template <int CI, int CO, int STAGES>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ in,
+                        float* __restrict__ partial, Geom g) {
+  using S = WgradSmem<CI, CO, STAGES>;
+  static_assert(CO == 64 || CO == 128, "UMMA M must be 64 or 128");
+  static_assert(S::ncols <= 512, "accumulator does not fit TMEM");
+  constexpr uint32_t TMEM_COLS = pow2_cols(S::ncols);
+  extern __shared__ __align__(128) uint8_t smem[];
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t s_ones = s_base + S::off_ones;
+  const uint32_t bar_full = s_base + S::off_bar;
+  const uint32_t bar_empty = bar_full + STAGES * 8;
+  const uint32_t bar_done = bar_empty + STAGES * 8;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+
+  for (int i = tid; i < 128; i += kConvThreads)
+    reinterpret_cast<__nv_bfloat16*>(smem + S::off_ones)[i] = __float2bfloat16(1.0f);
+  if (tid == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(bar_full + i * 8, 1);
+      mbar_init(bar_empty + i * 8, 1);
+    }
+    mbar_init(bar_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(s_tmem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % STAGES;
+        const uint32_t phase = (it / STAGES) & 1;
+        mbar_wait(bar_empty + stage * 8, phase ^ 1);
+        mbar_arrive_expect_tx(bar_full + stage * 8, S::stage_bytes);
+        const uint32_t sa = s_base + stage * S::stage_bytes;
+        const uint32_t sb = sa + S::a_bytes;
+        const long long rowa = (long long)kGuard + (long long)t * kTileM;
+#pragma unroll
+        for (uint32_t p = 0; p < S::AP; ++p)
+          bulk_g2s(sa + p * S::a_plane, dout + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane,
+                   bar_full + stage * 8);
+#pragma unroll
+        for (uint32_t p = 0; p < S::BP; ++p)
+          bulk_g2s(sb + p * kStagePlaneBytes,
+                   in + ((long long)p * g.plane_rows + rowa - kHalo) * 8, kStagePlaneBytes,
+                   bar_full + stage * 8);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(CO, CI, 1, 1);
+      constexpr uint32_t idesc_b = umma_idesc_bf16(CO, 8, 1, 1);
+      const uint64_t ones_desc = umma_smem_desc(s_ones, 128, 128);
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % STAGES;
+        const uint32_t phase = (it / STAGES) & 1;
+        mbar_wait(bar_full + stage * 8, phase);
+        tc_fence_after();
+        const uint32_t sa = s_base + stage * S::stage_bytes;
+        const uint32_t sb = sa + S::a_bytes;
+#pragma unroll 1
+        for (int ks = 0; ks < kTileM / 16; ++ks) {
+          const uint32_t accum = (it | ks) != 0;
+          const uint64_t adesc = umma_smem_desc(sa + ks * 16 * kRowBytes, 128, S::a_plane);
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const int d = (tap / 3 - 1) * g.PW + (tap % 3 - 1);
+            const uint64_t bdesc = umma_smem_desc(sb + (kHalo + d + ks * 16) * kRowBytes, 128,
+                                                  kStagePlaneBytes);
+            umma_bf16(tmem_base + tap * CI, adesc, bdesc, idesc, accum);
+          }
+          umma_bf16(tmem_base + 9 * CI, adesc, ones_desc, idesc_b, accum);
+        }
+        umma_commit(bar_empty + stage * 8);
+      }
+      umma_commit(bar_done);
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    mbar_wait(bar_done, 0);
+    tc_fence_after();
+    // M=64: accumulator row m sits in TMEM lane (m%16) + 32*(m/16); M=128: lane m.
+    const int rows_per_q = CO / 4;
+    const int m = q * rows_per_q + lane;
+    const bool has_row = lane < rows_per_q;
+    float* dst = partial + ((long long)blockIdx.x * CO + m) * S::ncols;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 9 * CI; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      if (has_row) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(dst + c0 + j * 4) =
+              make_uint4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+      }
+    }
+    {
+      uint32_t v[8];
+      tmem_ld8(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 9 * CI, v);
+      tmem_ld_wait();
+      if (has_row) {
+        *reinterpret_cast<uint4*>(dst + 9 * CI) = make_uint4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<uint4*>(dst + 9 * CI + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// dW[co][ci][tap] = sum_parts partial[part][co][tap*CI + ci];  db[co] = sum_parts partial[..][9*CI]
+template <int CI, int CO>
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int nparts,
+                                    float* __restrict__ dw, float* __restrict__ db) {
+  constexpr int ncols = 9 * CI + 8;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= CO * ncols) return;
+  const int co = idx / ncols;
+  const int col = idx - co * ncols;
+  if (col > 9 * CI) return;  // bias block: only its first column is used
+  float s = 0.f;
+  for (int p = 0; p < nparts; ++p) s += partial[(long long)p * CO * ncols + idx];
+  if (col == 9 * CI) {
+    db[co] = s;
+  } else {
+    const int tap = col / CI;
+    const int ci = col - tap * CI;
+    dw[(co * CI + ci) * 9 + tap] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+template <int CI, int CO, int MODE>
+static int launch_conv(const void* in, const float* w, const float* bias, const void* mask,
+                       void* out, const Geom& g, int num_sms, cudaStream_t st) {
+  constexpr int STAGES = 4;
+  using S = ConvSmem<CI, CO, STAGES>;
+  auto kern = conv3x3_tc_kernel<CI, CO, MODE, STAGES>;
+  static bool configured[64] = {};
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::total));
+    configured[dev & 63] = true;
+  }
+  const int grid = g.ntiles < num_sms ? g.ntiles : num_sms;
+  kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(in), w, bias,
+                                             static_cast<const __nv_bfloat16*>(mask),
+                                             static_cast<__nv_bfloat16*>(out), g);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" {
+
+int ddpb_conv3x3_fwd(const void* in, const float* w, const float* bias, void* out, int cin,
+                     int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int sms = ddpb_num_sms();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (cin == 32 && cout == 64) return launch_conv<32, 64, 0>(in, w, bias, nullptr, out, g, sms, st);
+  return DDPB_ERR_SHAPE;
+}
+
+// dout has `cout` channels, result din (and mask = the forward activation that fed the conv)
+// have `cin` channels; w is the layer weight [cout][cin][3][3].
+int ddpb_conv3x3_dgrad(const void* dout, const float* w, const void* mask, void* din, int cin,
+                       int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int sms = ddpb_num_sms();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (cin == 32 && cout == 64) return launch_conv<64, 32, 1>(dout, w, nullptr, mask, din, g, sms, st);
+  return DDPB_ERR_SHAPE;
+}
+
+size_t ddpb_conv3x3_wgrad_scratch_bytes(int cin, int cout) {
+  return static_cast<size_t>(ddpb_num_sms()) * cout * (9 * cin + 8) * sizeof(float);
+}
+
+int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, float* scratch,
+                       int cin, int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  constexpr int CI = 32, CO = 64, STAGES = 4;
+  using S = WgradSmem<CI, CO, STAGES>;
+  auto kern = conv3x3_wgrad_tc_kernel<CI, CO, STAGES>;
+  static bool configured[64] = {};
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::total));
+    configured[dev & 63] = true;
+  }
+  const int sms = ddpb_num_sms();
+  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(dout),
+                                             static_cast<const __nv_bfloat16*>(in), scratch, g);
+  DDPB_CUDA_OK(cudaGetLastError());
+  const int n = CO * (9 * CI + 8);
+  wgrad_reduce_kernel<CI, CO><<<(n + 255) / 256, 256, 0, st>>>(scratch, grid, dw, db);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // extern "C"

@@ -1,0 +1,585 @@
+// CUDA-core kernels of the training step: the ops whose shapes are too thin for a tensor-core
+// tile (Cin=1 convolution, N=10 linear layer) or are pure streaming/reduction work.
+//
+//   conv1 fwd + bias + ReLU            reference model.py:9-10    (SURVEY.md K1,K2)
+//   conv1 weight/bias gradient         reference train_ddp.py:199 (SURVEY.md K12,K13)
+//   linear fwd                         reference model.py:16,19   
+//   log-softmax + NLL(mean) + dlogits  reference train_ddp.py:40,198-199 (SURVEY.md K7,K8)
+//   linear bwd (dX with ReLU', dW, db) reference train_ddp.py:199 (SURVEY.md K9,K10)
+//   SGD update                         reference train_ddp.py:41,200
+//   dataset gather + u8->f32 scale     reference data.py:11-14 (ToTensor) + DataLoader collate
+//
+// All activations use the padded planar-chunk bf16 layout of layout.cuh; parameters and
+// gradients are fp32 in the reference's canonical (state_dict) layouts.
+#include "ptx.cuh"
+#include "layout.cuh"
+#include "api_internal.cuh"
+
+namespace ddpb {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& a, float (&f)[8]) {
+  f[0] = bf16_lo(a.x); f[1] = bf16_hi(a.x);
+  f[2] = bf16_lo(a.y); f[3] = bf16_hi(a.y);
+  f[4] = bf16_lo(a.z); f[5] = bf16_hi(a.z);
+  f[6] = bf16_lo(a.w); f[7] = bf16_hi(a.w);
+}
+
+// ------------------------------------------------------------------ dataset gather
+// x[i] = float(images[idx[i]]) / 255 ; y[i] = labels[idx[i]]     (ToTensor semantics)
+__global__ void gather_u8_kernel(const uint8_t* __restrict__ images,
+                                 const long long* __restrict__ labels,
+                                 const long long* __restrict__ idx, float* __restrict__ x,
+                                 long long* __restrict__ y, int batch, int pix) {
+  const int i = blockIdx.x;
+  if (i >= batch) return;
+  const long long src = idx[i];
+  const uint8_t* p = images + src * pix;
+  for (int k = threadIdx.x; k < pix; k += blockDim.x)
+    x[(long long)i * pix + k] = static_cast<float>(p[k]) * (1.0f / 255.0f);
+  if (threadIdx.x == 0) y[i] = labels[src];
+}
+
+// ------------------------------------------------------------------ conv1 forward
+template <int CIN0, int C1>
+__global__ void __launch_bounds__(256)
+conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                 const float* __restrict__ b, __nv_bfloat16* __restrict__ out, Geom g) {
+  __shared__ float sw[C1 * CIN0 * 9];
+  __shared__ float sb[C1];
+  for (int i = threadIdx.x; i < C1 * CIN0 * 9; i += blockDim.x) sw[i] = w[i];
+  for (int i = threadIdx.x; i < C1; i += blockDim.x) sb[i] = b[i];
+  __syncthreads();
+  const int nrows = g.ntiles * kTileM;
+  const long long total = (long long)(C1 / 8) * nrows;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int chunk = static_cast<int>(idx / nrows);
+    const int rel = static_cast<int>(idx - (long long)chunk * nrows);
+    int img, h, wc;
+    const bool valid = decode_row(g, rel, img, h, wc);
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (valid) {
+      float in[CIN0 * 9];
+#pragma unroll
+      for (int ci = 0; ci < CIN0; ++ci) {
+        const float* xp = x + ((long long)img * CIN0 + ci) * g.H * g.W;
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s = 0; s < 3; ++s) {
+            const int hh = h + r - 1, ww = wc + s - 1;
+            in[ci * 9 + r * 3 + s] =
+                (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
+          }
+      }
+      float acc[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float* wp = sw + (chunk * 8 + c) * CIN0 * 9;
+        float a = sb[chunk * 8 + c];
+#pragma unroll
+        for (int j = 0; j < CIN0 * 9; ++j) a = fmaf(wp[j], in[j], a);
+        acc[c] = fmaxf(a, 0.f);
+      }
+      o.x = pack_bf16x2(acc[0], acc[1]);
+      o.y = pack_bf16x2(acc[2], acc[3]);
+      o.z = pack_bf16x2(acc[4], acc[5]);
+      o.w = pack_bf16x2(acc[6], acc[7]);
+    }
+    *reinterpret_cast<uint4*>(out + ((long long)chunk * g.plane_rows + kGuard + rel) * 8) = o;
+  }
+}
+
+// ------------------------------------------------------------------ conv1 weight gradient
+// dW[c][ci][tap] = sum_p dact[p][c] * x[p + tap shift][ci],  db[c] = sum_p dact[p][c].
+// gridDim.y = C1/8 (channel chunk), gridDim.x = row blocks; one partial per blockIdx.x:
+// partial[bx][C1*CIN0*9 + C1]  (weights then biases, canonical order).
+template <int CIN0, int C1>
+__global__ void __launch_bounds__(256)
+conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restrict__ x,
+                   float* __restrict__ partial, Geom g) {
+  constexpr int NW = CIN0 * 9;
+  constexpr int NV = 8 * NW + 8;
+  __shared__ float red[8][NV];
+  const int chunk = blockIdx.y;
+  const int nrows = g.ntiles * kTileM;
+  float acc[8][NW];
+  float accb[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    accb[c] = 0.f;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) acc[c][j] = 0.f;
+  }
+  for (int rel = blockIdx.x * blockDim.x + threadIdx.x; rel < nrows;
+       rel += gridDim.x * blockDim.x) {
+    int img, h, wc;
+    if (!decode_row(g, rel, img, h, wc)) continue;
+    const uint4 dv = *reinterpret_cast<const uint4*>(
+        dact + ((long long)chunk * g.plane_rows + kGuard + rel) * 8);
+    float d[8];
+    unpack8(dv, d);
+    float in[NW];
+#pragma unroll
+    for (int ci = 0; ci < CIN0; ++ci) {
+      const float* xp = x + ((long long)img * CIN0 + ci) * g.H * g.W;
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          const int hh = h + r - 1, ww = wc + s - 1;
+          in[ci * 9 + r * 3 + s] =
+              (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      accb[c] += d[c];
+#pragma unroll
+      for (int j = 0; j < NW; ++j) acc[c][j] = fmaf(d[c], in[j], acc[c][j]);
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      const float v = warp_sum(acc[c][j]);
+      if (lane == 0) red[warp][c * NW + j] = v;
+    }
+    const float vb = warp_sum(accb[c]);
+    if (lane == 0) red[warp][8 * NW + c] = vb;
+  }
+  __syncthreads();
+  float* dst = partial + (long long)blockIdx.x * (C1 * NW + C1);
+  for (int i = threadIdx.x; i < NV; i += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][i];
+    if (i < 8 * NW) dst[chunk * 8 * NW + i] = s;
+    else dst[C1 * NW + chunk * 8 + (i - 8 * NW)] = s;
+  }
+}
+
+// ------------------------------------------------------------------ generic partial reduce
+// out[i] = sum_p part[p*n + i], fixed order => deterministic.
+__global__ void reduce_partials_kernel(const float* __restrict__ part, int nparts, long long n,
+                                       float* __restrict__ out) {
+  const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= n) return;
+  if (i4 + 3 < n && (n & 3) == 0) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p = 0; p < nparts; ++p) {
+      const float4 v = *reinterpret_cast<const float4*>(part + (long long)p * n + i4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(out + i4) = s;
+  } else {
+    for (long long i = i4; i < n && i < i4 + 4; ++i) {
+      float s = 0.f;
+      for (int p = 0; p < nparts; ++p) s += part[(long long)p * n + i];
+      out[i] = s;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ linear forward
+// logits[img][j] = sum_k act[img][k] * W[j][k]; k = c*H*W + h*W + w (NCHW flatten order of the
+// reference, model.py:13,16).  grid = (S feature slices, image groups of IMG); writes
+// partial[s][img][j]; the loss kernel adds the slices and the bias.
+template <int NOUT, int IMG>
+__global__ void __launch_bounds__(256, 1)
+linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ W,
+                  float* __restrict__ partial, Geom g, int C, int vec_per_slice) {
+  __shared__ float red[8][IMG * NOUT];
+  const int HW = g.H * g.W;
+  const int nvec = (C / 8) * HW;
+  const long long K = (long long)C * HW;
+  const int img0 = blockIdx.y * IMG;
+  const int v_begin = blockIdx.x * vec_per_slice;
+  const int v_end = min(nvec, v_begin + vec_per_slice);
+  float acc[IMG][NOUT];
+#pragma unroll
+  for (int i = 0; i < IMG; ++i)
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) acc[i][j] = 0.f;
+
+  for (int v = v_begin + threadIdx.x; v < v_end; v += blockDim.x) {
+    const int chunk = v / HW;
+    const int pix = v - chunk * HW;
+    const int h = pix / g.W, wc = pix - h * g.W;
+    const long long rowi = (long long)(h + 1) * g.PW + (wc + 1);
+    float wv[NOUT][8];
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) wv[j][c] = W[j * K + (long long)(chunk * 8 + c) * HW + pix];
+    uint4 av[IMG];
+#pragma unroll
+    for (int i = 0; i < IMG; ++i) {
+      const int img = img0 + i;
+      av[i] = make_uint4(0, 0, 0, 0);
+      if (img < g.batch)
+        av[i] = *reinterpret_cast<const uint4*>(
+            act + ((long long)chunk * g.plane_rows + kGuard + (long long)img * g.PHW + rowi) * 8);
+    }
+#pragma unroll
+    for (int i = 0; i < IMG; ++i) {
+      float a[8];
+      unpack8(av[i], a);
+#pragma unroll
+      for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[i][j] = fmaf(wv[j][c], a[c], acc[i][j]);
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < IMG; ++i)
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      const float v = warp_sum(acc[i][j]);
+      if (lane == 0) red[warp][i * NOUT + j] = v;
+    }
+  __syncthreads();
+  for (int t = threadIdx.x; t < IMG * NOUT; t += blockDim.x) {
+    const int i = t / NOUT, j = t - i * NOUT;
+    const int img = img0 + i;
+    if (img >= g.batch) continue;
+    float s = 0.f;
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][t];
+    partial[((long long)blockIdx.x * g.batch + img) * NOUT + j] = s;
+  }
+}
+
+// ------------------------------------------------------------------ loss
+// z = bias + sum_s partial[s]; loss = mean_i(logsumexp(z_i) - z_i[y_i]);
+// dlogits = (softmax(z) - onehot(y)) / batch; db[j] = sum_i dlogits[i][j].
+// Single block: the work is batch*NOUT*S floats.
+template <int NOUT>
+__global__ void __launch_bounds__(1024)
+softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
+                    const long long* __restrict__ labels, float* __restrict__ logits,
+                    float* __restrict__ dlogits, float* __restrict__ dbias,
+                    float* __restrict__ loss, int batch) {
+  __shared__ float red[32][NOUT + 1];
+  float lsum = 0.f;
+  float dbl[NOUT];
+#pragma unroll
+  for (int j = 0; j < NOUT; ++j) dbl[j] = 0.f;
+  const float inv = 1.0f / static_cast<float>(batch);
+  for (int i = threadIdx.x; i < batch; i += blockDim.x) {
+    float z[NOUT];
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) z[j] = bias[j];
+    for (int s = 0; s < S; ++s)
+#pragma unroll
+      for (int j = 0; j < NOUT; ++j) z[j] += partial[((long long)s * batch + i) * NOUT + j];
+    float m = z[0];
+#pragma unroll
+    for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
+    float se = 0.f;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) se += expf(z[j] - m);
+    const float lse = m + logf(se);
+    const int y = static_cast<int>(labels[i]);
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      const float p = expf(z[j] - lse);
+      const float d = (p - (j == y ? 1.f : 0.f)) * inv;
+      dlogits[(long long)i * NOUT + j] = d;
+      dbl[j] += d;
+      if (logits) logits[(long long)i * NOUT + j] = z[j];
+      if (j == y) lsum += lse - z[j];
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < NOUT; ++j) {
+    const float v = warp_sum(dbl[j]);
+    if (lane == 0) red[warp][j] = v;
+  }
+  {
+    const float v = warp_sum(lsum);
+    if (lane == 0) red[warp][NOUT] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x <= NOUT) {
+    float s = 0.f;
+    const int nw = blockDim.x >> 5;
+    for (int wdx = 0; wdx < nw; ++wdx) s += red[wdx][threadIdx.x];
+    if (threadIdx.x < NOUT) dbias[threadIdx.x] = s;
+    else loss[0] = s * inv;
+  }
+}
+
+// ------------------------------------------------------------------ linear backward
+// dact[img][k] = relu'(act[img][k]) * sum_j dlogits[img][j] W[j][k]     (bf16 planes)
+// dW[j][k]    = sum_img dlogits[img][j] act[img][k]                      (fp32, via partials)
+// grid = (feature-vector blocks, image splits); partial[split][NOUT][K].
+template <int NOUT>
+__global__ void __launch_bounds__(256, 1)
+linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ dlogits,
+                  const float* __restrict__ W, __nv_bfloat16* __restrict__ dact,
+                  float* __restrict__ dw_partial, Geom g, int C, int imgs_per_split) {
+  extern __shared__ float sdl[];  // [imgs_per_split][NOUT]
+  const int HW = g.H * g.W;
+  const int nvec = (C / 8) * HW;
+  const long long K = (long long)C * HW;
+  const int img_begin = blockIdx.y * imgs_per_split;
+  const int img_end = min(g.batch, img_begin + imgs_per_split);
+  for (int t = threadIdx.x; t < (img_end - img_begin) * NOUT; t += blockDim.x)
+    sdl[t] = dlogits[(long long)img_begin * NOUT + t];
+  __syncthreads();
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nvec) return;
+  const int chunk = v / HW;
+  const int pix = v - chunk * HW;
+  const int h = pix / g.W, wc = pix - h * g.W;
+  const long long rowi = (long long)(h + 1) * g.PW + (wc + 1);
+  float wv[NOUT][8], dwv[NOUT][8];
+#pragma unroll
+  for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      wv[j][c] = W[j * K + (long long)(chunk * 8 + c) * HW + pix];
+      dwv[j][c] = 0.f;
+    }
+  const long long base = ((long long)chunk * g.plane_rows + kGuard + rowi) * 8;
+#pragma unroll 2
+  for (int img = img_begin; img < img_end; ++img) {
+    const long long off = base + (long long)img * g.PHW * 8;
+    const uint4 av = *reinterpret_cast<const uint4*>(act + off);
+    float a[8], gr[8];
+    unpack8(av, a);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) gr[c] = 0.f;
+    const float* dl = sdl + (img - img_begin) * NOUT;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      const float d = dl[j];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        gr[c] = fmaf(d, wv[j][c], gr[c]);
+        dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) gr[c] = a[c] > 0.f ? gr[c] : 0.f;
+    uint4 o;
+    o.x = pack_bf16x2(gr[0], gr[1]);
+    o.y = pack_bf16x2(gr[2], gr[3]);
+    o.z = pack_bf16x2(gr[4], gr[5]);
+    o.w = pack_bf16x2(gr[6], gr[7]);
+    *reinterpret_cast<uint4*>(dact + off) = o;
+  }
+  float* dst = dw_partial + (long long)blockIdx.y * NOUT * K;
+#pragma unroll
+  for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) dst[j * K + (long long)(chunk * 8 + c) * HW + pix] = dwv[j][c];
+}
+
+// Zero the rows of every plane between the end of the batch and the end of its last tile, so
+// the weight-gradient GEMM (which reduces over whole tiles) never sees stale rows after a
+// short tail batch (reference data.py:21-25 uses drop_last=False).
+__global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int nplanes, Geom g) {
+  const int first = g.batch * g.PHW;
+  const int nrows = g.ntiles * kTileM - first;
+  const long long total = (long long)nplanes * nrows;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int p = static_cast<int>(idx / nrows);
+    const int r = static_cast<int>(idx - (long long)p * nrows);
+    *reinterpret_cast<uint4*>(planes + ((long long)p * g.plane_rows + kGuard + first + r) * 8) =
+        make_uint4(0, 0, 0, 0);
+  }
+}
+
+// ------------------------------------------------------------------ SGD (single-GPU path)
+// p -= lr * g.  lr lives in device memory so a captured graph can be replayed with a new value.
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ grad,
+                           const float* __restrict__ lr, long long n) {
+  const float l = *lr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    p[i] = fmaf(-l, grad[i], p[i]);
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+static int g_num_sms[64] = {};
+
+extern "C" {
+
+int ddpb_num_sms() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (g_num_sms[dev & 63] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    g_num_sms[dev & 63] = n;
+  }
+  return g_num_sms[dev & 63];
+}
+
+long long ddpb_plane_rows(int batch_cap, int H, int W) { return plane_rows_for(batch_cap, H, W); }
+int ddpb_guard_rows() { return kGuard; }
+int ddpb_tile_rows() { return kTileM; }
+
+int ddpb_gather_u8(const void* images, const void* labels, const void* idx, float* x, void* y,
+                   int batch, int pix, void* stream) {
+  if (batch <= 0) return 0;
+  gather_u8_kernel<<<batch, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(images), static_cast<const long long*>(labels),
+      static_cast<const long long*>(idx), x, static_cast<long long*>(y), batch, pix);
+  return static_cast<int>(cudaGetLastError());
+}
+
+int ddpb_conv1_fwd(const float* x, const float* w, const float* b, void* out, int cin, int cout,
+                   int batch, int batch_cap, int H, int W, void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const long long total = (long long)(cout / 8) * g.ntiles * kTileM;
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)ddpb_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  conv1_fwd_kernel<1, 32><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, w, b, static_cast<__nv_bfloat16*>(out), g);
+  return static_cast<int>(cudaGetLastError());
+}
+
+static int conv1_wgrad_blocks(int batch, int H, int W) {
+  const int nrows = tiles_for(batch, H, W) * kTileM;
+  int bx = (nrows + 255) / 256;
+  if (bx > 256) bx = 256;
+  return bx;
+}
+size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, int W) {
+  return static_cast<size_t>(conv1_wgrad_blocks(batch_cap, H, W)) * (cout * cin * 9 + cout) *
+         sizeof(float);
+}
+// dw and db must be contiguous (dw[cout*cin*9] immediately followed by db[cout]); the gradient
+// arena lays parameters out that way.
+int ddpb_conv1_wgrad(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
+                     int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int bx = conv1_wgrad_blocks(batch, H, W);
+  conv1_wgrad_kernel<1, 32><<<dim3(bx, cout / 8), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
+  DDPB_CUDA_OK(cudaGetLastError());
+  const long long n = (long long)cout * cin * 9 + cout;
+  reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, bx, n,
+                                                                                    dw_db);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ---- linear layer launch geometry (shared by scratch-size queries and launches)
+static void linear_fwd_geom(int batch, int nvec, int& S, int& per, int& groups) {
+  constexpr int IMG = 8;
+  groups = (batch + IMG - 1) / IMG;
+  const int want = (2 * ddpb_num_sms() + groups - 1) / groups;  // ~2 CTAs per SM
+  const int maxS = (nvec + 255) / 256;
+  S = want < 1 ? 1 : (want > maxS ? maxS : want);
+  per = ((nvec + S - 1) / S + 255) / 256 * 256;
+  S = (nvec + per - 1) / per;
+}
+size_t ddpb_linear_fwd_scratch_bytes(int nout, int C, int batch_cap, int H, int W) {
+  // S is largest for the smallest batch; bound it by the feature-vector block count.
+  const int nvec = (C / 8) * H * W;
+  const int maxS = (nvec + 255) / 256;
+  return static_cast<size_t>(maxS) * batch_cap * nout * sizeof(float);
+}
+int ddpb_linear_fwd(const void* act, const float* Wt, float* partial, int* S_out, int nout, int C,
+                    int batch, int batch_cap, int H, int W, void* stream) {
+  if (nout != 10 || (C % 8) != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int nvec = (C / 8) * H * W;
+  int S, per, groups;
+  linear_fwd_geom(batch, nvec, S, per, groups);
+  linear_fwd_kernel<10, 8><<<dim3(S, groups), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(act), Wt, partial, g, C, per);
+  if (S_out) *S_out = S;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels,
+                      float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                      int batch, void* stream) {
+  if (nout != 10 || batch <= 0) return DDPB_ERR_SHAPE;
+  int threads = ((batch + 31) / 32) * 32;
+  if (threads > 1024) threads = 1024;
+  softmax_xent_kernel<10><<<1, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+      partial, S, bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss, batch);
+  return static_cast<int>(cudaGetLastError());
+}
+
+static int linear_bwd_imgs_per_split(int batch) {
+  // enough splits to fill the GPU at small batch, few enough that partial traffic stays small
+  if (batch <= 64) return 16;
+  if (batch <= 512) return 32;
+  return 64;
+}
+size_t ddpb_linear_bwd_scratch_bytes(int nout, int C, int batch_cap, int H, int W) {
+  size_t worst = 0;
+  const int cands[3] = {64 < batch_cap ? 64 : batch_cap, 512 < batch_cap ? 512 : batch_cap, batch_cap};
+  for (int i = 0; i < 3; ++i) {
+    const int ips = linear_bwd_imgs_per_split(cands[i]);
+    const size_t splits = (cands[i] + ips - 1) / ips;
+    if (splits > worst) worst = splits;
+  }
+  return worst * nout * static_cast<size_t>(C) * H * W * sizeof(float);
+}
+int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void* dact, float* dW,
+                    float* scratch, int nout, int C, int batch, int batch_cap, int H, int W,
+                    void* stream) {
+  if (nout != 10 || (C % 8) != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nvec = (C / 8) * H * W;
+  const int ips = linear_bwd_imgs_per_split(batch);
+  const int splits = (batch + ips - 1) / ips;
+  if (g.ntiles * kTileM > batch * g.PHW) {
+    zero_tail_rows_kernel<<<8, 256, 0, st>>>(static_cast<__nv_bfloat16*>(dact), C / 8, g);
+    DDPB_CUDA_OK(cudaGetLastError());
+  }
+  linear_bwd_kernel<10><<<dim3((nvec + 255) / 256, splits), 256, ips * 10 * sizeof(float), st>>>(
+      static_cast<const __nv_bfloat16*>(act), dlogits, Wt, static_cast<__nv_bfloat16*>(dact),
+      scratch, g, C, ips);
+  DDPB_CUDA_OK(cudaGetLastError());
+  const long long n = (long long)nout * C * H * W;
+  reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, splits,
+                                                                                    n, dW);
+  return static_cast<int>(cudaGetLastError());
+}
+
+int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream) {
+  long long blocks = (n + 1023) / 1024;
+  if (blocks > 592) blocks = 592;
+  if (blocks < 1) blocks = 1;
+  sgd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, grad, lr_dev, n);
+  return static_cast<int>(cudaGetLastError());
+}
+
+const char* ddpb_error_string(int code) {
+  switch (code) {
+    case DDPB_ERR_SHAPE: return "ddp_b200: unsupported shape or argument";
+    case DDPB_ERR_STATE: return "ddp_b200: call made in the wrong state";
+    case DDPB_ERR_LIMIT: return "ddp_b200: size exceeds a fixed limit of this entry point";
+    default: return cudaGetErrorString(static_cast<cudaError_t>(code));
+  }
+}
+
+}  // extern "C"

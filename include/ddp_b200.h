@@ -1,0 +1,97 @@
+/* ddp_b200 — C ABI of the native library behind the B200 data-parallel trainer.
+ *
+ * Every function enqueues work on the CUDA stream passed as `stream` (a cudaStream_t cast to
+ * void*; NULL = the legacy default stream) and returns 0 on success, a cudaError_t value, or
+ * one of the DDPB_ERR_* codes below.  ddpb_error_string() renders any of them.
+ * Pointers are device pointers unless a comment says "host".  Nothing here allocates device
+ * memory unless the name says so (ddpb_comm_*): callers own all buffers, including scratch,
+ * and query scratch sizes with the *_scratch_bytes() functions.
+ *
+ * Layouts
+ *   parameters / gradients : fp32, the reference's state_dict layouts
+ *                            (conv weight [Cout][Cin][3][3], linear weight [Nout][C*H*W] with
+ *                            k = c*H*W + h*W + w, reference model.py:8-16).
+ *   activations            : bf16 "padded planar-chunk" planes, see csrc/layout.cuh:
+ *                            C/8 planes x ddpb_plane_rows(batch_cap,H,W) rows x 8 channels;
+ *                            pixel (b,h,w) is row ddpb_guard_rows() + b*(H+2)*(W+2) + (h+1)*(W+2) + (w+1).
+ *                            Buffers must be zero-filled once after allocation.
+ *   `batch` is the number of images in this step, `batch_cap` the capacity the activation
+ *   buffers were sized for (batch <= batch_cap), so a short tail batch reuses the same buffers
+ *   (reference data.py:21-25 keeps the last short batch: drop_last=False).
+ *
+ * The reference (zahmedy/PyTorch-Distributed-Data-Parallel-DDP-Trainer) has no native code; the
+ * comments name the reference line whose delegated library call each entry point replaces.
+ */
+#ifndef DDP_B200_H_
+#define DDP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPB_ERR_SHAPE 9001 /* unsupported shape / argument */
+#define DDPB_ERR_STATE 9002 /* call made in the wrong state */
+#define DDPB_ERR_LIMIT 9003 /* size beyond a documented fixed limit */
+
+const char* ddpb_error_string(int code);
+int ddpb_num_sms(void);
+
+/* ---- geometry of the activation layout */
+long long ddpb_plane_rows(int batch_cap, int H, int W);
+int ddpb_guard_rows(void);
+int ddpb_tile_rows(void);
+
+/* ---- input pipeline: x[i] = images[idx[i]]/255 (fp32 [batch][pix]), y[i] = labels[idx[i]].
+ * Replaces torchvision ToTensor + DataLoader collate, reference data.py:11-14,21-25. */
+int ddpb_gather_u8(const void* images_u8, const void* labels_i64, const void* idx_i64, float* x,
+                   void* y_i64, int batch, int pix, void* stream);
+
+/* ---- conv1 (Cin=1 -> 32), bias + ReLU fused; x is fp32 NCHW.  reference model.py:9-10 */
+int ddpb_conv1_fwd(const float* x, const float* w, const float* b, void* out_planes, int cin,
+                   int cout, int batch, int batch_cap, int H, int W, void* stream);
+/* dw_db: cout*cin*9 weight gradients immediately followed by cout bias gradients. */
+size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, int W);
+int ddpb_conv1_wgrad(const void* dact_planes, const float* x, float* dw_db, float* scratch,
+                     int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+
+/* ---- 3x3 pad-1 convolution on tcgen05 tensor cores (bf16 operands, fp32 accumulate in TMEM),
+ * operands fetched with bulk async copies.  reference model.py:11-12 (forward),
+ * train_ddp.py:199 (backward through cuDNN). Supported (cin,cout): (32,64). */
+int ddpb_conv3x3_fwd(const void* in_planes, const float* w, const float* bias, void* out_planes,
+                     int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+/* din = relu'(mask) * conv_transpose(dout, w); mask = the forward activation that fed the conv. */
+int ddpb_conv3x3_dgrad(const void* dout_planes, const float* w, const void* mask_planes,
+                       void* din_planes, int cin, int cout, int batch, int batch_cap, int H, int W,
+                       void* stream);
+size_t ddpb_conv3x3_wgrad_scratch_bytes(int cin, int cout);
+int ddpb_conv3x3_wgrad(const void* dout_planes, const void* in_planes, float* dw, float* db,
+                       float* scratch, int cin, int cout, int batch, int batch_cap, int H, int W,
+                       void* stream);
+
+/* ---- linear layer over the flattened activation (NCHW flatten order).  reference model.py:16,19.
+ * fwd writes per-slice partial logits partial[S][batch][nout]; *S_out (host) receives S. */
+size_t ddpb_linear_fwd_scratch_bytes(int nout, int C, int batch_cap, int H, int W);
+int ddpb_linear_fwd(const void* act_planes, const float* W_fl, float* partial, int* S_out,
+                    int nout, int C, int batch, int batch_cap, int H, int W, void* stream);
+/* loss = mean CE; dlogits = (softmax - onehot)/batch; dbias = column sums of dlogits;
+ * logits may be NULL.  reference train_ddp.py:40,198-199. */
+int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels_i64,
+                      float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                      int batch, void* stream);
+/* dact = relu'(act) * dlogits.W ; dW = dlogits^T.act (deterministic split + reduce). */
+size_t ddpb_linear_bwd_scratch_bytes(int nout, int C, int batch_cap, int H, int W);
+int ddpb_linear_bwd(const void* act_planes, const float* dlogits, const float* W_fl,
+                    void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,
+                    int batch_cap, int H, int W, void* stream);
+
+/* ---- p -= lr*g with lr read from device memory (single-GPU path; multi-GPU runs fuse the
+ * update into the all-reduce).  reference train_ddp.py:41,200. */
+int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDP_B200_H_ */

@@ -1,0 +1,191 @@
+"""ctypes binding of the native sm_100a library (``lib/libddp_b200.so``; C ABI in
+``include/ddp_b200.h``; sources in ``csrc/``).
+
+The reference has no native layer — every op below replaces a library call it delegates to
+PyTorch (cuDNN / cuBLAS / ATen / c10d).  There is deliberately no Python
+fallback here: on a GPU box a missing or stale library is an error, not a silent downgrade.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p, POINTER
+
+import torch
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG_DIR, "lib", "libddp_b200.so")
+
+_lib = None
+
+P = c_void_p
+I = c_int
+LL = c_longlong
+
+# name -> (restype, argtypes)
+_SIGNATURES = {
+    "ddpb_error_string": (c_char_p, [I]),
+    "ddpb_num_sms": (I, []),
+    "ddpb_plane_rows": (LL, [I, I, I]),
+    "ddpb_guard_rows": (I, []),
+    "ddpb_tile_rows": (I, []),
+    "ddpb_gather_u8": (I, [P, P, P, P, P, I, I, P]),
+    "ddpb_conv1_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_scratch_bytes": (c_size_t, [I, I, I, I, I]),
+    "ddpb_conv1_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_wgrad_scratch_bytes": (c_size_t, [I, I]),
+    "ddpb_conv3x3_wgrad": (I, [P, P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_linear_fwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
+    "ddpb_linear_fwd": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_softmax_xent": (I, [P, I, P, P, P, P, P, P, I, I, P]),
+    "ddpb_linear_bwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
+    "ddpb_linear_bwd": (I, [P, P, P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_sgd": (I, [P, P, P, LL, P]),
+}
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib() -> ctypes.CDLL:
+    """Load (once) and return the native library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NativeError(
+                f"{LIB_PATH} is missing: run `python build.py` (or __graft_entry__.build()) first")
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name, None)
+            if fn is None:
+                continue  # optional symbols are declared where they are used
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def declare(name: str, restype, argtypes) -> None:
+    """Register the signature of an entry point defined by another module of this package."""
+    _SIGNATURES[name] = (restype, argtypes)
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
+
+
+def check(code: int, what: str = "") -> None:
+    if code != 0:
+        msg = lib().ddpb_error_string(int(code))
+        raise NativeError(f"{what or 'native call'} failed: [{code}] {msg.decode() if msg else '?'}")
+
+
+def ptr(t) -> int | None:
+    """Device/host pointer of a tensor (None passes NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_ptr(stream=None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+# ----------------------------------------------------------------------------- geometry
+def plane_rows(batch_cap: int, H: int, W: int) -> int:
+    return int(lib().ddpb_plane_rows(batch_cap, H, W))
+
+
+def guard_rows() -> int:
+    return int(lib().ddpb_guard_rows())
+
+
+def alloc_planes(channels: int, batch_cap: int, H: int, W: int, device="cuda") -> torch.Tensor:
+    """Zero-filled activation buffer [C/8, plane_rows, 8] bf16."""
+    assert channels % 8 == 0
+    return torch.zeros(channels // 8, plane_rows(batch_cap, H, W), 8, dtype=torch.bfloat16,
+                       device=device)
+
+
+def scratch(nbytes: int, device="cuda") -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 16) // 4 + 4, dtype=torch.float32, device=device)
+
+
+# ----------------------------------------------------------------------------- op wrappers
+def gather_u8(images, labels, idx, x, y, stream=None):
+    batch = idx.numel()
+    pix = images[0].numel()
+    check(lib().ddpb_gather_u8(ptr(images), ptr(labels), ptr(idx), ptr(x), ptr(y), batch, pix,
+                               stream_ptr(stream)), "gather_u8")
+
+
+def conv1_fwd(x, w, b, out, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv1_fwd(ptr(x), ptr(w), ptr(b), ptr(out), w.shape[1], w.shape[0], batch,
+                               batch_cap, H, W, stream_ptr(stream)), "conv1_fwd")
+
+
+def conv1_wgrad_scratch_bytes(cin, cout, batch_cap, H, W) -> int:
+    return int(lib().ddpb_conv1_wgrad_scratch_bytes(cin, cout, batch_cap, H, W))
+
+
+def conv1_wgrad(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv1_wgrad(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
+                                 batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad")
+
+
+def conv3x3_fwd(inp, w, bias, out, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv3x3_fwd(ptr(inp), ptr(w), ptr(bias), ptr(out), w.shape[1], w.shape[0],
+                                 batch, batch_cap, H, W, stream_ptr(stream)), "conv3x3_fwd")
+
+
+def conv3x3_dgrad(dout, w, mask, din, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv3x3_dgrad(ptr(dout), ptr(w), ptr(mask), ptr(din), w.shape[1], w.shape[0],
+                                   batch, batch_cap, H, W, stream_ptr(stream)), "conv3x3_dgrad")
+
+
+def conv3x3_wgrad_scratch_bytes(cin, cout) -> int:
+    return int(lib().ddpb_conv3x3_wgrad_scratch_bytes(cin, cout))
+
+
+def conv3x3_wgrad(dout, inp, dw, db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv3x3_wgrad(ptr(dout), ptr(inp), ptr(dw), ptr(db), ptr(scr), cin, cout,
+                                   batch, batch_cap, H, W, stream_ptr(stream)), "conv3x3_wgrad")
+
+
+def linear_fwd_scratch_bytes(nout, C, batch_cap, H, W) -> int:
+    return int(lib().ddpb_linear_fwd_scratch_bytes(nout, C, batch_cap, H, W))
+
+
+def linear_fwd(act, Wfl, partial, nout, C, batch, batch_cap, H, W, stream=None) -> int:
+    """Returns S, the number of partial slices written."""
+    s = c_int(0)
+    check(lib().ddpb_linear_fwd(ptr(act), ptr(Wfl), ptr(partial), ctypes.byref(s), nout, C, batch,
+                                batch_cap, H, W, stream_ptr(stream)), "linear_fwd")
+    return s.value
+
+
+def softmax_xent(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch, stream=None):
+    check(lib().ddpb_softmax_xent(ptr(partial), S, ptr(bias), ptr(labels), ptr(logits),
+                                  ptr(dlogits), ptr(dbias), ptr(loss), nout, batch,
+                                  stream_ptr(stream)), "softmax_xent")
+
+
+def linear_bwd_scratch_bytes(nout, C, batch_cap, H, W) -> int:
+    return int(lib().ddpb_linear_bwd_scratch_bytes(nout, C, batch_cap, H, W))
+
+
+def linear_bwd(act, dlogits, Wfl, dact, dW, scr, nout, C, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_linear_bwd(ptr(act), ptr(dlogits), ptr(Wfl), ptr(dact), ptr(dW), ptr(scr),
+                                nout, C, batch, batch_cap, H, W, stream_ptr(stream)), "linear_bwd")
+
+
+def sgd(p, grad, lr_dev, stream=None):
+    check(lib().ddpb_sgd(ptr(p), ptr(grad), ptr(lr_dev), p.numel(), stream_ptr(stream)), "sgd")
