@@ -1,0 +1,442 @@
+// Symmetric-memory communicator and the gradient all-reduce kernels that replace DDP's Reducer +
+// NCCL all-reduce + "divide by world size" + foreach-SGD (reference train_ddp.py:34,199,200;
+// SURVEY.md X13,X16,K14) with ONE kernel per gradient bucket.
+//
+// Every rank (one process per GPU) cudaMalloc's an identically laid out buffer and exports it
+// with CUDA IPC; after the handle exchange (done by the Python side over torch.distributed)
+// every rank holds a device pointer to every peer's buffer.  On an NVSwitch box those pointers
+// are plain NVLink loads/stores at full bandwidth to any peer.
+//
+// Kernels (all: in-kernel flag barrier, no host synchronisation, CUDA-graph safe):
+//   one-shot  : wait until every peer's bucket is ready, read all W copies, sum in rank order
+//               0..W-1 (bit-identical on every rank), apply p -= lr/W * sum to the LOCAL params.
+//               One flag round.  Best when latency-bound.
+//   two-shot  : rank r reduces slice r only, computes the updated parameters of that slice and
+//               stores them into EVERY rank's parameter arena, then a second flag round.
+//               Moves 2(W-1)/W*S bytes per GPU instead of (W-1)*S.
+//   plain all-reduce (fp32 / bf16, one-shot or two-shot) for the size sweep, and a broadcast used
+//   for the initial parameter sync and for resume.
+//
+// Flag protocol: flag word [slot][block][src_rank] lives in the header of each rank's buffer and
+// is written only by src_rank (st.release.sys) with a per-(slot,block) monotonically increasing
+// epoch kept in device memory (so replaying a captured graph keeps counting).  Waiters spin on
+// their own copy with ld.acquire.sys and a wall-clock bound: a dead peer becomes a trap (a CUDA
+// error on the host), never a hung GPU.  Gradient buckets are double-buffered by step parity, so
+// a single flag round per bucket also protects buffer reuse.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string.h>
+#include <new>
+
+#include "ptx.cuh"
+#include "api_internal.cuh"
+
+namespace ddpb {
+
+constexpr int kMaxWorld = 8;
+constexpr int kSlots = 8;
+constexpr int kMaxBlocks = 160;
+constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * kMaxWorld;
+constexpr size_t kEpochWords = (size_t)kSlots * kMaxBlocks;
+// header: flags | epochs | status word, rounded up
+constexpr size_t kHeaderBytes = ((kFlagWords + kEpochWords + 64) * 4 + 4095) / 4096 * 4096;
+constexpr int kCommThreads = 512;
+
+struct Comm {
+  int rank = 0, world = 1, device = 0;
+  size_t bytes = 0;  // total buffer bytes incl. header
+  uint8_t* local = nullptr;
+  uint8_t* peer[kMaxWorld] = {};
+  bool opened[kMaxWorld] = {};
+  bool connected = false;
+  unsigned long long timeout_ns = 20ull * 1000 * 1000 * 1000;
+};
+
+struct PeerPtrs {
+  uint8_t* p[kMaxWorld];
+};
+
+__device__ __forceinline__ uint32_t* flag_word(uint8_t* base, int slot, int block, int src) {
+  return reinterpret_cast<uint32_t*>(base) + ((size_t)slot * kMaxBlocks + block) * kMaxWorld + src;
+}
+__device__ __forceinline__ uint32_t* epoch_word(uint8_t* base, int slot, int block) {
+  return reinterpret_cast<uint32_t*>(base) + kFlagWords + (size_t)slot * kMaxBlocks + block;
+}
+__device__ __forceinline__ uint32_t* status_word(uint8_t* base) {
+  return reinterpret_cast<uint32_t*>(base) + kFlagWords + kEpochWords;
+}
+
+// One flag round for this block: tell every peer "block `blockIdx.x` of rank `rank` reached
+// epoch e", then wait until every peer said the same.  Orders all prior global writes of the
+// whole block before the signal and all later reads after the wait.
+template <int WORLD>
+__device__ __forceinline__ void flag_round(const PeerPtrs& pp, int rank, int slot, uint32_t e,
+                                           unsigned long long timeout_ns) {
+  __syncthreads();
+  if (threadIdx.x < WORLD) {
+    const int r = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(flag_word(pp.p[r], slot, blockIdx.x, rank), e);
+    const uint32_t* mine = flag_word(pp.p[rank], slot, blockIdx.x, r);
+    if (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+      const uint64_t t0 = global_timer_ns();
+      uint32_t spins = 0;
+      while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+        if ((++spins & 0xff) == 0 && global_timer_ns() - t0 > timeout_ns) {
+          *status_word(pp.p[rank]) = 0xdead0000u | static_cast<uint32_t>(r);
+          __threadfence_system();
+          __trap();
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_f4(float* p, const float4& v) {
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
+               : "memory");
+}
+
+// ---------------------------------------------------------------- fused all-reduce + SGD
+// n4 = number of float4 elements in the bucket (buckets are 16-byte aligned slices).
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_sgd_oneshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
+                             long long n4, const float* __restrict__ lr,
+                             unsigned long long timeout_ns) {
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  const float scale = -(*lr) * (1.0f / WORLD);
+  float* params = reinterpret_cast<float*>(pp.p[rank] + param_off);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 v[WORLD];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      v[r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
+    float4 s = v[0];
+#pragma unroll
+    for (int r = 1; r < WORLD; ++r) {
+      s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+    }
+    float4 p = *reinterpret_cast<float4*>(params + i * 4);
+    p.x = fmaf(scale, s.x, p.x);
+    p.y = fmaf(scale, s.y, p.y);
+    p.z = fmaf(scale, s.z, p.z);
+    p.w = fmaf(scale, s.w, p.w);
+    *reinterpret_cast<float4*>(params + i * 4) = p;
+  }
+  if (threadIdx.x == 0) *ep = e;
+}
+
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_sgd_twoshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
+                             long long n4, const float* __restrict__ lr,
+                             unsigned long long timeout_ns) {
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  const float scale = -(*lr) * (1.0f / WORLD);
+  const long long per = (n4 + WORLD - 1) / WORLD;
+  const long long lo = per * rank;
+  const long long hi = lo + per < n4 ? lo + per : n4;
+  const float* params = reinterpret_cast<const float*>(pp.p[rank] + param_off);
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 v[WORLD];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      v[r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
+    float4 s = v[0];
+#pragma unroll
+    for (int r = 1; r < WORLD; ++r) {
+      s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+    }
+    float4 p = *reinterpret_cast<const float4*>(params + i * 4);
+    p.x = fmaf(scale, s.x, p.x);
+    p.y = fmaf(scale, s.y, p.y);
+    p.z = fmaf(scale, s.z, p.z);
+    p.w = fmaf(scale, s.w, p.w);
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      st_f4(reinterpret_cast<float*>(pp.p[r] + param_off) + i * 4, p);
+  }
+  flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
+  if (threadIdx.x == 0) *ep = e + 1;
+}
+
+// ---------------------------------------------------------------- plain all-reduce (sum)
+template <typename T>
+struct Vec16;
+template <>
+struct Vec16<float> {
+  static constexpr int N = 4;
+  __device__ static void add(float4& a, const float4& b) {
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+};
+template <>
+struct Vec16<__nv_bfloat16> {
+  static constexpr int N = 8;
+  // accumulate in fp32, round once per hop in rank order
+  __device__ static void add(float4& a, const float4& b) {
+    const uint32_t* ua = reinterpret_cast<const uint32_t*>(&a);
+    const uint32_t* ub = reinterpret_cast<const uint32_t*>(&b);
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      o[k] = pack_bf16x2(bf16_lo(ua[k]) + bf16_lo(ub[k]), bf16_hi(ua[k]) + bf16_hi(ub[k]));
+    a = *reinterpret_cast<float4*>(o);
+  }
+};
+
+// mode 0: one-shot (every rank reduces everything into its own `out`)
+// mode 1: two-shot (rank r reduces slice r and stores it into every rank's `out`)
+template <typename T, int WORLD, int MODE>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_kernel(PeerPtrs pp, int rank, int slot, size_t in_off, size_t out_off, long long nvec,
+                 unsigned long long timeout_ns) {
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  long long lo = 0, hi = nvec;
+  if (MODE == 1) {
+    const long long per = (nvec + WORLD - 1) / WORLD;
+    lo = per * rank;
+    hi = lo + per < nvec ? lo + per : nvec;
+  }
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 v[WORLD];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r)
+      v[r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + in_off) + i * 4);
+    float4 s = v[0];
+#pragma unroll
+    for (int r = 1; r < WORLD; ++r) Vec16<T>::add(s, v[r]);
+    if (MODE == 0) {
+      st_f4(reinterpret_cast<float*>(pp.p[rank] + out_off) + i * 4, s);
+    } else {
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) st_f4(reinterpret_cast<float*>(pp.p[r] + out_off) + i * 4, s);
+    }
+  }
+  // second round: (one-shot) peers finished reading my input, so the caller may overwrite it;
+  // (two-shot) every rank's slice has landed in my output.
+  flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
+  if (threadIdx.x == 0) *ep = e + 1;
+}
+
+// Every rank copies root's region into its own buffer (pull), bracketed by flag rounds.
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads)
+broadcast_kernel(PeerPtrs pp, int rank, int slot, int root, size_t off, long long nvec,
+                 unsigned long long timeout_ns) {
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  if (rank != root) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+         i += (long long)gridDim.x * blockDim.x)
+      st_f4(reinterpret_cast<float*>(pp.p[rank] + off) + i * 4,
+            ld_f4(reinterpret_cast<const float*>(pp.p[root] + off) + i * 4));
+  }
+  flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
+  if (threadIdx.x == 0) *ep = e + 1;
+}
+
+static int blocks_for(long long nvec, int world, bool twoshot) {
+  long long work = twoshot ? (nvec + world - 1) / world : nvec;
+  long long b = (work + 4 * kCommThreads - 1) / (4 * kCommThreads);
+  if (b < 1) b = 1;
+  const long long cap = nvec * 16 <= (8ll << 20) ? 48 : kMaxBlocks;
+  if (b > cap) b = cap;
+  return static_cast<int>(b);
+}
+
+static PeerPtrs peer_ptrs(const Comm* c) {
+  PeerPtrs pp;
+  for (int r = 0; r < kMaxWorld; ++r) pp.p[r] = r < c->world ? c->peer[r] : c->peer[c->rank];
+  return pp;
+}
+
+#define DDPB_DISPATCH_WORLD(W, ...)                   \
+  switch (W) {                                        \
+    case 1: { constexpr int WORLD = 1; __VA_ARGS__; } break; \
+    case 2: { constexpr int WORLD = 2; __VA_ARGS__; } break; \
+    case 4: { constexpr int WORLD = 4; __VA_ARGS__; } break; \
+    case 8: { constexpr int WORLD = 8; __VA_ARGS__; } break; \
+    default: return DDPB_ERR_SHAPE;                   \
+  }
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" {
+
+size_t ddpb_comm_header_bytes() { return kHeaderBytes; }
+int ddpb_comm_handle_bytes() { return static_cast<int>(sizeof(cudaIpcMemHandle_t)); }
+int ddpb_comm_max_world() { return kMaxWorld; }
+int ddpb_comm_num_slots() { return kSlots; }
+
+// Allocates this rank's symmetric buffer (header + payload_bytes, zero-filled) on the current
+// device.  world must be 1, 2, 4 or 8.
+int ddpb_comm_create(int rank, int world, size_t payload_bytes, void** out) {
+  if (!(world == 1 || world == 2 || world == 4 || world == 8) || rank < 0 || rank >= world)
+    return DDPB_ERR_SHAPE;
+  Comm* c = new (std::nothrow) Comm();
+  if (!c) return static_cast<int>(cudaErrorMemoryAllocation);
+  c->rank = rank;
+  c->world = world;
+  DDPB_CUDA_OK(cudaGetDevice(&c->device));
+  c->bytes = kHeaderBytes + (payload_bytes + 255) / 256 * 256;
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&c->local), c->bytes);
+  if (e != cudaSuccess) {
+    delete c;
+    return static_cast<int>(e);
+  }
+  DDPB_CUDA_OK(cudaMemset(c->local, 0, c->bytes));
+  DDPB_CUDA_OK(cudaDeviceSynchronize());
+  c->peer[rank] = c->local;
+  c->connected = (world == 1);
+  *out = c;
+  return 0;
+}
+
+int ddpb_comm_get_handle(void* comm, void* handle_out) {
+  Comm* c = static_cast<Comm*>(comm);
+  cudaIpcMemHandle_t h;
+  DDPB_CUDA_OK(cudaIpcGetMemHandle(&h, c->local));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+// all_handles: world * ddpb_comm_handle_bytes() bytes (host), rank-major.
+int ddpb_comm_connect(void* comm, const void* all_handles) {
+  Comm* c = static_cast<Comm*>(comm);
+  const uint8_t* hs = static_cast<const uint8_t*>(all_handles);
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, hs + (size_t)r * sizeof(h), sizeof(h));
+    void* p = nullptr;
+    DDPB_CUDA_OK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer[r] = static_cast<uint8_t*>(p);
+    c->opened[r] = true;
+  }
+  c->connected = true;
+  return 0;
+}
+
+void* ddpb_comm_local_ptr(void* comm) { return static_cast<Comm*>(comm)->local + kHeaderBytes; }
+void* ddpb_comm_peer_ptr(void* comm, int r) {
+  Comm* c = static_cast<Comm*>(comm);
+  return (r >= 0 && r < c->world && c->peer[r]) ? c->peer[r] + kHeaderBytes : nullptr;
+}
+size_t ddpb_comm_payload_bytes(void* comm) { return static_cast<Comm*>(comm)->bytes - kHeaderBytes; }
+void ddpb_comm_set_timeout_ms(void* comm, long long ms) {
+  static_cast<Comm*>(comm)->timeout_ns = static_cast<unsigned long long>(ms) * 1000000ull;
+}
+// Last status word written by a kernel that timed out waiting for a peer (0 = healthy).
+int ddpb_comm_status(void* comm, unsigned int* status_out) {
+  Comm* c = static_cast<Comm*>(comm);
+  return static_cast<int>(cudaMemcpy(status_out,
+                                     reinterpret_cast<uint32_t*>(c->local) + kFlagWords + kEpochWords,
+                                     4, cudaMemcpyDeviceToHost));
+}
+
+int ddpb_comm_destroy(void* comm) {
+  Comm* c = static_cast<Comm*>(comm);
+  if (!c) return 0;
+  cudaDeviceSynchronize();
+  for (int r = 0; r < c->world; ++r)
+    if (c->opened[r]) cudaIpcCloseMemHandle(c->peer[r]);
+  if (c->local) cudaFree(c->local);
+  delete c;
+  return 0;
+}
+
+// Offsets below are byte offsets into the payload (i.e. relative to ddpb_comm_local_ptr),
+// 16-byte aligned, identical on every rank.  algo: 1 = one-shot, 2 = two-shot, 0 = by size.
+int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long n_floats,
+                       const float* lr_dev, int algo, int slot, void* stream) {
+  Comm* c = static_cast<Comm*>(comm);
+  if (!c->connected) return DDPB_ERR_STATE;
+  if ((n_floats & 3) || (grad_off & 15) || (param_off & 15) || slot < 0 || slot >= kSlots)
+    return DDPB_ERR_SHAPE;
+  const long long n4 = n_floats / 4;
+  if (algo == 0) algo = (c->world <= 2 || n_floats * 4 <= (256 << 10)) ? 1 : 2;
+  const bool two = algo == 2;
+  const int blocks = blocks_for(n4, c->world, two);
+  const PeerPtrs pp = peer_ptrs(c);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t go = grad_off + kHeaderBytes, po = param_off + kHeaderBytes;
+  DDPB_DISPATCH_WORLD(c->world, {
+    if (two)
+      allreduce_sgd_twoshot_kernel<WORLD><<<blocks, kCommThreads, 0, st>>>(
+          pp, c->rank, slot, go, po, n4, lr_dev, c->timeout_ns);
+    else
+      allreduce_sgd_oneshot_kernel<WORLD><<<blocks, kCommThreads, 0, st>>>(
+          pp, c->rank, slot, go, po, n4, lr_dev, c->timeout_ns);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+// dtype: 0 = fp32, 1 = bf16.  out_off must not overlap in_off.
+int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, int dtype, int algo,
+                   int slot, void* stream) {
+  Comm* c = static_cast<Comm*>(comm);
+  if (!c->connected) return DDPB_ERR_STATE;
+  if ((nbytes & 15) || (in_off & 15) || (out_off & 15) || slot < 0 || slot >= kSlots)
+    return DDPB_ERR_SHAPE;
+  const long long nvec = nbytes / 16;
+  if (algo == 0) algo = (c->world <= 2 || nbytes <= (256 << 10)) ? 1 : 2;
+  const bool two = algo == 2;
+  const int blocks = blocks_for(nvec, c->world, two);
+  const PeerPtrs pp = peer_ptrs(c);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t io = in_off + kHeaderBytes, oo = out_off + kHeaderBytes;
+  DDPB_DISPATCH_WORLD(c->world, {
+    if (dtype == 0) {
+      if (two) allreduce_kernel<float, WORLD, 1><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
+      else allreduce_kernel<float, WORLD, 0><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
+    } else if (dtype == 1) {
+      if (two) allreduce_kernel<__nv_bfloat16, WORLD, 1><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
+      else allreduce_kernel<__nv_bfloat16, WORLD, 0><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
+    } else {
+      return DDPB_ERR_SHAPE;
+    }
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+int ddpb_broadcast(void* comm, size_t off, long long nbytes, int root, int slot, void* stream) {
+  Comm* c = static_cast<Comm*>(comm);
+  if (!c->connected) return DDPB_ERR_STATE;
+  if ((nbytes & 15) || (off & 15) || slot < 0 || slot >= kSlots || root < 0 || root >= c->world)
+    return DDPB_ERR_SHAPE;
+  const long long nvec = nbytes / 16;
+  const int blocks = blocks_for(nvec, c->world, false);
+  const PeerPtrs pp = peer_ptrs(c);
+  DDPB_DISPATCH_WORLD(c->world, {
+    broadcast_kernel<WORLD><<<blocks, kCommThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        pp, c->rank, slot, root, off + kHeaderBytes, nvec, c->timeout_ns);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // extern "C"

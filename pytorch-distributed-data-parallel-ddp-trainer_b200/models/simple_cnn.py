@@ -1,0 +1,249 @@
+"""SimpleCNN: conv(1->32,3x3,p1)+ReLU -> conv(32->64,3x3,p1)+ReLU -> flatten -> linear(50176->10).
+
+Same function, parameter names, shapes and initialisation as the reference classifier
+(reference model.py:4-20; state_dict keys net.0.*, net.2.*, fl.*), but built on a flat
+parameter/gradient arena (arena.py) with two execution paths:
+
+* ``SimpleCNN``      — CPU path (the reference's own gloo/CPU fallback contract,
+                       reference utils.py:6): torch ops + autograd writing straight into the
+                       gradient arena.  Also the numerical oracle for the GPU path.
+* ``SimpleCNNB200``  — B200 path: an explicit kernel sequence over the native sm_100a library
+                       (no autograd engine, no cuDNN/cuBLAS): conv1 SIMT, conv2 fwd/dgrad/wgrad
+                       on tcgen05 tensor cores, fused softmax-CE, split linear layer.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn.functional as F
+
+from .arena import ParamArena
+
+IMG_H = IMG_W = 28
+C1, C2, NCLS = 32, 64, 10
+FEATURES = C2 * IMG_H * IMG_W  # 50176
+
+SPECS = (
+    ("net.0.weight", (C1, 1, 3, 3)),
+    ("net.0.bias", (C1,)),
+    ("net.2.weight", (C2, C1, 3, 3)),
+    ("net.2.bias", (C2,)),
+    ("fl.weight", (NCLS, FEATURES)),
+    ("fl.bias", (NCLS,)),
+)
+# torch's Module.state_dict() records one `_metadata` entry per sub-module
+METADATA_KEYS = ("", "net", "net.0", "net.1", "net.2", "net.3", "net.4", "fl")
+# gradient-ready order: the linear layer's gradients exist right after its backward, before the
+# expensive conv backward — 96% of the bytes
+BUCKET_GROUPS = (("fl.weight", "fl.bias"),
+                 ("net.0.weight", "net.0.bias", "net.2.weight", "net.2.bias"))
+
+
+def _default_init_(arena: ParamArena, generator: torch.Generator | None = None) -> None:
+    """torch's default Conv2d/Linear init (kaiming-uniform a=sqrt(5) == U(-1/sqrt(fan_in), ..)
+    for weight and bias), drawn in module-construction order so that, under the same seed, the
+    values equal what ``SimpleCNN()`` of the reference produces (reference model.py:8-16)."""
+    with torch.no_grad():
+        for wname, bname in (("net.0.weight", "net.0.bias"), ("net.2.weight", "net.2.bias"),
+                             ("fl.weight", "fl.bias")):
+            w = arena.view(wname)
+            fan_in = w[0].numel()
+            bound = 1.0 / math.sqrt(fan_in)
+            wcpu = torch.empty(w.shape, dtype=torch.float32)
+            # kaiming_uniform_(a=sqrt(5)), spelled exactly as torch.nn.init computes it so the
+            # bounds agree to the last bit: gain = sqrt(2/(1+a^2)), bound = sqrt(3)*gain/sqrt(fan_in)
+            wbound = math.sqrt(3.0) * (math.sqrt(2.0 / (1 + math.sqrt(5) ** 2)) / math.sqrt(fan_in))
+            wcpu.uniform_(-wbound, wbound, generator=generator)
+            bcpu = torch.empty(arena.view(bname).shape, dtype=torch.float32)
+            bcpu.uniform_(-bound, bound, generator=generator)
+            w.copy_(wcpu)
+            arena.view(bname).copy_(bcpu)
+
+
+class _ModelBase:
+    """Shared state_dict / parameter plumbing (what nn.Module gives the reference)."""
+
+    arena: ParamArena
+
+    def state_dict(self) -> OrderedDict:
+        return self.arena.state_dict(METADATA_KEYS)
+
+    def load_state_dict(self, sd, strict: bool = True) -> None:
+        self.arena.load_state_dict(sd, strict=strict)
+
+    def named_parameters(self):
+        for s in self.arena.specs:
+            yield s.name, self.arena.view(s.name)
+
+    def parameters(self):
+        for _, p in self.named_parameters():
+            yield p
+
+    def buckets(self):
+        return self.arena.make_buckets(BUCKET_GROUPS)
+
+    def train(self, mode: bool = True):  # no dropout / batch-norm: nothing to switch
+        return self
+
+    def eval(self):
+        return self
+
+
+class SimpleCNN(_ModelBase):
+    """CPU execution path (also usable on CUDA as an fp32 oracle)."""
+
+    def __init__(self, device="cpu", params=None, grads=None, init: bool = True,
+                 generator: torch.Generator | None = None):
+        self.arena = ParamArena(SPECS, device=device, params=params, grads=grads)
+        if init:
+            _default_init_(self.arena, generator)
+        self.arena.params.requires_grad_(True)
+        # autograd accumulates in place into an existing .grad => gradients land in the arena
+        self.arena.params.grad = self.arena.grads
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        a = self.arena
+        h = F.relu(F.conv2d(x, a.view("net.0.weight"), a.view("net.0.bias"), padding=1))
+        h = F.relu(F.conv2d(h, a.view("net.2.weight"), a.view("net.2.bias"), padding=1))
+        return F.linear(h.flatten(1), a.view("fl.weight"), a.view("fl.bias"))
+
+    __call__ = forward
+
+    def forward_backward(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """loss = CE(model(x), y); gradients of the mean loss are written to the gradient arena."""
+        self.arena.grads.zero_()
+        loss = F.cross_entropy(self.forward(x), y)
+        loss.backward()
+        if self.arena.params.grad is not self.arena.grads:  # defensive: keep the arena authoritative
+            self.arena.grads.copy_(self.arena.params.grad)
+            self.arena.params.grad = self.arena.grads
+        return loss.detach()
+
+    def sgd_step(self, lr: float) -> None:
+        with torch.no_grad():
+            self.arena.params.add_(self.arena.grads, alpha=-lr)
+
+
+class SimpleCNNB200(_ModelBase):
+    """sm_100a execution path: explicit forward/backward kernel sequence on one GPU.
+
+    The step is split at the points where a gradient bucket becomes complete, so the engine
+    can launch that bucket's all-reduce while the rest of backward runs
+    (reference train_ddp.py:199 + DDP Reducer hooks):
+
+        forward_loss -> backward_head   (bucket 0: fl.weight, fl.bias ready)
+                     -> backward_body   (bucket 1: net.2.*, net.0.* ready)
+    """
+
+    def __init__(self, batch_cap: int, device="cuda", params=None, grads=None, init: bool = True,
+                 generator: torch.Generator | None = None, alt_grads=None):
+        from ..ops import native as nat
+        self.nat = nat
+        nat.lib()
+        self.device = torch.device(device)
+        self.batch_cap = int(batch_cap)
+        self.arena = ParamArena(SPECS, device=self.device, params=params, grads=grads)
+        if init:
+            _default_init_(self.arena, generator)
+        H, W = IMG_H, IMG_W
+        with torch.cuda.device(self.device):
+            dev = self.device
+            self.act1 = nat.alloc_planes(C1, batch_cap, H, W, dev)
+            self.act2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
+            self.dact2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
+            self.dact1 = nat.alloc_planes(C1, batch_cap, H, W, dev)
+            self.lin_partial = nat.scratch(nat.linear_fwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+            self.logits = torch.zeros(batch_cap, NCLS, device=dev)
+            self.dlogits = torch.zeros(batch_cap, NCLS, device=dev)
+            self.loss = torch.zeros(1, device=dev)
+            self.scr_lin = nat.scratch(nat.linear_bwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+            self.scr_w2 = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(C1, C2), dev)
+            self.scr_w1 = nat.scratch(nat.conv1_wgrad_scratch_bytes(1, C1, batch_cap, H, W), dev)
+            self.lr_dev = torch.full((1,), 0.01, device=dev)
+        a = self.arena
+        self.w1, self.b1 = a.view("net.0.weight"), a.view("net.0.bias")
+        self.w2, self.b2 = a.view("net.2.weight"), a.view("net.2.bias")
+        self.wf, self.bf = a.view("fl.weight"), a.view("fl.bias")
+        # Gradient arenas: one per step parity when a communicator double-buffers them so that a
+        # single flag round per bucket also covers buffer reuse (csrc/comm.cu); otherwise one.
+        self.grad_sets = []
+        for gbuf in ([a.grads] if alt_grads is None else [a.grads, alt_grads]):
+            self.grad_sets.append({
+                "flat": gbuf,
+                "w1": a.view("net.0.weight", gbuf),  # followed in memory by net.0.bias
+                "w2": a.view("net.2.weight", gbuf), "b2": a.view("net.2.bias", gbuf),
+                "wf": a.view("fl.weight", gbuf), "bf": a.view("fl.bias", gbuf),
+            })
+
+    # ------------------------------------------------------------------ step pieces
+    def forward_loss(self, x: torch.Tensor, y: torch.Tensor, batch: int | None = None, stream=None,
+                     parity: int = 0):
+        nat = self.nat
+        gs = self.grad_sets[parity]
+        b = int(batch if batch is not None else x.shape[0])
+        assert 0 < b <= self.batch_cap
+        cap, H, W = self.batch_cap, IMG_H, IMG_W
+        nat.conv1_fwd(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
+        nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W, stream)
+        S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
+        nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, gs["bf"],
+                         self.loss, NCLS, b, stream)
+        return self.loss
+
+    def backward_head(self, batch: int, stream=None, parity: int = 0):
+        """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel)."""
+        gs = self.grad_sets[parity]
+        self.nat.linear_bwd(self.act2, self.dlogits, self.wf, self.dact2, gs["wf"], self.scr_lin,
+                            NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
+
+    def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
+        """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""
+        nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
+        gs = self.grad_sets[parity]
+        nat.conv3x3_wgrad(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
+                          cap, H, W, stream)
+        nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
+        nat.conv1_wgrad(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
+
+    def forward_backward(self, x: torch.Tensor, y: torch.Tensor, stream=None,
+                         parity: int = 0) -> torch.Tensor:
+        b = int(x.shape[0])
+        self.forward_loss(x, y, b, stream, parity)
+        self.backward_head(b, stream, parity)
+        self.backward_body(x, b, stream, parity)
+        return self.loss
+
+    def launches_per_step(self, batch: int) -> int:
+        """Kernels one forward+backward launches (bench.py reports it as part of gpu_launches)."""
+        from ..ops import layout as lay
+        tail = 1 if lay.tiles_for(batch, IMG_H, IMG_W) * lay.TILE_M > batch * 900 else 0
+        return 4 + (2 + tail) + 2 + 1 + 2
+
+    def sgd_step(self, lr: float | None = None, stream=None) -> None:
+        if lr is not None:
+            self.lr_dev.fill_(float(lr))
+        n = self.arena.numel
+        self.nat.sgd(self.arena.params[:n], self.arena.grads[:n], self.lr_dev, stream)
+
+    def train_step(self, x: torch.Tensor, y: torch.Tensor, lr: float = 0.01) -> torch.Tensor:
+        """Single-GPU convenience: forward, backward, SGD.  Returns the (device) loss tensor."""
+        self.forward_backward(x, y)
+        self.sgd_step(lr)
+        return self.loss
+
+    @torch.no_grad()
+    def predict(self, x: torch.Tensor) -> torch.Tensor:
+        """Forward only; returns logits [batch, 10] (a view of an internal buffer)."""
+        nat = self.nat
+        b = int(x.shape[0])
+        cap, H, W = self.batch_cap, IMG_H, IMG_W
+        y = torch.zeros(b, dtype=torch.int64, device=self.device)
+        scratch_db = torch.empty(NCLS, device=self.device)
+        nat.conv1_fwd(x, self.w1, self.b1, self.act1, b, cap, H, W)
+        nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W)
+        S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W)
+        nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, scratch_db,
+                         self.loss, NCLS, b)
+        return self.logits[:b]

@@ -1,0 +1,242 @@
+"""Data-parallel step engines: what ``DDP(model)`` + ``loss.backward()`` + ``opt.step()`` are in the
+reference (reference train_ddp.py:34,196-200), re-designed around a flat arena.
+
+``CpuDataParallel``   gloo path (the reference's CPU fallback): torch ops, bucketed
+                      ``dist.all_reduce`` on slices of the gradient arena, in-place SGD.
+``B200DataParallel``  B200 path: static kernel sequence (models/simple_cnn.py), gradient buckets
+                      all-reduced by the fused all-reduce+SGD kernel over the symmetric-memory
+                      communicator, bucket 0 on a side stream so it overlaps the conv backward,
+                      the whole step captured once per (batch size, parity) in a CUDA graph.
+
+Both: parameters are broadcast from rank 0 at construction (what DDP's constructor does,
+SURVEY.md X13) so all ranks start identical without any seed being set.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from ..models.simple_cnn import IMG_H, IMG_W, SimpleCNN, SimpleCNNB200
+from ..utils.checkpoint import sgd_state_dict
+
+
+def _align(n: int, a: int) -> int:
+    return (n + a - 1) // a * a
+
+
+class _EngineBase:
+    lr: float
+    model: object
+
+    def state_dict(self):
+        return self.model.state_dict()
+
+    def optimizer_state_dict(self) -> dict:
+        return sgd_state_dict(self.lr, len(self.model.arena.specs))
+
+    def set_lr(self, lr: float) -> None:
+        self.lr = float(lr)
+
+
+class CpuDataParallel(_EngineBase):
+    def __init__(self, rank: int, world_size: int, lr: float = 0.01, device="cpu"):
+        self.rank, self.world_size, self.lr = rank, world_size, float(lr)
+        self.device = torch.device(device)
+        self.model = SimpleCNN(device=self.device)
+        self.buckets = self.model.buckets()
+        self.sync_params()
+
+    @property
+    def flat_params(self) -> torch.Tensor:
+        return self.model.arena.params
+
+    def sync_params(self, src: int = 0) -> None:
+        if self.world_size > 1:
+            dist.broadcast(self.model.arena.params.detach(), src=src)
+
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        loss = self.model.forward_backward(x, y)
+        a = self.model.arena
+        if self.world_size > 1:
+            works = [dist.all_reduce(a.grads[b.start:b.start + b.numel], async_op=True)
+                     for b in self.buckets]
+            for w in works:
+                w.wait()
+        with torch.no_grad():
+            a.params.add_(a.grads, alpha=-self.lr / self.world_size)
+        return loss
+
+    def read_loss(self, loss) -> float:
+        return float(loss)
+
+    def close(self) -> None:
+        pass
+
+
+class B200DataParallel(_EngineBase):
+    def __init__(self, rank: int, world_size: int, device, batch_cap: int, lr: float = 0.01,
+                 use_graph: bool = True, algo: int = 0, timeout_ms: int | None = None):
+        from .comm import SymmetricComm
+        self.rank, self.world_size, self.lr = rank, world_size, float(lr)
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.batch_cap = int(batch_cap)
+        self.use_graph = use_graph
+        self.algo = algo
+
+        from ..models.arena import ParamArena
+        from ..models.simple_cnn import SPECS
+        n = ParamArena(SPECS, device="meta").padded_numel
+        self._n = n
+        region = _align(n * 4, 256)
+        self.param_off, self.grad_off = 0, [region, 2 * region]
+        self.comm = SymmetricComm(rank, world_size, 3 * region, timeout_ms=timeout_ms)
+        params = self.comm.tensor(self.param_off, n)
+        grads = [self.comm.tensor(off, n) for off in self.grad_off]
+        self.model = SimpleCNNB200(batch_cap, self.device, params=params, grads=grads[0],
+                                   alt_grads=grads[1])
+        self.model.lr_dev.fill_(self.lr)
+        # bucket slices rounded to whole float4 (the arena tail is zero padding)
+        self.buckets = [(b.start, _align(b.numel, 4)) for b in self.model.buckets()]
+        assert all(s % 4 == 0 and s + m <= n for s, m in self.buckets)
+
+        self.main = torch.cuda.Stream(self.device)
+        self.side = torch.cuda.Stream(self.device)
+        self.copy = torch.cuda.Stream(self.device)
+        self._ev_fork = torch.cuda.Event()
+        self._ev_join = torch.cuda.Event()
+        self._ev_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self._ev_free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.x_in = [torch.zeros(batch_cap, 1, IMG_H, IMG_W, device=self.device) for _ in range(2)]
+        self.y_in = [torch.zeros(batch_cap, dtype=torch.int64, device=self.device) for _ in range(2)]
+        self.loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self._ev_loss = [torch.cuda.Event(), torch.cuda.Event()]
+        self._graphs: dict = {}
+        self._seen: dict = {}
+        self.step_count = 0
+        self.sync_params()
+
+    # ------------------------------------------------------------------ parameters
+    @property
+    def flat_params(self) -> torch.Tensor:
+        return self.model.arena.params
+
+    def set_lr(self, lr: float) -> None:
+        self.lr = float(lr)
+        self.model.lr_dev.fill_(self.lr)
+
+    def sync_params(self, src: int = 0) -> None:
+        """Initial (and post-resume) parameter broadcast from ``src`` over the peer-mapped arena."""
+        torch.cuda.synchronize(self.device)
+        if self.world_size > 1:
+            self.comm.broadcast(self.param_off, self._n * 4, root=src, slot=7, stream=self.main)
+            self.main.synchronize()
+
+    # ------------------------------------------------------------------ the step
+    def launches_per_step(self, batch: int) -> int:
+        return self.model.launches_per_step(batch) + (2 if self.world_size > 1 else 1)
+
+    def _enqueue(self, b: int, parity: int) -> None:
+        """Enqueue one full training step on self.main (+ self.side); capturable."""
+        m, main = self.model, self.main
+        x, y = self.x_in[parity][:b], self.y_in[parity][:b]
+        m.forward_loss(x, y, b, main, parity)
+        m.backward_head(b, main, parity)
+        if self.world_size > 1:
+            (s0, n0), (s1, n1) = self.buckets
+            goff = self.grad_off[parity]
+            self._ev_fork.record(main)
+            self.side.wait_event(self._ev_fork)
+            self.comm.allreduce_sgd(goff + s0 * 4, self.param_off + s0 * 4, n0, m.lr_dev,
+                                    self.algo, slot=0, stream=self.side)
+            self._ev_join.record(self.side)
+            m.backward_body(x, b, main, parity)
+            self.comm.allreduce_sgd(goff + s1 * 4, self.param_off + s1 * 4, n1, m.lr_dev,
+                                    self.algo, slot=1, stream=main)
+            main.wait_event(self._ev_join)
+        else:
+            m.backward_body(x, b, main, parity)
+            n = m.arena.numel
+            m.nat.sgd(m.arena.params[:n], m.grad_sets[parity]["flat"][:n], m.lr_dev, main)
+
+    def acquire_inputs(self):
+        """Device buffers the next step() will read.  A loader may fill them in place on the
+        current stream: that stream is first made to wait for the step that last read them."""
+        p = self.step_count & 1
+        torch.cuda.current_stream(self.device).wait_event(self._ev_free[p])
+        return self.x_in[p], self.y_in[p]
+
+    def state_dict(self):
+        self.synchronize()
+        return self.model.state_dict()
+
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One data-parallel training step.  ``x`` float32 [b,1,28,28], ``y`` int64 [b]; CPU
+        (ideally pinned) or CUDA tensors.  Returns the device loss scalar (valid on self.main;
+        use read_loss() for a synchronised Python float)."""
+        b = int(x.shape[0])
+        parity = self.step_count & 1
+        xin, yin = self.x_in[parity], self.y_in[parity]
+        if x.data_ptr() != xin.data_ptr():
+            if x.is_cuda:
+                cur = torch.cuda.current_stream(self.device)
+                self.main.wait_stream(cur)
+                with torch.cuda.stream(self.main):
+                    xin[:b].copy_(x, non_blocking=True)
+                    yin[:b].copy_(y, non_blocking=True)
+            else:
+                with torch.cuda.stream(self.copy):
+                    self.copy.wait_event(self._ev_free[parity])
+                    xin[:b].copy_(x, non_blocking=True)
+                    yin[:b].copy_(y, non_blocking=True)
+                    self._ev_ready[parity].record(self.copy)
+                self.main.wait_event(self._ev_ready[parity])
+        else:
+            self.main.wait_stream(torch.cuda.current_stream(self.device))
+        key = (b, parity)
+        seen = self._seen.get(key, 0)
+        self._seen[key] = seen + 1
+        if self.use_graph and seen >= 1:
+            g = self._graphs.get(key)
+            if g is None:
+                g = torch.cuda.CUDAGraph()
+                self.main.synchronize()
+                with torch.cuda.graph(g, stream=self.main):
+                    self._enqueue(b, parity)
+                self._graphs[key] = g
+            with torch.cuda.stream(self.main):
+                g.replay()
+        else:
+            with torch.cuda.stream(self.main):
+                self._enqueue(b, parity)
+        with torch.cuda.stream(self.main):
+            self.loss_host[parity:parity + 1].copy_(self.model.loss, non_blocking=True)
+            self._ev_loss[parity].record(self.main)
+            self._ev_free[parity].record(self.main)
+        self.step_count += 1
+        return self.model.loss
+
+    def read_loss(self, loss=None) -> float:
+        """Loss of the most recent step as a Python float (waits for that step only)."""
+        parity = (self.step_count - 1) & 1
+        self._ev_loss[parity].synchronize()
+        return float(self.loss_host[parity])
+
+    def synchronize(self) -> None:
+        self.main.synchronize()
+        self.side.synchronize()
+        self.copy.synchronize()
+
+    def close(self) -> None:
+        self.synchronize()
+        self._graphs.clear()
+        self.comm.close()
+
+
+def make_engine(rank: int, world_size: int, device, batch_cap: int, lr: float = 0.01, **kw):
+    """CUDA device -> B200DataParallel, CPU -> CpuDataParallel (the reference's backend switch,
+    reference utils.py:6)."""
+    device = torch.device(device)
+    if device.type == "cuda":
+        return B200DataParallel(rank, world_size, device, batch_cap, lr=lr, **kw)
+    return CpuDataParallel(rank, world_size, lr=lr, device=device)

@@ -1,0 +1,84 @@
+"""CPU model path: same function and initialisation as the reference classifier
+(reference model.py:4-20), gradients land in the flat arena, buckets are contiguous slices."""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ddp_b200.models.simple_cnn import SimpleCNN
+
+
+def _torch_modules():
+    net = nn.Sequential(nn.Conv2d(1, 32, 3, padding=1), nn.ReLU(), nn.Conv2d(32, 64, 3, padding=1),
+                        nn.ReLU(), nn.Flatten())
+    fl = nn.Linear(50176, 10)
+    return net, fl
+
+
+def test_param_count_and_layout():
+    m = SimpleCNN()
+    assert m.arena.numel == 520586
+    assert [s.offset for s in m.arena.specs] == [0, 288, 320, 18752, 18816, 520576]
+    b0, b1 = m.buckets()
+    assert (b0.start, b0.numel) == (18816, 501770)      # fl.weight + fl.bias: 2,007,080 B
+    assert (b1.start, b1.numel) == (0, 18816)           # conv params: 75,264 B
+    assert b0.numel * 4 == 2007080 and b1.numel * 4 == 75264
+
+
+def test_init_matches_torch_default_under_same_seed():
+    torch.manual_seed(42)
+    m = SimpleCNN()
+    torch.manual_seed(42)
+    net, fl = _torch_modules()
+    sd = m.state_dict()
+    assert torch.equal(sd["net.0.weight"], net[0].weight)
+    assert torch.equal(sd["net.0.bias"], net[0].bias)
+    assert torch.equal(sd["net.2.weight"], net[2].weight)
+    assert torch.equal(sd["net.2.bias"], net[2].bias)
+    assert torch.equal(sd["fl.weight"], fl.weight)
+    assert torch.equal(sd["fl.bias"], fl.bias)
+
+
+def test_forward_backward_matches_autograd_modules():
+    torch.manual_seed(0)
+    m = SimpleCNN()
+    torch.manual_seed(0)
+    net, fl = _torch_modules()
+    x = torch.rand(5, 1, 28, 28)
+    y = torch.randint(0, 10, (5,))
+    loss = m.forward_backward(x, y)
+    ref = F.cross_entropy(fl(net(x)), y)
+    ref.backward()
+    assert torch.allclose(loss, ref.detach(), atol=1e-6)
+    assert m.arena.params.grad is m.arena.grads
+    for name, p in (("net.0.weight", net[0].weight), ("net.0.bias", net[0].bias),
+                    ("net.2.weight", net[2].weight), ("net.2.bias", net[2].bias),
+                    ("fl.weight", fl.weight), ("fl.bias", fl.bias)):
+        assert torch.allclose(m.arena.grad_view(name), p.grad, atol=1e-6), name
+    # second step: gradients are overwritten, not accumulated
+    m.forward_backward(x, y)
+    assert torch.allclose(m.arena.grad_view("fl.bias"), fl.bias.grad, atol=1e-6)
+
+
+def test_sgd_step_matches_torch_sgd():
+    torch.manual_seed(0)
+    m = SimpleCNN()
+    torch.manual_seed(0)
+    net, fl = _torch_modules()
+    opt = torch.optim.SGD(list(net.parameters()) + list(fl.parameters()), lr=0.01)
+    x = torch.rand(4, 1, 28, 28)
+    y = torch.randint(0, 10, (4,))
+    for _ in range(3):
+        m.forward_backward(x, y)
+        m.sgd_step(0.01)
+        opt.zero_grad()
+        F.cross_entropy(fl(net(x)), y).backward()
+        opt.step()
+    assert torch.allclose(m.arena.view("fl.weight").detach(), fl.weight.detach(), atol=1e-6)
+    assert torch.allclose(m.arena.view("net.2.weight").detach(), net[2].weight.detach(), atol=1e-6)
+
+
+def test_state_dict_is_a_copy():
+    m = SimpleCNN()
+    sd = m.state_dict()
+    sd["fl.bias"].add_(1.0)
+    assert not torch.equal(sd["fl.bias"], m.arena.view("fl.bias").detach())

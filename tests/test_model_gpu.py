@@ -1,0 +1,102 @@
+"""End-to-end slice on one B200: the sm_100a kernel path must track the
+fp32 PyTorch oracle step for step, through the engine (CUDA graph included), and write a
+checkpoint the reference loads."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return torch.device("cuda", 0)
+
+
+def test_gradients_match_oracle(cuda):
+    from ddp_b200.models.simple_cnn import SimpleCNN, SimpleCNNB200
+    torch.manual_seed(0)
+    oracle = SimpleCNN(device=cuda)
+    gpu = SimpleCNNB200(batch_cap=64, device=cuda, init=False)
+    gpu.load_state_dict(oracle.state_dict())
+    x = torch.rand(64, 1, 28, 28, device=cuda)
+    y = torch.randint(0, 10, (64,), device=cuda)
+    want = oracle.forward_backward(x, y)
+    got = gpu.forward_backward(x, y)
+    torch.cuda.synchronize()
+    assert abs(got.item() - want.item()) < 5e-3
+    for name in ("fl.bias", "fl.weight", "net.2.bias", "net.2.weight", "net.0.bias", "net.0.weight"):
+        g, w = gpu.arena.grad_view(name), oracle.arena.grad_view(name)
+        scale = w.abs().max().item()
+        err = (g - w).abs().max().item()
+        assert err <= 3e-2 * scale + 1e-6, (name, err, scale)
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_training_tracks_oracle_and_short_batches(cuda, use_graph):
+    from ddp_b200.models.simple_cnn import SimpleCNN
+    from ddp_b200.parallel.engine import B200DataParallel
+    torch.manual_seed(1)
+    oracle = SimpleCNN(device=cuda)
+    eng = B200DataParallel(0, 1, cuda, batch_cap=32, lr=0.05, use_graph=use_graph)
+    eng.model.load_state_dict(oracle.state_dict())
+    torch.manual_seed(2)
+    xs = torch.rand(8, 32, 1, 28, 28, device=cuda)
+    ys = torch.randint(0, 10, (8, 32), device=cuda)
+    losses_o, losses_g = [], []
+    for i in range(16):
+        b = 32 if i % 5 != 4 else 19          # a short tail batch every fifth step
+        x, y = xs[i % 8, :b], ys[i % 8, :b]
+        lo = oracle.forward_backward(x, y)
+        oracle.sgd_step(0.05)
+        eng.step(x, y)
+        losses_o.append(lo.item())
+        losses_g.append(eng.read_loss())
+    eng.synchronize()
+    for a, b in zip(losses_o, losses_g):
+        assert abs(a - b) < 2e-2 * max(1.0, abs(a)), (losses_o, losses_g)
+    assert losses_g[-1] < losses_g[0]
+    for name in ("fl.weight", "net.2.weight", "net.0.weight"):
+        p, q = eng.model.arena.view(name), oracle.arena.view(name).detach()
+        assert (p - q).abs().max().item() < 5e-3, name
+    eng.close()
+
+
+def test_cpu_pinned_inputs_and_checkpoint_roundtrip(cuda, tmp_path):
+    from ddp_b200.models.simple_cnn import SimpleCNN
+    from ddp_b200.parallel.engine import B200DataParallel
+    from ddp_b200.utils import checkpoint as ck
+    torch.manual_seed(3)
+    eng = B200DataParallel(0, 1, cuda, batch_cap=16, lr=0.01)
+    x = torch.rand(16, 1, 28, 28).pin_memory()
+    y = torch.randint(0, 10, (16,)).pin_memory()
+    first = None
+    for _ in range(6):
+        eng.step(x, y)
+        first = first if first is not None else eng.read_loss()
+    last = eng.read_loss()
+    assert last < first
+    path = ck.save_checkpoint(0, eng.state_dict(), eng.optimizer_state_dict(), str(tmp_path))
+    c = ck.load_checkpoint(path)
+    cpu = SimpleCNN(init=False)
+    cpu.load_state_dict(c["model"])
+    logits_cpu = cpu(x)
+    logits_gpu = eng.model.predict(x.to(cuda)).cpu()
+    assert torch.allclose(logits_cpu, logits_gpu, atol=3e-2, rtol=3e-2)
+    assert c["optimizer"]["param_groups"][0]["lr"] == 0.01
+    eng.close()
+
+
+def test_device_loader_matches_cpu_loader(cuda):
+    from ddp_b200.utils.data import get_dataloader, synthetic_mnist
+    ds = synthetic_mnist(n=300, seed=5)
+    lc, sc = get_dataloader(64, 2, 1, device="cpu", dataset=ds)
+    lg, sg = get_dataloader(64, 2, 1, device=cuda, dataset=ds)
+    sc.set_epoch(3)
+    sg.set_epoch(3)
+    assert len(lc) == len(lg) == 3
+    for (xc, yc), (xg, yg) in zip(lc, lg):
+        assert torch.equal(xc, xg.cpu()) and torch.equal(yc, yg.cpu())
+        assert xg.shape[1:] == (1, 28, 28) and xg.dtype == torch.float32
