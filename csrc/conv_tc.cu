@@ -27,11 +27,22 @@ struct ConvSmem {
   static constexpr uint32_t w_bytes = 9 * w_tap_bytes;
   static constexpr uint32_t a_stage_bytes = KP * kStagePlaneBytes;
   static constexpr uint32_t off_a = w_bytes;
-  static constexpr uint32_t off_bias = off_a + STAGES * a_stage_bytes;
+  // fp32 master weights are bulk-copied (TMA) into a staging area and converted from there.
+  // It aliases the A-stage ring when that is large enough (the ring is idle during setup).
+  static constexpr uint32_t wstage_bytes = 9 * CI * CO * 4;
+  static constexpr bool stage_aliases_ring = STAGES * a_stage_bytes >= wstage_bytes;
+  static constexpr uint32_t off_wstage = stage_aliases_ring ? off_a : off_a + STAGES * a_stage_bytes;
+  static constexpr uint32_t off_bias =
+      off_a + STAGES * a_stage_bytes + (stage_aliases_ring ? 0 : wstage_bytes);
   static constexpr uint32_t off_bar = off_bias + CO * 4;
-  static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 4) * 8;
+  static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 5) * 8;
   static constexpr uint32_t total = off_tmem + 16;
 };
+
+// Optional in-kernel phase timestamps (SM clock) for bring-up/tuning: prof[block*16 + slot].
+__device__ __forceinline__ void prof_stamp(unsigned long long* prof, int slot) {
+  if (prof) prof[blockIdx.x * 16 + slot] = clock64();
+}
 
 constexpr uint32_t pow2_cols(uint32_t c) {
   return c <= 32 ? 32 : c <= 64 ? 64 : c <= 128 ? 128 : c <= 256 ? 256 : 512;
@@ -44,7 +55,7 @@ template <int CI, int CO, int MODE, int STAGES>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w,
                   const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask,
-                  __nv_bfloat16* __restrict__ out, Geom g) {
+                  __nv_bfloat16* __restrict__ out, Geom g, unsigned long long* prof) {
   using S = ConvSmem<CI, CO, STAGES>;
   constexpr uint32_t KP = CI / 8;
   constexpr uint32_t TMEM_COLS = pow2_cols(2 * CO);
@@ -63,27 +74,8 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
   const uint32_t bar_tempty = bar_tfull + 16;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
 
-  // ---- one-time setup: fp32 master weights -> bf16 UMMA canonical (K-major, no swizzle) tiles
-  // B operand of tap t: rows n (GEMM N), 8-element K chunks; byte offset
-  //   t*w_tap + (k/8)*(CO*16) + n*16 + (k%8)*2        => LBO = CO*16, SBO = 128
-  for (int idx = tid; idx < CI * CO * 9; idx += kConvThreads) {
-    int n, k, tap;
-    if (MODE == 0) {  // w[n=co][k=ci][tap]
-      n = idx / (CI * 9);
-      int rem = idx - n * (CI * 9);
-      k = rem / 9;
-      tap = rem - k * 9;
-    } else {  // w[k=layer out ch][n=layer in ch][tap], taps mirrored
-      k = idx / (CO * 9);
-      int rem = idx - k * (CO * 9);
-      n = rem / 9;
-      tap = 8 - (rem - n * 9);
-    }
-    uint32_t off = tap * S::w_tap_bytes + (k >> 3) * (CO * 16) + n * 16 + (k & 7) * 2;
-    *reinterpret_cast<__nv_bfloat16*>(smem + off) = __float2bfloat16(w[idx]);
-  }
-  if (MODE == 0)
-    for (int i = tid; i < CO; i += kConvThreads) s_bias[i] = bias[i];
+  const uint32_t bar_w = bar_tempty + 16;
+  if (tid == 0) prof_stamp(prof, 0);
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(bar_full + i * 8, 1);
@@ -93,17 +85,51 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
       mbar_init(bar_tfull + i * 8, 1);
       mbar_init(bar_tempty + i * 8, 128);
     }
+    mbar_init(bar_w, 1);
     fence_mbar_init();
+    // fp32 master weights: one bulk async copy into the staging area
+    mbar_arrive_expect_tx(bar_w, S::wstage_bytes);
+    bulk_g2s(s_base + S::off_wstage, w, S::wstage_bytes, bar_w);
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(s_tmem), TMEM_COLS);
     tmem_relinquish();
+  }
+  if (MODE == 0)
+    for (int i = tid; i < CO; i += kConvThreads) s_bias[i] = bias[i];
+  __syncthreads();  // barrier inits visible to everyone
+  mbar_wait(bar_w, 0);
+  if (tid == 0) prof_stamp(prof, 1);
+  // ---- staged fp32 weights -> bf16 UMMA canonical (K-major, no swizzle) B tiles.
+  // B operand of tap t: rows n (GEMM N), 8-element K chunks; 32-bit word index
+  //   ((t*KP + k/8)*CO + n)*4 + (k%8)/2        => LBO = CO*16 B, SBO = 128 B
+  {
+    const float* ws = reinterpret_cast<const float*>(smem + S::off_wstage);
+    uint32_t* wd = reinterpret_cast<uint32_t*>(smem);
+    for (int widx = tid; widx < 9 * CI * CO / 2; widx += kConvThreads) {
+      const int j = widx & 3;
+      const int n = (widx >> 2) % CO;
+      const int rest = (widx >> 2) / CO;
+      const int kc = rest % KP;
+      const int tap = rest / KP;
+      const int k = kc * 8 + j * 2;
+      float lo, hi;
+      if (MODE == 0) {  // w[n = co][k = ci][tap]
+        lo = ws[(n * CI + k) * 9 + tap];
+        hi = ws[(n * CI + k + 1) * 9 + tap];
+      } else {  // w[k = layer out ch][n = layer in ch][8 - tap]   (taps mirrored)
+        lo = ws[(k * CO + n) * 9 + (8 - tap)];
+        hi = ws[((k + 1) * CO + n) * 9 + (8 - tap)];
+      }
+      wd[widx] = pack_bf16x2(lo, hi);
+    }
   }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  if (tid == 0) prof_stamp(prof, 2);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -134,6 +160,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
         mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
         mbar_wait(bar_full + stage * 8, phase);
         tc_fence_after();
+        if (it == 0) prof_stamp(prof, 4);
         const uint32_t a_stage = s_a + stage * S::a_stage_bytes;
         const uint32_t d_tmem = tmem_base + acc * CO;
 #pragma unroll
@@ -152,6 +179,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
         umma_commit(bar_empty + stage * 8);
         umma_commit(bar_tfull + acc * 8);
       }
+      prof_stamp(prof, 5);
     }
     __syncwarp();
   } else {
@@ -162,6 +190,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(bar_tfull + acc * 8, aphase);
       tc_fence_after();
+      if (it == 0 && tid == 64) prof_stamp(prof, 6);
       const int rel = t * kTileM + q * 32 + lane;
       int img, h, wc;
       const bool valid = decode_row(g, rel, img, h, wc);
@@ -203,11 +232,13 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
       tc_fence_before();
       mbar_arrive(bar_tempty + acc * 8);
     }
+    if (tid == 64) prof_stamp(prof, 7);
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  if (tid == 0) prof_stamp(prof, 8);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -233,7 +264,7 @@ struct WgradSmem {
 template <int CI, int CO, int STAGES>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ in,
-                        float* __restrict__ partial, Geom g) {
+                        float* __restrict__ partial, Geom g, unsigned long long* prof) {
   using S = WgradSmem<CI, CO, STAGES>;
   static_assert(CO == 64 || CO == 128, "UMMA M must be 64 or 128");
   static_assert(S::ncols <= 512, "accumulator does not fit TMEM");
@@ -250,6 +281,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
   const uint32_t bar_done = bar_empty + STAGES * 8;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
 
+  if (tid == 0) prof_stamp(prof, 0);
   for (int i = tid; i < 128; i += kConvThreads)
     reinterpret_cast<__nv_bfloat16*>(smem + S::off_ones)[i] = __float2bfloat16(1.0f);
   if (tid == 0) {
@@ -269,6 +301,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  if (tid == 0) prof_stamp(prof, 2);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -304,6 +337,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         const uint32_t phase = (it / STAGES) & 1;
         mbar_wait(bar_full + stage * 8, phase);
         tc_fence_after();
+        if (it == 0) prof_stamp(prof, 4);
         const uint32_t sa = s_base + stage * S::stage_bytes;
         const uint32_t sb = sa + S::a_bytes;
 #pragma unroll 1
@@ -322,12 +356,14 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         umma_commit(bar_empty + stage * 8);
       }
       umma_commit(bar_done);
+      prof_stamp(prof, 5);
     }
     __syncwarp();
   } else {
     const int q = warp & 3;
     mbar_wait(bar_done, 0);
     tc_fence_after();
+    if (tid == 64) prof_stamp(prof, 6);
     // M=64: accumulator row m sits in TMEM lane (m%16) + 32*(m/16); M=128: lane m.
     const int rows_per_q = CO / 4;
     const int m = q * rows_per_q + lane;
@@ -354,25 +390,46 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         *reinterpret_cast<uint4*>(dst + 9 * CI + 4) = make_uint4(v[4], v[5], v[6], v[7]);
       }
     }
+    if (tid == 64) prof_stamp(prof, 7);
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  if (tid == 0) prof_stamp(prof, 8);
 }
 
 // dW[co][ci][tap] = sum_parts partial[part][co][tap*CI + ci];  db[co] = sum_parts partial[..][9*CI]
 template <int CI, int CO>
-__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int nparts,
-                                    float* __restrict__ dw, float* __restrict__ db) {
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __restrict__ dw,
+                    float* __restrict__ db) {
+  // 256 threads = 32 consecutive outputs x 8 partial groups; group pg sums parts pg, pg+8, ...
   constexpr int ncols = 9 * CI + 8;
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= CO * ncols) return;
+  constexpr int total = CO * ncols;
+  __shared__ float sm[8][32];
+  const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
+  const int idx = blockIdx.x * 32 + lane;
+  float s = 0.f;
+  if (idx < total) {
+    int p = pg;
+    for (; p + 24 < nparts; p += 32) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(p + 8 * u) * total + idx];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s += v[u];
+    }
+    for (; p < nparts; p += 8) s += partial[(long long)p * total + idx];
+  }
+  sm[pg][lane] = s;
+  __syncthreads();
+  if (pg != 0 || idx >= total) return;
+#pragma unroll
+  for (int u = 1; u < 8; ++u) s += sm[u][lane];
   const int co = idx / ncols;
   const int col = idx - co * ncols;
   if (col > 9 * CI) return;  // bias block: only its first column is used
-  float s = 0.f;
-  for (int p = 0; p < nparts; ++p) s += partial[(long long)p * CO * ncols + idx];
   if (col == 9 * CI) {
     db[co] = s;
   } else {
@@ -383,6 +440,8 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int npart
 }
 
 // ------------------------------------------------------------------------------------------
+static unsigned long long* g_prof = nullptr;  // set by ddpb_set_prof_buffer (tuning only)
+
 template <int CI, int CO, int MODE>
 static int launch_conv(const void* in, const float* w, const float* bias, const void* mask,
                        void* out, const Geom& g, int num_sms, cudaStream_t st) {
@@ -399,7 +458,7 @@ static int launch_conv(const void* in, const float* w, const float* bias, const 
   const int grid = g.ntiles < num_sms ? g.ntiles : num_sms;
   kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(in), w, bias,
                                              static_cast<const __nv_bfloat16*>(mask),
-                                             static_cast<__nv_bfloat16*>(out), g);
+                                             static_cast<__nv_bfloat16*>(out), g, g_prof);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -408,6 +467,10 @@ static int launch_conv(const void* in, const float* w, const float* bias, const 
 using namespace ddpb;
 
 extern "C" {
+
+// Tuning hook: when non-NULL, the conv kernels write SM-clock phase stamps to
+// buf[block*16 + slot] (needs >= gridDim*16 entries).  NULL (default) disables it.
+void ddpb_set_prof_buffer(void* buf) { g_prof = static_cast<unsigned long long*>(buf); }
 
 int ddpb_conv3x3_fwd(const void* in, const float* w, const float* bias, void* out, int cin,
                      int cout, int batch, int batch_cap, int H, int W, void* stream) {
@@ -454,10 +517,10 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
   const int sms = ddpb_num_sms();
   const int grid = g.ntiles < sms ? g.ntiles : sms;
   kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(dout),
-                                             static_cast<const __nv_bfloat16*>(in), scratch, g);
+                                             static_cast<const __nv_bfloat16*>(in), scratch, g, g_prof);
   DDPB_CUDA_OK(cudaGetLastError());
   const int n = CO * (9 * CI + 8);
-  wgrad_reduce_kernel<CI, CO><<<(n + 255) / 256, 256, 0, st>>>(scratch, grid, dw, db);
+  wgrad_reduce_kernel<CI, CO><<<(n + 31) / 32, 256, 0, st>>>(scratch, grid, dw, db);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -41,7 +41,7 @@ __global__ void gather_u8_kernel(const uint8_t* __restrict__ images,
   const long long src = idx[i];
   const uint8_t* p = images + src * pix;
   for (int k = threadIdx.x; k < pix; k += blockDim.x)
-    x[(long long)i * pix + k] = static_cast<float>(p[k]) * (1.0f / 255.0f);
+    x[(long long)i * pix + k] = static_cast<float>(p[k]) / 255.0f;  // true division: bit-equal to ToTensor
   if (threadIdx.x == 0) y[i] = labels[src];
 }
 
@@ -175,7 +175,18 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int npart
   if (i4 >= n) return;
   if (i4 + 3 < n && (n & 3) == 0) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int p = 0; p < nparts; ++p) {
+    int p = 0;
+    for (; p + 4 <= nparts; p += 4) {  // 4 independent loads in flight, summed in order
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        v[u] = *reinterpret_cast<const float4*>(part + (long long)(p + u) * n + i4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w;
+      }
+    }
+    for (; p < nparts; ++p) {
       const float4 v = *reinterpret_cast<const float4*>(part + (long long)p * n + i4);
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
@@ -270,6 +281,23 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
                     float* __restrict__ dlogits, float* __restrict__ dbias,
                     float* __restrict__ loss, int batch) {
   __shared__ float red[32][NOUT + 1];
+  // phase 1: every (image, class) pair in parallel: z = bias + sum of the feature-slice partials
+  const int npair = batch * NOUT;
+  for (int t = threadIdx.x; t < npair; t += blockDim.x) {
+    float z = bias[t % NOUT];
+    int sidx = 0;
+    for (; sidx + 4 <= S; sidx += 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sidx + u) * npair + t];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) z += v[u];
+    }
+    for (; sidx < S; ++sidx) z += partial[(long long)sidx * npair + t];
+    logits[t] = z;
+  }
+  __syncthreads();
+  // phase 2: per-image log-softmax, loss and gradient
   float lsum = 0.f;
   float dbl[NOUT];
 #pragma unroll
@@ -278,10 +306,7 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
   for (int i = threadIdx.x; i < batch; i += blockDim.x) {
     float z[NOUT];
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) z[j] = bias[j];
-    for (int s = 0; s < S; ++s)
-#pragma unroll
-      for (int j = 0; j < NOUT; ++j) z[j] += partial[((long long)s * batch + i) * NOUT + j];
+    for (int j = 0; j < NOUT; ++j) z[j] = logits[(long long)i * NOUT + j];
     float m = z[0];
 #pragma unroll
     for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
@@ -296,7 +321,6 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
       const float d = (p - (j == y ? 1.f : 0.f)) * inv;
       dlogits[(long long)i * NOUT + j] = d;
       dbl[j] += d;
-      if (logits) logits[(long long)i * NOUT + j] = z[j];
       if (j == y) lsum += lse - z[j];
     }
   }
@@ -325,13 +349,14 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
 // dW[j][k]    = sum_img dlogits[img][j] act[img][k]                      (fp32, via partials)
 // grid = (feature-vector blocks, image splits); partial[split][NOUT][K].
 template <int NOUT>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ dlogits,
                   const float* __restrict__ W, __nv_bfloat16* __restrict__ dact,
                   float* __restrict__ dw_partial, Geom g, int C, int imgs_per_split) {
   extern __shared__ float sdl[];  // [imgs_per_split][NOUT]
+  constexpr int PF = 8;           // image vectors kept in flight per thread
   const int HW = g.H * g.W;
-  const int nvec = (C / 8) * HW;
+  const int nhv = (C / 4) * HW;   // half-vectors: 4 channels (8 bytes) of one pixel
   const long long K = (long long)C * HW;
   const int img_begin = blockIdx.y * imgs_per_split;
   const int img_end = min(g.batch, img_begin + imgs_per_split);
@@ -339,52 +364,57 @@ linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
     sdl[t] = dlogits[(long long)img_begin * NOUT + t];
   __syncthreads();
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= nvec) return;
-  const int chunk = v / HW;
-  const int pix = v - chunk * HW;
+  if (v >= nhv) return;
+  const int hc = v / HW;  // half-chunk index: channels [hc*4, hc*4+4)
+  const int pix = v - hc * HW;
   const int h = pix / g.W, wc = pix - h * g.W;
   const long long rowi = (long long)(h + 1) * g.PW + (wc + 1);
-  float wv[NOUT][8], dwv[NOUT][8];
+  float wv[NOUT][4], dwv[NOUT][4];
 #pragma unroll
   for (int j = 0; j < NOUT; ++j)
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      wv[j][c] = W[j * K + (long long)(chunk * 8 + c) * HW + pix];
+    for (int c = 0; c < 4; ++c) {
+      wv[j][c] = W[j * K + (long long)(hc * 4 + c) * HW + pix];
       dwv[j][c] = 0.f;
     }
-  const long long base = ((long long)chunk * g.plane_rows + kGuard + rowi) * 8;
-#pragma unroll 2
-  for (int img = img_begin; img < img_end; ++img) {
-    const long long off = base + (long long)img * g.PHW * 8;
-    const uint4 av = *reinterpret_cast<const uint4*>(act + off);
-    float a[8], gr[8];
-    unpack8(av, a);
+  const long long base =
+      ((long long)(hc >> 1) * g.plane_rows + kGuard + rowi) * 8 + (hc & 1) * 4;
+  const long long img_stride = (long long)g.PHW * 8;
+  for (int i0 = img_begin; i0 < img_end; i0 += PF) {
+    uint2 av[PF];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) gr[c] = 0.f;
-    const float* dl = sdl + (img - img_begin) * NOUT;
+    for (int u = 0; u < PF; ++u)
+      av[u] = (i0 + u < img_end)
+                  ? *reinterpret_cast<const uint2*>(act + base + (long long)(i0 + u) * img_stride)
+                  : make_uint2(0, 0);
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) {
-      const float d = dl[j];
+    for (int u = 0; u < PF; ++u) {
+      if (i0 + u >= img_end) break;
+      const float a[4] = {bf16_lo(av[u].x), bf16_hi(av[u].x), bf16_lo(av[u].y), bf16_hi(av[u].y)};
+      float gr[4] = {0.f, 0.f, 0.f, 0.f};
+      const float* dl = sdl + (i0 + u - img_begin) * NOUT;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        gr[c] = fmaf(d, wv[j][c], gr[c]);
-        dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
+      for (int j = 0; j < NOUT; ++j) {
+        const float d = dl[j];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          gr[c] = fmaf(d, wv[j][c], gr[c]);
+          dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
+        }
       }
-    }
 #pragma unroll
-    for (int c = 0; c < 8; ++c) gr[c] = a[c] > 0.f ? gr[c] : 0.f;
-    uint4 o;
-    o.x = pack_bf16x2(gr[0], gr[1]);
-    o.y = pack_bf16x2(gr[2], gr[3]);
-    o.z = pack_bf16x2(gr[4], gr[5]);
-    o.w = pack_bf16x2(gr[6], gr[7]);
-    *reinterpret_cast<uint4*>(dact + off) = o;
+      for (int c = 0; c < 4; ++c) gr[c] = a[c] > 0.f ? gr[c] : 0.f;
+      uint2 o;
+      o.x = pack_bf16x2(gr[0], gr[1]);
+      o.y = pack_bf16x2(gr[2], gr[3]);
+      *reinterpret_cast<uint2*>(dact + base + (long long)(i0 + u) * img_stride) = o;
+    }
   }
   float* dst = dw_partial + (long long)blockIdx.y * NOUT * K;
 #pragma unroll
   for (int j = 0; j < NOUT; ++j)
 #pragma unroll
-    for (int c = 0; c < 8; ++c) dst[j * K + (long long)(chunk * 8 + c) * HW + pix] = dwv[j][c];
+    for (int c = 0; c < 4; ++c) dst[j * K + (long long)(hc * 4 + c) * HW + pix] = dwv[j][c];
 }
 
 // Zero the rows of every plane between the end of the batch and the end of its last tile, so
@@ -460,9 +490,11 @@ int ddpb_conv1_fwd(const float* x, const float* w, const float* b, void* out, in
 }
 
 static int conv1_wgrad_blocks(int batch, int H, int W) {
+  // few row blocks: every block ends in an 80-value reduction and its partial must be re-read
   const int nrows = tiles_for(batch, H, W) * kTileM;
-  int bx = (nrows + 255) / 256;
-  if (bx > 256) bx = 256;
+  int bx = nrows / (256 * 8);
+  if (bx < 4) bx = 4;
+  if (bx > 64) bx = 64;
   return bx;
 }
 size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, int W) {
@@ -490,7 +522,7 @@ int ddpb_conv1_wgrad(const void* dact, const float* x, float* dw_db, float* scra
 static void linear_fwd_geom(int batch, int nvec, int& S, int& per, int& groups) {
   constexpr int IMG = 8;
   groups = (batch + IMG - 1) / IMG;
-  const int want = (2 * ddpb_num_sms() + groups - 1) / groups;  // ~2 CTAs per SM
+  const int want = ddpb_num_sms() / groups;  // one CTA per SM (255 registers): stay within one wave
   const int maxS = (nvec + 255) / 256;
   S = want < 1 ? 1 : (want > maxS ? maxS : want);
   per = ((nvec + S - 1) / S + 255) / 256 * 256;
@@ -518,9 +550,10 @@ int ddpb_linear_fwd(const void* act, const float* Wt, float* partial, int* S_out
 int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels,
                       float* logits, float* dlogits, float* dbias, float* loss, int nout,
                       int batch, void* stream) {
-  if (nout != 10 || batch <= 0) return DDPB_ERR_SHAPE;
-  int threads = ((batch + 31) / 32) * 32;
+  if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
+  int threads = ((batch * nout + 31) / 32) * 32;
   if (threads > 1024) threads = 1024;
+  if (threads < 64) threads = 64;
   softmax_xent_kernel<10><<<1, threads, 0, static_cast<cudaStream_t>(stream)>>>(
       partial, S, bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss, batch);
   return static_cast<int>(cudaGetLastError());
@@ -530,7 +563,7 @@ static int linear_bwd_imgs_per_split(int batch) {
   // enough splits to fill the GPU at small batch, few enough that partial traffic stays small
   if (batch <= 64) return 16;
   if (batch <= 512) return 32;
-  return 64;
+  return 128;
 }
 size_t ddpb_linear_bwd_scratch_bytes(int nout, int C, int batch_cap, int H, int W) {
   size_t worst = 0;
@@ -548,7 +581,7 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
   if (nout != 10 || (C % 8) != 0) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int nvec = (C / 8) * H * W;
+  const int nvec = (C / 4) * H * W;  // half-vectors
   const int ips = linear_bwd_imgs_per_split(batch);
   const int splits = (batch + ips - 1) / ips;
   if (g.ntiles * kTileM > batch * g.PHW) {

@@ -1,0 +1,49 @@
+"""Worker functions for the CPU (gloo) multi-process tests; importable by spawn."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def dp_worker(rank, world_size, out_path, steps, batch, seed):
+    import torch
+    from ddp_b200.parallel.engine import CpuDataParallel
+    from ddp_b200.parallel.process_group import cleanup, setup
+    torch.set_num_threads(2)
+    setup(rank, world_size, backend="gloo")
+    torch.manual_seed(1000 + rank)           # different init per rank: the engine must sync from rank 0
+    eng = CpuDataParallel(rank, world_size, lr=0.05)
+    if rank == 0:
+        init = eng.flat_params.detach().clone()
+    g = torch.Generator().manual_seed(seed)
+    xs = torch.rand(steps, world_size, batch, 1, 28, 28, generator=g)
+    ys = torch.randint(0, 10, (steps, world_size, batch), generator=g)
+    losses = []
+    for it in range(steps):
+        losses.append(float(eng.step(xs[it, rank], ys[it, rank])))
+    torch.save({"params": eng.flat_params.detach().clone(), "losses": losses,
+                "init": init if rank == 0 else None}, f"{out_path}.{rank}")
+    cleanup()
+
+
+def ours_loop_worker(rank, world_size, out_path, epochs, batch, seed, data_root):
+    """Ours, same schedule as baseline/ref_oracle.py `loop` (for per-step comparison)."""
+    import torch
+    from ddp_b200.parallel.engine import CpuDataParallel
+    from ddp_b200.parallel.process_group import cleanup, setup
+    from ddp_b200.utils.data import get_dataloader
+    torch.set_num_threads(2)
+    setup(rank, world_size, backend="gloo")
+    torch.manual_seed(seed)
+    eng = CpuDataParallel(rank, world_size, lr=0.01)
+    loader, sampler = get_dataloader(batch, world_size, rank, root=data_root)
+    losses = []
+    for epoch in range(epochs):
+        sampler.set_epoch(epoch)
+        for x, y in loader:
+            losses.append(float(eng.step(x, y)))
+    if rank == 0:
+        torch.save({"losses": losses, "model": eng.state_dict()}, out_path)
+    cleanup()

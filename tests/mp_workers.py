@@ -1,0 +1,165 @@
+"""Multi-rank GPU scenarios, launched by tests/test_multi_gpu.py under torch.distributed.run
+(one rank per GPU).  Each scenario asserts internally; a failing rank exits non-zero.
+
+    python -m torch.distributed.run --nproc-per-node N tests/mp_workers.py <scenario>
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+
+def _init():
+    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    return rank, world, dev
+
+
+def _rank_data(seed, r, n, dtype, dev):
+    g = torch.Generator(device="cpu").manual_seed(seed * 131 + r)
+    return (torch.randn(n, generator=g) * (r + 1)).to(dtype).to(dev)
+
+
+def scenario_allreduce():
+    """Bit-compare the P2P all-reduce with a host-ordered sum (rank 0..W-1), both algorithms,
+    fp32 and bf16, 4 KB .. 64 MB (SURVEY.md §4.2 "all-reduce kernel")."""
+    from ddp_b200.parallel.comm import ALGO_ONESHOT, ALGO_TWOSHOT, SymmetricComm
+    rank, world, dev = _init()
+    max_bytes = 64 << 20
+    comm = SymmetricComm(rank, world, 2 * max_bytes)
+    for dtype, esize in ((torch.float32, 4), (torch.bfloat16, 2)):
+        for nbytes in (4096, 75264, 2007088, 16 << 20, max_bytes):
+            n = nbytes // esize
+            src = comm.tensor(0, n, dtype)
+            dst = comm.tensor(max_bytes, n, dtype)
+            for it, algo in enumerate((ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_TWOSHOT)):
+                seed = nbytes % 9973 + it
+                src.copy_(_rank_data(seed, rank, n, dtype, dev))
+                dst.zero_()
+                comm.allreduce(0, max_bytes, nbytes, dtype, algo=algo, slot=2)
+                torch.cuda.synchronize()
+                want = _rank_data(seed, 0, n, dtype, dev)
+                for r in range(1, world):
+                    want = (want.float() + _rank_data(seed, r, n, dtype, dev).float()).to(dtype)
+                assert torch.equal(dst, want), (str(dtype), nbytes, algo, (dst.float() - want.float()).abs().max().item())
+    comm.close()
+    dist.barrier()
+    if rank == 0:
+        print("allreduce ok", flush=True)
+
+
+def scenario_fused_sgd():
+    """Fused all-reduce + /W + SGD vs p - lr*mean(g); every rank must end bit-identical."""
+    from ddp_b200.parallel.comm import ALGO_ONESHOT, ALGO_TWOSHOT, SymmetricComm
+    rank, world, dev = _init()
+    n = 501772
+    region = n * 4 + 256 - (n * 4) % 256
+    comm = SymmetricComm(rank, world, 2 * region)
+    p = comm.tensor(0, n)
+    gr = comm.tensor(region, n)
+    lr = torch.tensor([0.01], device=dev)
+    p.copy_(_rank_data(7, 0, n, torch.float32, dev))          # identical on all ranks
+    want = p.clone()
+    for it, algo in enumerate((ALGO_ONESHOT, ALGO_TWOSHOT) * 3):
+        gr.copy_(_rank_data(100 + it, rank, n, torch.float32, dev))
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_sgd(region, 0, n, lr, algo=algo, slot=it % 2)
+        torch.cuda.synchronize()
+        s = _rank_data(100 + it, 0, n, torch.float32, dev)
+        for r in range(1, world):
+            s = s + _rank_data(100 + it, r, n, torch.float32, dev)
+        want = want - 0.01 * (s / world)
+        assert torch.allclose(p, want, rtol=1e-5, atol=1e-6), (it, (p - want).abs().max().item())
+        gathered = [torch.empty_like(p) for _ in range(world)]
+        dist.all_gather(gathered, p.clone())
+        for r in range(world):
+            assert torch.equal(gathered[r], gathered[0]), f"rank {r} diverged bitwise at it {it}"
+        dist.barrier()
+    comm.close()
+    if rank == 0:
+        print("fused_sgd ok", flush=True)
+
+
+def scenario_stress():
+    """Flag-protocol stress: thousands of back-to-back fused steps with per-rank random delays
+    and changing payloads (compute-sanitizer cannot see cross-GPU races)."""
+    from ddp_b200.parallel.comm import SymmetricComm
+    rank, world, dev = _init()
+    n = 18816
+    region = 128 << 10
+    comm = SymmetricComm(rank, world, 3 * region)
+    p = comm.tensor(0, n)
+    g = [comm.tensor(region, n), comm.tensor(2 * region, n)]
+    lr = torch.tensor([1.0], device=dev)
+    p.zero_()
+    rng = torch.Generator().manual_seed(rank)
+    total = 0.0
+    iters = 3000
+    for it in range(iters):
+        par = it & 1
+        g[par].fill_(float((it % 7) + rank))                 # mean over ranks = it%7 + (W-1)/2
+        if int(torch.randint(0, 4, (1,), generator=rng)) == 0:
+            torch.cuda._sleep(int(torch.randint(1000, 200000, (1,), generator=rng)))
+        comm.allreduce_sgd(region * (1 + par), 0, n, lr, algo=1 + (it % 2), slot=it % 2)
+        total += (it % 7) + (world - 1) / 2.0
+    torch.cuda.synchronize()
+    assert torch.allclose(p, torch.full_like(p, -total), rtol=1e-5), (p[:4].tolist(), -total)
+    assert comm.status() == 0
+    comm.close()
+    dist.barrier()
+    if rank == 0:
+        print("stress ok", flush=True)
+
+
+def scenario_dp_equiv():
+    """ws=k with per-rank batch b == one process with batch k*b on the concatenated shards
+    (SURVEY.md §4.2 "DP equivalence"), CUDA graph on, plus a short tail batch."""
+    from ddp_b200.models.simple_cnn import SimpleCNN
+    from ddp_b200.parallel.engine import B200DataParallel
+    rank, world, dev = _init()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    b = 16
+    torch.manual_seed(1000 + rank)                  # ranks start DIFFERENT; the engine must sync them
+    eng = B200DataParallel(rank, world, dev, batch_cap=b, lr=0.05)
+    torch.manual_seed(5)
+    oracle = SimpleCNN(device=dev, init=False)
+    sd = eng.state_dict()
+    oracle.load_state_dict(sd)
+    gathered = [torch.empty_like(eng.flat_params) for _ in range(world)]
+    dist.all_gather(gathered, eng.flat_params.clone())
+    assert all(torch.equal(t, gathered[0]) for t in gathered), "initial broadcast failed"
+    g = torch.Generator().manual_seed(99)
+    xs = torch.rand(12, world, b, 1, 28, 28, generator=g).to(dev)
+    ys = torch.randint(0, 10, (12, world, b), generator=g).to(dev)
+    for it in range(12):
+        bb = b if it % 4 != 3 else 9
+        lo = oracle.forward_backward(xs[it, :, :bb].reshape(-1, 1, 28, 28), ys[it, :, :bb].reshape(-1))
+        oracle.sgd_step(0.05)
+        eng.step(xs[it, rank, :bb], ys[it, rank, :bb])
+        lg = torch.tensor([eng.read_loss()], device=dev)
+        dist.all_reduce(lg)
+        assert abs(lg.item() / world - lo.item()) < 2e-2 * max(1.0, abs(lo.item())), (it, lg.item() / world, lo.item())
+    eng.synchronize()
+    dist.all_gather(gathered, eng.flat_params.clone())
+    assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas diverged bitwise"
+    diff = (eng.flat_params[:520586] - oracle.arena.params.detach()[:520586]).abs().max().item()
+    assert diff < 5e-3, diff
+    eng.close()
+    dist.barrier()
+    if rank == 0:
+        print("dp_equiv ok", flush=True)
+
+
+if __name__ == "__main__":
+    {"allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
+     "dp_equiv": scenario_dp_equiv}[sys.argv[1]]()
+    if dist.is_initialized():
+        dist.destroy_process_group()
