@@ -198,5 +198,6 @@ def test_gather_u8(nat):
     y = torch.empty(64, dtype=torch.int64, device="cuda")
     nat.gather_u8(imgs, labels, idx, x, y)
     torch.cuda.synchronize()
-    assert torch.equal(x, imgs[idx].float().div(255).unsqueeze(1))
+    # ToTensor semantics = true division on the CPU (CUDA's scalar div multiplies by 1/255)
+    assert torch.equal(x.cpu(), imgs[idx].cpu().float().div(255).unsqueeze(1))
     assert torch.equal(y, labels[idx])
