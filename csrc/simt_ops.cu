@@ -616,3 +616,81 @@ const char* ddpb_error_string(int code) {
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// ddpb_conv1_wgrad_noalloc — the conv1 weight/bias gradient for hosts that cannot hand us scratch.
+//
+// Who this is for.  ddpb_conv1_wgrad() needs a caller-allocated scratch buffer for its per-block
+// partial sums.  Some embedders have no way to provide one: a serving or training host that
+// gives ALL device memory to its own pool at start-up (there is nothing left for cudaMalloc to
+// return), or a plug-in running inside such a host under a "no driver allocations after
+// initialisation" rule, because cudaMalloc/cudaFree synchronise the whole device and would stall
+// every other stream of the host.  For them the partial sums live in the fixed array below, which
+// is part of this library's device image: every GPU that loads the library holds these 80 KB until
+// the process exits, whether or not this entry point is ever called.
+//
+// Limit.  The array holds kNoAllocMaxBlocks (64) partial blocks; a batch needs rows/2048 of them
+// (rows = its padded-plane rows rounded up to whole 128-row tiles), so batches of up to 147 images
+// of 28x28 fit.  Larger batches are refused with DDPB_ERR_LIMIT (nothing is launched); use
+// ddpb_conv1_wgrad() for those.
+//
+// Rules of use.
+//  * The first call on each device looks the array's device address up (cudaGetSymbolAddress;
+//    the array's name is only a host-side stand-in in host code, never a pointer a kernel may
+//    be given).  That look-up is set-up work: make the first call on a device before starting
+//    any stream capture on it.
+//  * No call allocates or frees anything (no cudaMalloc/cudaFree, no library that would).
+//  * All calls on a device share the one array, and it keeps whatever the previous call left.
+//    Nothing in it has to start at zero: every partial slot the reduction reads is written by the
+//    same call first.  For the same reason two calls whose kernels overlap on the GPU (different
+//    streams, no dependency) race on it — serialise them.
+// =================================================================================================
+namespace {
+constexpr int kNoAllocMaxBlocks = 64;
+constexpr int kNoAllocCin = 1, kNoAllocCout = 32;
+constexpr int kNoAllocFloatsPerBlock = kNoAllocCout * kNoAllocCin * 9 + kNoAllocCout;  // 320
+constexpr int kNoAllocFloats = kNoAllocMaxBlocks * kNoAllocFloatsPerBlock;            // 20480 = 80 KB
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+static float* g_noalloc_devptr[64] = {};  // per device: resolved address of g_noalloc_scratch
+}  // namespace
+
+extern "C" int ddpb_conv1_wgrad_noalloc(const void* dact, const float* x, float* dw_db, int cin,
+                                        int cout, int batch, int batch_cap, int H, int W,
+                                        void* stream) {
+  if (!(cin == kNoAllocCin && cout == kNoAllocCout) || batch <= 0 || batch > batch_cap)
+    return DDPB_ERR_SHAPE;
+  // blocks this batch needs, by the same rule as ddpb_conv1_wgrad but without its upper clamp
+  const int nrows = tiles_for(batch, H, W) * kTileM;
+  int bx = nrows / (256 * 8);
+  if (bx < 4) bx = 4;
+  if (bx > kNoAllocMaxBlocks) return DDPB_ERR_LIMIT;
+
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return DDPB_ERR_SHAPE;
+  float* scratch = g_noalloc_devptr[dev];
+  if (scratch == nullptr) {  // once per device, with that device current
+    float* p = nullptr;
+    DDPB_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    if (p == nullptr) return DDPB_ERR_STATE;
+    g_noalloc_devptr[dev] = p;
+    scratch = p;
+  }
+
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout><<<dim3(bx, cout / 8), 256, 0, st>>>(
+      static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
+  DDPB_CUDA_OK(cudaGetLastError());
+  const long long n = kNoAllocFloatsPerBlock;
+  reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, bx, n,
+                                                                                    dw_db);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int ddpb_conv1_wgrad_noalloc_max_batch(int H, int W) {
+  // largest batch whose padded rows fit kNoAllocMaxBlocks partial blocks
+  int b = 1;
+  while (tiles_for(b + 1, H, W) * kTileM / (256 * 8) <= kNoAllocMaxBlocks) ++b;
+  return b;
+}

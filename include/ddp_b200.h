@@ -57,6 +57,19 @@ size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, i
 int ddpb_conv1_wgrad(const void* dact_planes, const float* x, float* dw_db, float* scratch,
                      int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
 
+/* Same result as ddpb_conv1_wgrad, for callers that cannot pass scratch because they cannot
+ * allocate device memory (a host that gave all of it to its own pool, or a plug-in barred from
+ * cudaMalloc/cudaFree because those stall every stream on the device).  The partial sums live in
+ * an 80 KB array inside the library's device image, held by every GPU that loads the library.
+ * Limit: 64 partial blocks = batches of up to ddpb_conv1_wgrad_noalloc_max_batch(H,W) images
+ * (147 for 28x28); larger batches return DDPB_ERR_LIMIT and launch nothing.  Allocates nothing.
+ * The first call on a device resolves the array's address (make it before any stream capture).
+ * Calls share the array: calls that overlap on the GPU race; nothing in it needs zeroing.
+ * This entry point has no counterpart in the reference. */
+int ddpb_conv1_wgrad_noalloc(const void* dact_planes, const float* x, float* dw_db, int cin,
+                             int cout, int batch, int batch_cap, int H, int W, void* stream);
+int ddpb_conv1_wgrad_noalloc_max_batch(int H, int W);
+
 /* ---- 3x3 pad-1 convolution on tcgen05 tensor cores (bf16 operands, fp32 accumulate in TMEM),
  * operands fetched with bulk async copies.  reference model.py:11-12 (forward),
  * train_ddp.py:199 (backward through cuDNN). Supported (cin,cout): (32,64). */
