@@ -18,7 +18,7 @@ namespace ddpb {
 
 constexpr int kConvThreads = 192;
 constexpr uint32_t kRowBytes = 16;
-constexpr uint32_t kStagePlaneBytes = kStageRows * kRowBytes;  // 3328
+constexpr uint32_t kStagePlaneBytes = kStageRows * kRowBytes;  // 3072
 
 template <int CI, int CO, int STAGES>
 struct ConvSmem {
@@ -106,6 +106,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
   {
     const float* ws = reinterpret_cast<const float*>(smem + S::off_wstage);
     uint32_t* wd = reinterpret_cast<uint32_t*>(smem);
+#pragma unroll 8
     for (int widx = tid; widx < 9 * CI * CO / 2; widx += kConvThreads) {
       const int j = widx & 3;
       const int n = (widx >> 2) % CO;
@@ -243,22 +244,31 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
 
 // ------------------------------------------------------------------------------------------
 // Weight gradient:  dW[co][ci][tap] = sum_p dout[p][co] * in[p + d(tap)][ci],  db[co] = sum_p dout
-// GEMM per tap: M = CO (dout channels), N = CI (in channels), K = pixels.  Both operands are
-// MN-major views of the planar buffers.  The bias gradient is one more N=8 MMA against a tile of
-// ones.  Each CTA accumulates its share of pixel tiles in TMEM (9*CI + 8 fp32 columns) and writes
-// one partial; wgrad_reduce_kernel sums the partials in a fixed order (deterministic).
+// GEMM: M = CO (dout channels), K = pixels, both operands MN-major views of the planar buffers.
+//
+// Measured on B200 (tools/mma_bench.py): a tcgen05.mma costs max(~45, N/2) cycles whatever M is,
+// so nine N=32 MMAs per K-step waste 3x.  Instead the in-planes of a tile are staged THREE times,
+// shifted by -1/0/+1 rows (the three horizontal taps), as 3*CI/8 consecutive planes; one MMA
+// with N = 3*CI then covers a whole filter row, and the vertical tap is the descriptor's start
+// row.  A constant plane of ones appended after them makes the bias gradient 8 more columns of the
+// first MMA (N = 3*CI + 8).  Accumulator columns: [row0: 3*CI taps | 8 bias][row1: 3*CI][row2: 3*CI].
+// Each CTA accumulates its share of pixel tiles in TMEM and writes one partial; wgrad_reduce_kernel
+// sums the partials in a fixed order (deterministic).
 template <int CI, int CO, int STAGES>
 struct WgradSmem {
   static constexpr uint32_t AP = CO / 8, BP = CI / 8;
+  static constexpr uint32_t NBP = 3 * BP + 1;              // B planes per stage incl. the ones plane
   static constexpr uint32_t a_plane = kTileM * kRowBytes;  // 2048
   static constexpr uint32_t a_bytes = AP * a_plane;
-  static constexpr uint32_t b_bytes = BP * kStagePlaneBytes;
+  static constexpr uint32_t b_bytes = NBP * kStagePlaneBytes;
   static constexpr uint32_t stage_bytes = a_bytes + b_bytes;
-  static constexpr uint32_t off_ones = STAGES * stage_bytes;
-  static constexpr uint32_t off_bar = off_ones + 256;
+  static constexpr uint32_t tx_bytes = a_bytes + 3 * BP * kStagePlaneBytes;
+  static constexpr uint32_t off_bar = STAGES * stage_bytes;
   static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 1) * 8;
   static constexpr uint32_t total = off_tmem + 16;
-  static constexpr uint32_t ncols = 9 * CI + 8;  // accumulator columns incl. bias block
+  static constexpr uint32_t n0 = 3 * CI + 8;  // first filter row + bias block
+  static constexpr uint32_t n1 = 3 * CI;
+  static constexpr uint32_t ncols = n0 + 2 * n1;  // 9*CI + 8
 };
 
 template <int CI, int CO, int STAGES>
@@ -267,23 +277,28 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
                         float* __restrict__ partial, Geom g, unsigned long long* prof) {
   using S = WgradSmem<CI, CO, STAGES>;
   static_assert(CO == 64 || CO == 128, "UMMA M must be 64 or 128");
-  static_assert(S::ncols <= 512, "accumulator does not fit TMEM");
-  constexpr uint32_t TMEM_COLS = pow2_cols(S::ncols);
+  static_assert(S::n0 <= 128, "one filter row must fit a 128-column TMEM allocation");
+  // Three separate 128-column allocations (one per filter row) instead of one 512-column block:
+  // 384 columns leave room for a concurrently resident dgrad CTA (64 columns) on the same SM.
+  constexpr uint32_t TMEM_COLS = 128;
   extern __shared__ __align__(128) uint8_t smem[];
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
   const uint32_t s_base = smem_u32(smem);
-  const uint32_t s_ones = s_base + S::off_ones;
   const uint32_t bar_full = s_base + S::off_bar;
   const uint32_t bar_empty = bar_full + STAGES * 8;
   const uint32_t bar_done = bar_empty + STAGES * 8;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
 
   if (tid == 0) prof_stamp(prof, 0);
-  for (int i = tid; i < 128; i += kConvThreads)
-    reinterpret_cast<__nv_bfloat16*>(smem + S::off_ones)[i] = __float2bfloat16(1.0f);
+  // the constant ones plane of every stage (never touched by the bulk copies)
+  for (int st = 0; st < STAGES; ++st) {
+    uint32_t* ones = reinterpret_cast<uint32_t*>(smem + st * S::stage_bytes + S::a_bytes +
+                                                 3 * S::BP * kStagePlaneBytes);
+    for (int i = tid; i < (int)kStagePlaneBytes / 4; i += kConvThreads) ones[i] = 0x3f803f80u;
+  }
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(bar_full + i * 8, 1);
@@ -293,14 +308,14 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(smem_u32(s_tmem), TMEM_COLS);
+    for (int r = 0; r < 3; ++r) tmem_alloc(smem_u32(s_tmem + r), TMEM_COLS);
     tmem_relinquish();
   }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *s_tmem;
+  const uint32_t tmem_row[3] = {s_tmem[0], s_tmem[1], s_tmem[2]};
   if (tid == 0) prof_stamp(prof, 2);
 
   if (warp == 0) {
@@ -310,7 +325,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         const int stage = it % STAGES;
         const uint32_t phase = (it / STAGES) & 1;
         mbar_wait(bar_empty + stage * 8, phase ^ 1);
-        mbar_arrive_expect_tx(bar_full + stage * 8, S::stage_bytes);
+        mbar_arrive_expect_tx(bar_full + stage * 8, S::tx_bytes);
         const uint32_t sa = s_base + stage * S::stage_bytes;
         const uint32_t sb = sa + S::a_bytes;
         const long long rowa = (long long)kGuard + (long long)t * kTileM;
@@ -319,18 +334,19 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
           bulk_g2s(sa + p * S::a_plane, dout + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane,
                    bar_full + stage * 8);
 #pragma unroll
-        for (uint32_t p = 0; p < S::BP; ++p)
-          bulk_g2s(sb + p * kStagePlaneBytes,
-                   in + ((long long)p * g.plane_rows + rowa - kHalo) * 8, kStagePlaneBytes,
-                   bar_full + stage * 8);
+        for (int sh = 0; sh < 3; ++sh)  // horizontal tap s: rows shifted by s-1
+#pragma unroll
+          for (uint32_t p = 0; p < S::BP; ++p)
+            bulk_g2s(sb + (sh * S::BP + p) * kStagePlaneBytes,
+                     in + ((long long)p * g.plane_rows + rowa - kHalo + (sh - 1)) * 8,
+                     kStagePlaneBytes, bar_full + stage * 8);
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(CO, CI, 1, 1);
-      constexpr uint32_t idesc_b = umma_idesc_bf16(CO, 8, 1, 1);
-      const uint64_t ones_desc = umma_smem_desc(s_ones, 128, 128);
+      constexpr uint32_t idesc0 = umma_idesc_bf16(CO, S::n0, 1, 1);
+      constexpr uint32_t idesc1 = umma_idesc_bf16(CO, S::n1, 1, 1);
       int it = 0;
       for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
         const int stage = it % STAGES;
@@ -340,18 +356,16 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         if (it == 0) prof_stamp(prof, 4);
         const uint32_t sa = s_base + stage * S::stage_bytes;
         const uint32_t sb = sa + S::a_bytes;
-#pragma unroll 1
+#pragma unroll
         for (int ks = 0; ks < kTileM / 16; ++ks) {
           const uint32_t accum = (it | ks) != 0;
           const uint64_t adesc = umma_smem_desc(sa + ks * 16 * kRowBytes, 128, S::a_plane);
 #pragma unroll
-          for (int tap = 0; tap < 9; ++tap) {
-            const int d = (tap / 3 - 1) * g.PW + (tap % 3 - 1);
-            const uint64_t bdesc = umma_smem_desc(sb + (kHalo + d + ks * 16) * kRowBytes, 128,
-                                                  kStagePlaneBytes);
-            umma_bf16(tmem_base + tap * CI, adesc, bdesc, idesc, accum);
+          for (int r = 0; r < 3; ++r) {  // vertical tap r: start row shifted by (r-1)*PW
+            const uint64_t bdesc = umma_smem_desc(
+                sb + (kHalo + (r - 1) * g.PW + ks * 16) * kRowBytes, 128, kStagePlaneBytes);
+            umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
           }
-          umma_bf16(tmem_base + 9 * CI, adesc, ones_desc, idesc_b, accum);
         }
         umma_commit(bar_empty + stage * 8);
       }
@@ -369,25 +383,30 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
     const int m = q * rows_per_q + lane;
     const bool has_row = lane < rows_per_q;
     float* dst = partial + ((long long)blockIdx.x * CO + m) * S::ncols;
-#pragma unroll 1
-    for (int c0 = 0; c0 < 9 * CI; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      if (has_row) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(dst + c0 + j * 4) =
-              make_uint4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+    for (int r = 0; r < 3; ++r) {
+      const uint32_t tb = tmem_row[r] + (static_cast<uint32_t>(q * 32) << 16);
+      float* drow = dst + (r == 0 ? 0 : S::n0 + (r - 1) * S::n1);
+#pragma unroll 1
+      for (int c0 = 0; c0 < (int)S::n1; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tb + c0, v);
+        tmem_ld_wait();
+        if (has_row) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(drow + c0 + j * 4) =
+                make_uint4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+        }
       }
-    }
-    {
-      uint32_t v[8];
-      tmem_ld8(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + 9 * CI, v);
-      tmem_ld_wait();
-      if (has_row) {
-        *reinterpret_cast<uint4*>(dst + 9 * CI) = make_uint4(v[0], v[1], v[2], v[3]);
-        *reinterpret_cast<uint4*>(dst + 9 * CI + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+      if (r == 0) {  // bias block: 8 columns after the first filter row
+        uint32_t v[8];
+        tmem_ld8(tb + S::n1, v);
+        tmem_ld_wait();
+        if (has_row) {
+          *reinterpret_cast<uint4*>(drow + S::n1) = make_uint4(v[0], v[1], v[2], v[3]);
+          *reinterpret_cast<uint4*>(drow + S::n1 + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+        }
       }
     }
     if (tid == 64) prof_stamp(prof, 7);
@@ -395,17 +414,19 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  if (warp == 1)
+    for (int r = 0; r < 3; ++r) tmem_dealloc(tmem_row[r], TMEM_COLS);
   if (tid == 0) prof_stamp(prof, 8);
 }
 
-// dW[co][ci][tap] = sum_parts partial[part][co][tap*CI + ci];  db[co] = sum_parts partial[..][9*CI]
+// Partial column layout -> dW[co][ci][tap], db[co]; see the accumulator layout above.
 template <int CI, int CO>
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __restrict__ dw,
                     float* __restrict__ db) {
   // 256 threads = 32 consecutive outputs x 8 partial groups; group pg sums parts pg, pg+8, ...
-  constexpr int ncols = 9 * CI + 8;
+  constexpr int n0 = 3 * CI + 8, n1 = 3 * CI;
+  constexpr int ncols = n0 + 2 * n1;
   constexpr int total = CO * ncols;
   __shared__ float sm[8][32];
   const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
@@ -428,15 +449,24 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __rest
 #pragma unroll
   for (int u = 1; u < 8; ++u) s += sm[u][lane];
   const int co = idx / ncols;
-  const int col = idx - co * ncols;
-  if (col > 9 * CI) return;  // bias block: only its first column is used
-  if (col == 9 * CI) {
-    db[co] = s;
+  int col = idx - co * ncols;
+  int r;
+  if (col < n0) {
+    r = 0;
+    if (col >= n1) {  // bias block: only its first column is used
+      if (col == n1) db[co] = s;
+      return;
+    }
+  } else if (col < n0 + n1) {
+    r = 1;
+    col -= n0;
   } else {
-    const int tap = col / CI;
-    const int ci = col - tap * CI;
-    dw[(co * CI + ci) * 9 + tap] = s;
+    r = 2;
+    col -= n0 + n1;
   }
+  const int sx = col / CI;
+  const int ci = col - sx * CI;
+  dw[(co * CI + ci) * 9 + r * 3 + sx] = s;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -445,7 +475,9 @@ static unsigned long long* g_prof = nullptr;  // set by ddpb_set_prof_buffer (tu
 template <int CI, int CO, int MODE>
 static int launch_conv(const void* in, const float* w, const float* bias, const void* mask,
                        void* out, const Geom& g, int num_sms, cudaStream_t st) {
-  constexpr int STAGES = 4;
+  // dgrad: 3 stages (its ring then exactly holds the fp32 weight staging area) keeps the CTA at
+  // ~111 KB so it can share an SM with a weight-gradient CTA running on another stream.
+  constexpr int STAGES = MODE == 0 ? 4 : 3;
   using S = ConvSmem<CI, CO, STAGES>;
   auto kern = conv3x3_tc_kernel<CI, CO, MODE, STAGES>;
   static bool configured[64] = {};
@@ -504,7 +536,7 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
   if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
-  constexpr int CI = 32, CO = 64, STAGES = 4;
+  constexpr int CI = 32, CO = 64, STAGES = 2;
   using S = WgradSmem<CI, CO, STAGES>;
   auto kern = conv3x3_wgrad_tc_kernel<CI, CO, STAGES>;
   static bool configured[64] = {};

@@ -20,9 +20,9 @@
 namespace ddpb {
 
 constexpr int kTileM = 128;  // pixels (rows) per GEMM tile
-constexpr int kHalo = 40;    // rows fetched before/after a tile; >= (W+2)+1 for W <= 37
+constexpr int kHalo = 32;    // rows fetched before/after a tile; >= (W+2)+1, i.e. W <= 29
 constexpr int kGuard = 64;   // zero rows before the first / after the last tile
-constexpr int kStageRows = kTileM + 2 * kHalo;  // 208 rows per plane per pipeline stage
+constexpr int kStageRows = kTileM + 2 * kHalo;  // 192 rows per plane per pipeline stage
 
 struct Geom {
   int batch;      // images in this step (<= capacity the buffers were sized for)

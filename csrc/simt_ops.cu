@@ -23,6 +23,31 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// Reduce 80 per-lane values across the 32 lanes of a warp with recursive halving: each stage
+// swaps half of the values with the partner lane, so 80 shuffles do the work of 400.  On return
+// v[0..4] of lane l hold the warp totals of elements  40*b4 + 20*b3 + 10*b2 + 5*b1 + (0..4)
+// (b_k = bit k of l); lanes l and l^1 hold the same five totals.
+__device__ __forceinline__ void warp_reduce80(float (&v)[80], int lane) {
+#define DDPB_HALVE(H, BIT)                                          \
+  _Pragma("unroll") for (int i = 0; i < H; ++i) {                   \
+    const bool up = (lane & BIT) != 0;                              \
+    const float send = up ? v[i] : v[i + H];                        \
+    const float keep = up ? v[i + H] : v[i];                        \
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, BIT);          \
+  }
+  DDPB_HALVE(40, 16)
+  DDPB_HALVE(20, 8)
+  DDPB_HALVE(10, 4)
+  DDPB_HALVE(5, 2)
+#undef DDPB_HALVE
+#pragma unroll
+  for (int i = 0; i < 5; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);
+}
+__device__ __forceinline__ int warp_reduce80_base(int lane) {
+  return ((lane >> 4) & 1) * 40 + ((lane >> 3) & 1) * 20 + ((lane >> 2) & 1) * 10 +
+         ((lane >> 1) & 1) * 5;
+}
+
 __device__ __forceinline__ void unpack8(const uint4& a, float (&f)[8]) {
   f[0] = bf16_lo(a.x); f[1] = bf16_hi(a.x);
   f[2] = bf16_lo(a.y); f[3] = bf16_hi(a.y);
@@ -46,115 +71,162 @@ __global__ void gather_u8_kernel(const uint8_t* __restrict__ images,
 }
 
 // ------------------------------------------------------------------ conv1 forward
+// Block (bx, chunk) handles a contiguous range of images for 8 output channels.  Per image the
+// (zero-bordered) input tile is staged in shared memory so the 3x3 window needs no bounds tests;
+// the chunk's 8x(CIN0*9) weights live in registers.  Border rows are written as zeros.
+constexpr int kConv1Group = 8;  // images staged in shared memory per round
+
+// Stage `ng` zero-bordered images [CIN0][PHW] each into shared memory.
+template <int CIN0>
+__device__ __forceinline__ void stage_padded_images(float* xs, const float* __restrict__ x, int img0,
+                                                    int ng, const Geom& g) {
+  const int per = CIN0 * g.PHW;
+  for (int i = threadIdx.x; i < ng * per; i += blockDim.x) {
+    const int li = i / per;
+    const int rem = i - li * per;
+    const int ci = rem / g.PHW;
+    const int pos = rem - ci * g.PHW;
+    const int hp = pos / g.PW, wp = pos - hp * g.PW;
+    const bool in = hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W;
+    xs[i] = in ? x[((long long)(img0 + li) * CIN0 + ci) * g.H * g.W + (hp - 1) * g.W + (wp - 1)] : 0.f;
+  }
+}
+
 template <int CIN0, int C1>
 __global__ void __launch_bounds__(256)
 conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                  const float* __restrict__ b, __nv_bfloat16* __restrict__ out, Geom g) {
-  __shared__ float sw[C1 * CIN0 * 9];
-  __shared__ float sb[C1];
-  for (int i = threadIdx.x; i < C1 * CIN0 * 9; i += blockDim.x) sw[i] = w[i];
-  for (int i = threadIdx.x; i < C1; i += blockDim.x) sb[i] = b[i];
-  __syncthreads();
-  const int nrows = g.ntiles * kTileM;
-  const long long total = (long long)(C1 / 8) * nrows;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int chunk = static_cast<int>(idx / nrows);
-    const int rel = static_cast<int>(idx - (long long)chunk * nrows);
-    int img, h, wc;
-    const bool valid = decode_row(g, rel, img, h, wc);
-    uint4 o = make_uint4(0, 0, 0, 0);
-    if (valid) {
-      float in[CIN0 * 9];
+  extern __shared__ float xs[];  // [kConv1Group][CIN0][PHW]
+  constexpr int NW = CIN0 * 9;
+  const int chunk = blockIdx.y;
+  float wr[8][NW], br[8];
 #pragma unroll
-      for (int ci = 0; ci < CIN0; ++ci) {
-        const float* xp = x + ((long long)img * CIN0 + ci) * g.H * g.W;
+  for (int c = 0; c < 8; ++c) {
+    br[c] = b[chunk * 8 + c];
 #pragma unroll
-        for (int r = 0; r < 3; ++r)
+    for (int j = 0; j < NW; ++j) wr[c][j] = w[(chunk * 8 + c) * NW + j];
+  }
+  const int ipb = (g.batch + gridDim.x - 1) / gridDim.x;
+  const int lo = blockIdx.x * ipb;
+  const int hi = min(g.batch, lo + ipb);
+  __nv_bfloat16* plane = out + ((long long)chunk * g.plane_rows + kGuard) * 8;
+  for (int img0 = lo; img0 < hi; img0 += kConv1Group) {
+    const int ng = min(kConv1Group, hi - img0);
+    __syncthreads();
+    stage_padded_images<CIN0>(xs, x, img0, ng, g);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < ng * g.PHW; idx += blockDim.x) {
+      const int li = idx / g.PHW;
+      const int pos = idx - li * g.PHW;
+      const int hp = pos / g.PW, wp = pos - hp * g.PW;
+      uint4 o = make_uint4(0, 0, 0, 0);
+      if (hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W) {
+        const float* xi = xs + li * CIN0 * g.PHW;
+        float in[NW];
 #pragma unroll
-          for (int s = 0; s < 3; ++s) {
-            const int hh = h + r - 1, ww = wc + s - 1;
-            in[ci * 9 + r * 3 + s] =
-                (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
-          }
+        for (int ci = 0; ci < CIN0; ++ci)
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int s2 = 0; s2 < 3; ++s2)
+              in[ci * 9 + r * 3 + s2] = xi[ci * g.PHW + (hp + r - 1) * g.PW + (wp + s2 - 1)];
+        float acc[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float a = br[c];
+#pragma unroll
+          for (int j = 0; j < NW; ++j) a = fmaf(wr[c][j], in[j], a);
+          acc[c] = fmaxf(a, 0.f);
+        }
+        o.x = pack_bf16x2(acc[0], acc[1]);
+        o.y = pack_bf16x2(acc[2], acc[3]);
+        o.z = pack_bf16x2(acc[4], acc[5]);
+        o.w = pack_bf16x2(acc[6], acc[7]);
       }
-      float acc[8];
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const float* wp = sw + (chunk * 8 + c) * CIN0 * 9;
-        float a = sb[chunk * 8 + c];
-#pragma unroll
-        for (int j = 0; j < CIN0 * 9; ++j) a = fmaf(wp[j], in[j], a);
-        acc[c] = fmaxf(a, 0.f);
-      }
-      o.x = pack_bf16x2(acc[0], acc[1]);
-      o.y = pack_bf16x2(acc[2], acc[3]);
-      o.z = pack_bf16x2(acc[4], acc[5]);
-      o.w = pack_bf16x2(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(plane + ((long long)img0 * g.PHW + idx) * 8) = o;
     }
-    *reinterpret_cast<uint4*>(out + ((long long)chunk * g.plane_rows + kGuard + rel) * 8) = o;
+  }
+  // rows between the end of the batch and the end of its last tile
+  if (blockIdx.x == gridDim.x - 1) {
+    const int first = g.batch * g.PHW, last = g.ntiles * kTileM;
+    for (int r = first + threadIdx.x; r < last; r += blockDim.x)
+      *reinterpret_cast<uint4*>(plane + (long long)r * 8) = make_uint4(0, 0, 0, 0);
   }
 }
 
 // ------------------------------------------------------------------ conv1 weight gradient
 // dW[c][ci][tap] = sum_p dact[p][c] * x[p + tap shift][ci],  db[c] = sum_p dact[p][c].
-// gridDim.y = C1/8 (channel chunk), gridDim.x = row blocks; one partial per blockIdx.x:
-// partial[bx][C1*CIN0*9 + C1]  (weights then biases, canonical order).
+// gridDim.y = C1/8 (channel chunk); block (bx, chunk) accumulates a contiguous range of images and
+// writes one partial per blockIdx.x: partial[bx][C1*CIN0*9 + C1] (weights then biases, canonical
+// order); reduce_partials_kernel sums them in a fixed order.
 template <int CIN0, int C1>
 __global__ void __launch_bounds__(256)
 conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restrict__ x,
                    float* __restrict__ partial, Geom g) {
   constexpr int NW = CIN0 * 9;
   constexpr int NV = 8 * NW + 8;
+  constexpr int PF = 4;          // gradient vectors kept in flight per thread
+  extern __shared__ float xs[];  // [kConv1Group][CIN0][PHW]
   __shared__ float red[8][NV];
   const int chunk = blockIdx.y;
-  const int nrows = g.ntiles * kTileM;
-  float acc[8][NW];
-  float accb[8];
+  static_assert(NV == 80, "warp_reduce80 expects 8*(CIN0*9) + 8 == 80 accumulators (CIN0 == 1)");
+  float acc[NV];  // [c*NW + j] weight taps, then [8*NW + c] bias
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    accb[c] = 0.f;
+  for (int i = 0; i < NV; ++i) acc[i] = 0.f;
+  const int ipb = (g.batch + gridDim.x - 1) / gridDim.x;
+  const int lo = blockIdx.x * ipb;
+  const int hi = min(g.batch, lo + ipb);
+  const __nv_bfloat16* plane = dact + ((long long)chunk * g.plane_rows + kGuard) * 8;
+  for (int img0 = lo; img0 < hi; img0 += kConv1Group) {
+    const int ng = min(kConv1Group, hi - img0);
+    const int nidx = ng * g.PHW;
+    __syncthreads();
+    stage_padded_images<CIN0>(xs, x, img0, ng, g);
+    __syncthreads();
+    // border rows of dact are zero, so every row of the group can be accumulated unconditionally;
+    // the window read stays inside the image's padded tile for interior rows only -> test those.
+    for (int base = threadIdx.x; base < nidx; base += PF * blockDim.x) {
+      uint4 dv[PF];
 #pragma unroll
-    for (int j = 0; j < NW; ++j) acc[c][j] = 0.f;
-  }
-  for (int rel = blockIdx.x * blockDim.x + threadIdx.x; rel < nrows;
-       rel += gridDim.x * blockDim.x) {
-    int img, h, wc;
-    if (!decode_row(g, rel, img, h, wc)) continue;
-    const uint4 dv = *reinterpret_cast<const uint4*>(
-        dact + ((long long)chunk * g.plane_rows + kGuard + rel) * 8);
-    float d[8];
-    unpack8(dv, d);
-    float in[NW];
+      for (int u = 0; u < PF; ++u) {
+        const int idx = base + u * blockDim.x;
+        dv[u] = idx < nidx ? *reinterpret_cast<const uint4*>(plane + ((long long)img0 * g.PHW + idx) * 8)
+                           : make_uint4(0, 0, 0, 0);
+      }
 #pragma unroll
-    for (int ci = 0; ci < CIN0; ++ci) {
-      const float* xp = x + ((long long)img * CIN0 + ci) * g.H * g.W;
+      for (int u = 0; u < PF; ++u) {
+        const int idx = base + u * blockDim.x;
+        if (idx >= nidx) break;
+        const int li = idx / g.PHW;
+        const int pos = idx - li * g.PHW;
+        const int hp = pos / g.PW, wp = pos - hp * g.PW;
+        if (!(hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W)) continue;
+        float d[8];
+        unpack8(dv[u], d);
+        const float* xi = xs + li * CIN0 * g.PHW;
+        float in[NW];
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
+        for (int ci = 0; ci < CIN0; ++ci)
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
-          const int hh = h + r - 1, ww = wc + s - 1;
-          in[ci * 9 + r * 3 + s] =
-              (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
+          for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int s2 = 0; s2 < 3; ++s2)
+              in[ci * 9 + r * 3 + s2] = xi[ci * g.PHW + (hp + r - 1) * g.PW + (wp + s2 - 1)];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          acc[8 * NW + c] += d[c];
+#pragma unroll
+          for (int j = 0; j < NW; ++j) acc[c * NW + j] = fmaf(d[c], in[j], acc[c * NW + j]);
         }
-    }
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      accb[c] += d[c];
-#pragma unroll
-      for (int j = 0; j < NW; ++j) acc[c][j] = fmaf(d[c], in[j], acc[c][j]);
+      }
     }
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  warp_reduce80(acc, lane);
+  if ((lane & 1) == 0) {
+    const int base = warp_reduce80_base(lane);
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-#pragma unroll
-    for (int j = 0; j < NW; ++j) {
-      const float v = warp_sum(acc[c][j]);
-      if (lane == 0) red[warp][c * NW + j] = v;
-    }
-    const float vb = warp_sum(accb[c]);
-    if (lane == 0) red[warp][8 * NW + c] = vb;
+    for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
   }
   __syncthreads();
   float* dst = partial + (long long)blockIdx.x * (C1 * NW + C1);
@@ -215,11 +287,10 @@ linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
   const int img0 = blockIdx.y * IMG;
   const int v_begin = blockIdx.x * vec_per_slice;
   const int v_end = min(nvec, v_begin + vec_per_slice);
-  float acc[IMG][NOUT];
+  static_assert(IMG * NOUT == 80, "warp_reduce80 expects 80 accumulators");
+  float acc[IMG * NOUT];
 #pragma unroll
-  for (int i = 0; i < IMG; ++i)
-#pragma unroll
-    for (int j = 0; j < NOUT; ++j) acc[i][j] = 0.f;
+  for (int i = 0; i < IMG * NOUT; ++i) acc[i] = 0.f;
 
   for (int v = v_begin + threadIdx.x; v < v_end; v += blockDim.x) {
     const int chunk = v / HW;
@@ -247,17 +318,16 @@ linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 #pragma unroll
       for (int j = 0; j < NOUT; ++j)
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[i][j] = fmaf(wv[j][c], a[c], acc[i][j]);
+        for (int c = 0; c < 8; ++c) acc[i * NOUT + j] = fmaf(wv[j][c], a[c], acc[i * NOUT + j]);
     }
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  warp_reduce80(acc, lane);
+  if ((lane & 1) == 0) {
+    const int base = warp_reduce80_base(lane);
 #pragma unroll
-  for (int i = 0; i < IMG; ++i)
-#pragma unroll
-    for (int j = 0; j < NOUT; ++j) {
-      const float v = warp_sum(acc[i][j]);
-      if (lane == 0) red[warp][i * NOUT + j] = v;
-    }
+    for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+  }
   __syncthreads();
   for (int t = threadIdx.x; t < IMG * NOUT; t += blockDim.x) {
     const int i = t / NOUT, j = t - i * NOUT;
@@ -274,27 +344,41 @@ linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 // z = bias + sum_s partial[s]; loss = mean_i(logsumexp(z_i) - z_i[y_i]);
 // dlogits = (softmax(z) - onehot(y)) / batch; db[j] = sum_i dlogits[i][j].
 // Single block: the work is batch*NOUT*S floats.
+// Multi-block: block b handles images [256b, 256b+256).  Block sums of the loss and of dbias go to
+// a small library-resident array; the block that finishes last (ticket counter) adds them up in
+// block order, so the result is deterministic.  The ticket resets itself; calls on one device must
+// not overlap (the step engine issues one at a time).
+constexpr int kXentImgsPerBlock = 256;
+constexpr int kXentMaxBlocks = 512;  // batches up to 131072
+static __device__ float g_xent_block_sums[kXentMaxBlocks * 12];
+static __device__ unsigned int g_xent_ticket;
+
 template <int NOUT>
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(256)
 softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
                     const long long* __restrict__ labels, float* __restrict__ logits,
                     float* __restrict__ dlogits, float* __restrict__ dbias,
                     float* __restrict__ loss, int batch) {
-  __shared__ float red[32][NOUT + 1];
+  static_assert(NOUT + 1 <= 12, "block-sum row too small");
+  __shared__ float red[8][NOUT + 1];
+  __shared__ bool is_last;
+  const int img0 = blockIdx.x * kXentImgsPerBlock;
+  const int nimg = min(kXentImgsPerBlock, batch - img0);
   // phase 1: every (image, class) pair in parallel: z = bias + sum of the feature-slice partials
-  const int npair = batch * NOUT;
-  for (int t = threadIdx.x; t < npair; t += blockDim.x) {
+  const long long npair_all = (long long)batch * NOUT;
+  for (int t = threadIdx.x; t < nimg * NOUT; t += blockDim.x) {
+    const long long gt = (long long)img0 * NOUT + t;
     float z = bias[t % NOUT];
     int sidx = 0;
     for (; sidx + 4 <= S; sidx += 4) {
       float v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sidx + u) * npair + t];
+      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sidx + u) * npair_all + gt];
 #pragma unroll
       for (int u = 0; u < 4; ++u) z += v[u];
     }
-    for (; sidx < S; ++sidx) z += partial[(long long)sidx * npair + t];
-    logits[t] = z;
+    for (; sidx < S; ++sidx) z += partial[(long long)sidx * npair_all + gt];
+    logits[gt] = z;
   }
   __syncthreads();
   // phase 2: per-image log-softmax, loss and gradient
@@ -303,10 +387,11 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
 #pragma unroll
   for (int j = 0; j < NOUT; ++j) dbl[j] = 0.f;
   const float inv = 1.0f / static_cast<float>(batch);
-  for (int i = threadIdx.x; i < batch; i += blockDim.x) {
+  for (int li = threadIdx.x; li < nimg; li += blockDim.x) {
+    const long long i = img0 + li;
     float z[NOUT];
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) z[j] = logits[(long long)i * NOUT + j];
+    for (int j = 0; j < NOUT; ++j) z[j] = logits[i * NOUT + j];
     float m = z[0];
 #pragma unroll
     for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
@@ -319,7 +404,7 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
     for (int j = 0; j < NOUT; ++j) {
       const float p = expf(z[j] - lse);
       const float d = (p - (j == y ? 1.f : 0.f)) * inv;
-      dlogits[(long long)i * NOUT + j] = d;
+      dlogits[i * NOUT + j] = d;
       dbl[j] += d;
       if (j == y) lsum += lse - z[j];
     }
@@ -337,8 +422,23 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
   __syncthreads();
   if (threadIdx.x <= NOUT) {
     float s = 0.f;
-    const int nw = blockDim.x >> 5;
-    for (int wdx = 0; wdx < nw; ++wdx) s += red[wdx][threadIdx.x];
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][threadIdx.x];
+    g_xent_block_sums[blockIdx.x * 12 + threadIdx.x] = s;
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&g_xent_ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+    if (is_last) g_xent_ticket = 0;
+  }
+  __syncthreads();
+  if (is_last && threadIdx.x <= NOUT) {
+    __threadfence();
+    float s = 0.f;
+    for (unsigned int bk = 0; bk < gridDim.x; ++bk)
+      s += *reinterpret_cast<volatile float*>(&g_xent_block_sums[bk * 12 + threadIdx.x]);
     if (threadIdx.x < NOUT) dbias[threadIdx.x] = s;
     else loss[0] = s * inv;
   }
@@ -438,7 +538,19 @@ __global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int np
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ grad,
                            const float* __restrict__ lr, long long n) {
   const float l = *lr;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(grad)) & 15) == 0;
+  const long long n4 = vec ? n / 4 : 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 a = reinterpret_cast<float4*>(p)[i];
+    const float4 g4 = reinterpret_cast<const float4*>(grad)[i];
+    a.x = fmaf(-l, g4.x, a.x);
+    a.y = fmaf(-l, g4.y, a.y);
+    a.z = fmaf(-l, g4.z, a.z);
+    a.w = fmaf(-l, g4.w, a.w);
+    reinterpret_cast<float4*>(p)[i] = a;
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (long long)gridDim.x * blockDim.x)
     p[i] = fmaf(-l, grad[i], p[i]);
 }
@@ -480,21 +592,19 @@ int ddpb_conv1_fwd(const float* x, const float* w, const float* b, void* out, in
                    int batch, int batch_cap, int H, int W, void* stream) {
   if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
-  const long long total = (long long)(cout / 8) * g.ntiles * kTileM;
-  long long blocks = (total + 255) / 256;
-  const long long cap = (long long)ddpb_num_sms() * 16;
-  if (blocks > cap) blocks = cap;
-  conv1_fwd_kernel<1, 32><<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  int bx = batch < ddpb_num_sms() ? batch : ddpb_num_sms();
+  const size_t smem = (size_t)kConv1Group * cin * g.PHW * sizeof(float);
+  conv1_fwd_kernel<1, 32><<<dim3(bx, cout / 8), 256, smem, static_cast<cudaStream_t>(stream)>>>(
       x, w, b, static_cast<__nv_bfloat16*>(out), g);
   return static_cast<int>(cudaGetLastError());
 }
 
 static int conv1_wgrad_blocks(int batch, int H, int W) {
-  // few row blocks: every block ends in an 80-value reduction and its partial must be re-read
-  const int nrows = tiles_for(batch, H, W) * kTileM;
-  int bx = nrows / (256 * 8);
-  if (bx < 4) bx = 4;
-  if (bx > 64) bx = 64;
+  // one block per image up to 64 blocks: every block ends in an 80-value reduction and its
+  // partial must be re-read, so more blocks than that only adds reduction work
+  (void)H; (void)W;
+  int bx = batch < 64 ? batch : 64;
+  if (bx < 1) bx = 1;
   return bx;
 }
 size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, int W) {
@@ -509,7 +619,7 @@ int ddpb_conv1_wgrad(const void* dact, const float* x, float* dw_db, float* scra
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int bx = conv1_wgrad_blocks(batch, H, W);
-  conv1_wgrad_kernel<1, 32><<<dim3(bx, cout / 8), 256, 0, st>>>(
+  conv1_wgrad_kernel<1, 32><<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
       static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = (long long)cout * cin * 9 + cout;
@@ -551,10 +661,9 @@ int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void
                       float* logits, float* dlogits, float* dbias, float* loss, int nout,
                       int batch, void* stream) {
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
-  int threads = ((batch * nout + 31) / 32) * 32;
-  if (threads > 1024) threads = 1024;
-  if (threads < 64) threads = 64;
-  softmax_xent_kernel<10><<<1, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+  const int blocks = (batch + kXentImgsPerBlock - 1) / kXentImgsPerBlock;
+  if (blocks > kXentMaxBlocks) return DDPB_ERR_LIMIT;
+  softmax_xent_kernel<10><<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       partial, S, bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss, batch);
   return static_cast<int>(cudaGetLastError());
 }
@@ -599,7 +708,7 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
 }
 
 int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream) {
-  long long blocks = (n + 1023) / 1024;
+  long long blocks = (n / 4 + 255) / 256;
   if (blocks > 592) blocks = 592;
   if (blocks < 1) blocks = 1;
   sgd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, grad, lr_dev, n);
@@ -659,7 +768,7 @@ extern "C" int ddpb_conv1_wgrad_noalloc(const void* dact, const float* x, float*
                                         void* stream) {
   if (!(cin == kNoAllocCin && cout == kNoAllocCout) || batch <= 0 || batch > batch_cap)
     return DDPB_ERR_SHAPE;
-  // blocks this batch needs, by the same rule as ddpb_conv1_wgrad but without its upper clamp
+  // partial blocks this batch is split into: one per 2048 padded-plane rows, at least 4
   const int nrows = tiles_for(batch, H, W) * kTileM;
   int bx = nrows / (256 * 8);
   if (bx < 4) bx = 4;
@@ -679,8 +788,9 @@ extern "C" int ddpb_conv1_wgrad_noalloc(const void* dact, const float* x, float*
 
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout><<<dim3(bx, cout / 8), 256, 0, st>>>(
-      static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
+  conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout>
+      <<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
+          static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = kNoAllocFloatsPerBlock;
   reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, bx, n,

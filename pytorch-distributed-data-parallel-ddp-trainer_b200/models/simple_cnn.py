@@ -198,14 +198,23 @@ class SimpleCNNB200(_ModelBase):
         self.nat.linear_bwd(self.act2, self.dlogits, self.wf, self.dact2, gs["wf"], self.scr_lin,
                             NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
-    def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
-        """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""
+    def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):
+        """conv2 weight + bias gradient (independent of the dgrad chain: may run on its own stream)."""
+        gs = self.grad_sets[parity]
+        self.nat.conv3x3_wgrad(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
+                               self.batch_cap, IMG_H, IMG_W, stream)
+
+    def backward_dgrad_conv1(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
+        """conv2 data gradient (with ReLU') followed by the conv1 weight + bias gradient."""
         nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
         gs = self.grad_sets[parity]
-        nat.conv3x3_wgrad(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
-                          cap, H, W, stream)
         nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
         nat.conv1_wgrad(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
+
+    def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
+        """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""
+        self.backward_conv2_wgrad(batch, stream, parity)
+        self.backward_dgrad_conv1(x, batch, stream, parity)
 
     def forward_backward(self, x: torch.Tensor, y: torch.Tensor, stream=None,
                          parity: int = 0) -> torch.Tensor:

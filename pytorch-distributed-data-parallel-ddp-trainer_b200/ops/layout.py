@@ -9,7 +9,7 @@ from __future__ import annotations
 import torch
 
 TILE_M = 128
-HALO = 40
+HALO = 32
 GUARD = 64
 
 

@@ -102,9 +102,11 @@ class B200DataParallel(_EngineBase):
 
         self.main = torch.cuda.Stream(self.device)
         self.side = torch.cuda.Stream(self.device)
+        self.side2 = torch.cuda.Stream(self.device)
         self.copy = torch.cuda.Stream(self.device)
         self._ev_fork = torch.cuda.Event()
         self._ev_join = torch.cuda.Event()
+        self._ev_join2 = torch.cuda.Event()
         self._ev_ready = [torch.cuda.Event(), torch.cuda.Event()]
         self._ev_free = [torch.cuda.Event(), torch.cuda.Event()]
         self.x_in = [torch.zeros(batch_cap, 1, IMG_H, IMG_W, device=self.device) for _ in range(2)]
@@ -134,30 +136,42 @@ class B200DataParallel(_EngineBase):
 
     # ------------------------------------------------------------------ the step
     def launches_per_step(self, batch: int) -> int:
-        return self.model.launches_per_step(batch) + (2 if self.world_size > 1 else 1)
+        return self.model.launches_per_step(batch) + 2
 
     def _enqueue(self, b: int, parity: int) -> None:
-        """Enqueue one full training step on self.main (+ self.side); capturable."""
+        """Enqueue one full training step; capturable.  Stream plan:
+
+            main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad | bucket-1 update
+            side : (after linear bwd)    bucket-0 all-reduce+SGD      (overlaps the conv backward)
+            side2: (after linear bwd)    conv2 wgrad                  (independent of the dgrad chain)
+        """
         m, main = self.model, self.main
         x, y = self.x_in[parity][:b], self.y_in[parity][:b]
+        (s0, n0), (s1, n1) = self.buckets
+        gflat = m.grad_sets[parity]["flat"]
         m.forward_loss(x, y, b, main, parity)
         m.backward_head(b, main, parity)
+        self._ev_fork.record(main)
+        self.side.wait_event(self._ev_fork)
+        self.side2.wait_event(self._ev_fork)
+        # bucket 0 (fl.weight, fl.bias) is complete: update it while the conv backward runs
         if self.world_size > 1:
-            (s0, n0), (s1, n1) = self.buckets
             goff = self.grad_off[parity]
-            self._ev_fork.record(main)
-            self.side.wait_event(self._ev_fork)
             self.comm.allreduce_sgd(goff + s0 * 4, self.param_off + s0 * 4, n0, m.lr_dev,
                                     self.algo, slot=0, stream=self.side)
-            self._ev_join.record(self.side)
-            m.backward_body(x, b, main, parity)
+        else:
+            m.nat.sgd(m.arena.params[s0:s0 + n0], gflat[s0:s0 + n0], m.lr_dev, self.side)
+        self._ev_join.record(self.side)
+        m.backward_conv2_wgrad(b, self.side2, parity)
+        self._ev_join2.record(self.side2)
+        m.backward_dgrad_conv1(x, b, main, parity)
+        main.wait_event(self._ev_join2)
+        if self.world_size > 1:
             self.comm.allreduce_sgd(goff + s1 * 4, self.param_off + s1 * 4, n1, m.lr_dev,
                                     self.algo, slot=1, stream=main)
-            main.wait_event(self._ev_join)
         else:
-            m.backward_body(x, b, main, parity)
-            n = m.arena.numel
-            m.nat.sgd(m.arena.params[:n], m.grad_sets[parity]["flat"][:n], m.lr_dev, main)
+            m.nat.sgd(m.arena.params[s1:s1 + n1], gflat[s1:s1 + n1], m.lr_dev, main)
+        main.wait_event(self._ev_join)
 
     def acquire_inputs(self):
         """Device buffers the next step() will read.  A loader may fill them in place on the
@@ -225,6 +239,7 @@ class B200DataParallel(_EngineBase):
     def synchronize(self) -> None:
         self.main.synchronize()
         self.side.synchronize()
+        self.side2.synchronize()
         self.copy.synchronize()
 
     def close(self) -> None:

@@ -1,4 +1,4 @@
-"""tcgen05.mma issue-cost microbenchmark (one CTA, one issuing thread).
+"""tcgen05.mma issue-cost microbenchmark (one CTA, one issuing thread, 32 MMAs unrolled).
 Prints cycles per MMA for the shapes/majors the conv kernels use.   python tools/mma_bench.py"""
 import ctypes
 import os
@@ -12,35 +12,40 @@ from ddp_b200.ops import native as nat
 lib = nat.lib()
 I, U, P = ctypes.c_int, ctypes.c_uint, ctypes.c_void_p
 lib.ddpb_mma_microbench.restype = I
-lib.ddpb_mma_microbench.argtypes = [I, I, I, I, I, I, I, I, U, U, U, U, P, P]
+lib.ddpb_mma_microbench.argtypes = [I, I, I, I, U, U, U, U, P, P]
 out = torch.zeros(2, dtype=torch.int64, device="cuda")
-ITERS = 512
+OUTER = 16
+PL = 3072  # stage plane bytes (192 rows x 16 B)
+# config -> (label, M, N)
+CFG = {0: ("K/K", 128, 256), 1: ("K/K", 128, 128), 2: ("K/K", 128, 64), 3: ("K/K", 128, 32),
+       4: ("K/K", 128, 16), 5: ("K/K one accumulator", 128, 64), 6: ("MN/MN", 64, 32),
+       7: ("MN/MN", 64, 96), 8: ("MN/MN", 64, 64), 9: ("MN/MN", 64, 8), 10: ("MN/MN", 128, 32),
+       11: ("MN/MN one accumulator", 64, 32), 12: ("K/K", 64, 32), 13: ("K/K", 64, 256)}
 
 
-def run(name, M, N, a_mn, b_mn, ash, bsh, nacc, lbo_a, sbo_a, lbo_b, sbo_b):
+def run(cfg, ash, bsh, la, sa, lb, sb, note=""):
+    label, M, N = CFG[cfg]
     for _ in range(2):
-        nat.check(lib.ddpb_mma_microbench(M, N, a_mn, b_mn, ash, bsh, nacc, ITERS, lbo_a, sbo_a, lbo_b,
-                                          sbo_b, out.data_ptr(), None), name)
+        nat.check(lib.ddpb_mma_microbench(cfg, ash, bsh, OUTER, la, sa, lb, sb, out.data_ptr(), None), label)
         torch.cuda.synchronize()
     issue, total = out.tolist()
-    ideal = max(M, 128) * N / 256
-    print(f"{name:52s} M={M:3d} N={N:3d} nacc={nacc}  issue {issue / ITERS:7.1f} cyc/mma   complete {total / ITERS:7.1f} cyc/mma"
-          f"   (model floor {ideal:5.1f})", flush=True)
+    n = OUTER * 32
+    print(f"{label:24s} M={M:3d} N={N:3d} {note:22s} issue {issue / n:6.1f}  complete {total / n:6.1f} cyc/mma"
+          f"  (floor {max(M, 128) * N / 256:5.1f})", flush=True)
 
 
-PL = 3328  # stage plane bytes (208 rows x 16 B)
-# K-major A (planes), K-major B (weights: LBO = N*16, SBO = 128)
-for N in (256, 128, 64, 32, 16):
-    run(f"K/K  A aligned      ", 128, N, 0, 0, 40, 0, min(4, 512 // N), PL, 128, N * 16, 128)
-run("K/K  A shifted +9 rows (tap)", 128, 64, 0, 0, 49, 0, 4, PL, 128, 64 * 16, 128)
-run("K/K  A shifted +9, same accumulator", 128, 64, 0, 0, 49, 0, 1, PL, 128, 64 * 16, 128)
-run("K/K  dgrad shape, shifted", 128, 32, 0, 0, 49, 0, 8, PL, 128, 32 * 16, 128)
-# MN-major A (dout planes 2048 B) and B (in planes 3328 B): LBO = 128 (K groups), SBO = plane
-for N in (32, 96, 128, 256):
-    run(f"MN/MN wgrad M=64, B aligned", 64, N, 1, 1, 0, 40, min(8, 512 // N), 128, 2048, 128, PL)
-run("MN/MN wgrad M=64 N=32, B shifted +9", 64, 32, 1, 1, 0, 49, 9, 128, 2048, 128, PL)
-run("MN/MN wgrad M=64 N=32, B shifted, same acc", 64, 32, 1, 1, 0, 49, 1, 128, 2048, 128, PL)
-run("MN/MN M=128 N=32 (two 64-ch halves)", 128, 32, 1, 1, 0, 49, 9, 128, 2048, 128, PL)
-run("MN/MN M=64 N=8 (bias)", 64, 8, 1, 1, 0, 0, 8, 128, 2048, 128, 128)
-run("MN A / K B  M=64 N=32", 64, 32, 1, 0, 0, 0, 8, 128, 2048, 32 * 16, 128)
-run("K A / MN B  M=128 N=32", 128, 32, 0, 1, 40, 49, 8, PL, 128, 128, PL)
+for cfg in (0, 1, 2, 3, 4):
+    N = CFG[cfg][2]
+    run(cfg, 40, 0, PL, 128, N * 16, 128, "A aligned")
+run(2, 49, 0, PL, 128, 64 * 16, 128, "A shifted 9 rows")
+run(5, 49, 0, PL, 128, 64 * 16, 128, "A shifted 9 rows")
+run(3, 49, 0, PL, 128, 32 * 16, 128, "A shifted (dgrad)")
+run(12, 40, 0, PL, 128, 32 * 16, 128, "M=64 K-major")
+run(13, 40, 0, PL, 128, 256 * 16, 128, "M=64 K-major")
+for cfg in (6, 8, 7):
+    run(cfg, 0, 40, 128, 2048, 128, PL, "B aligned")
+run(6, 0, 49, 128, 2048, 128, PL, "B shifted 9 rows")
+run(7, 0, 49, 128, 2048, 128, PL, "B shifted 9 rows")
+run(11, 0, 49, 128, 2048, 128, PL, "B shifted 9 rows")
+run(10, 0, 49, 128, 2048, 128, PL, "M=128 (16 planes)")
+run(9, 0, 0, 128, 2048, 128, 128, "bias block")
