@@ -344,23 +344,23 @@ linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 // z = bias + sum_s partial[s]; loss = mean_i(logsumexp(z_i) - z_i[y_i]);
 // dlogits = (softmax(z) - onehot(y)) / batch; db[j] = sum_i dlogits[i][j].
 // Single block: the work is batch*NOUT*S floats.
-// Multi-block: block b handles images [256b, 256b+256).  Block sums of the loss and of dbias go to
+// Multi-block: block b handles images [32b, 32b+32).  Block sums of the loss and of dbias go to
 // a small library-resident array; the block that finishes last (ticket counter) adds them up in
 // block order, so the result is deterministic.  The ticket resets itself; calls on one device must
 // not overlap (the step engine issues one at a time).
-constexpr int kXentImgsPerBlock = 256;
-constexpr int kXentMaxBlocks = 512;  // batches up to 131072
+constexpr int kXentImgsPerBlock = 32;  // x NOUT classes = one (image, class) pair per thread
+constexpr int kXentMaxBlocks = 2048;   // batches up to 65536
 static __device__ float g_xent_block_sums[kXentMaxBlocks * 12];
 static __device__ unsigned int g_xent_ticket;
 
 template <int NOUT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kXentImgsPerBlock * NOUT)
 softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
                     const long long* __restrict__ labels, float* __restrict__ logits,
                     float* __restrict__ dlogits, float* __restrict__ dbias,
                     float* __restrict__ loss, int batch) {
   static_assert(NOUT + 1 <= 12, "block-sum row too small");
-  __shared__ float red[8][NOUT + 1];
+  __shared__ float red[(kXentImgsPerBlock * NOUT + 31) / 32][NOUT + 1];
   __shared__ bool is_last;
   const int img0 = blockIdx.x * kXentImgsPerBlock;
   const int nimg = min(kXentImgsPerBlock, batch - img0);
@@ -370,12 +370,12 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
     const long long gt = (long long)img0 * NOUT + t;
     float z = bias[t % NOUT];
     int sidx = 0;
-    for (; sidx + 4 <= S; sidx += 4) {
-      float v[4];
+    for (; sidx + 8 <= S; sidx += 8) {
+      float v[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sidx + u) * npair_all + gt];
+      for (int u = 0; u < 8; ++u) v[u] = partial[(long long)(sidx + u) * npair_all + gt];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) z += v[u];
+      for (int u = 0; u < 8; ++u) z += v[u];
     }
     for (; sidx < S; ++sidx) z += partial[(long long)sidx * npair_all + gt];
     logits[gt] = z;
@@ -422,8 +422,8 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
   __syncthreads();
   if (threadIdx.x <= NOUT) {
     float s = 0.f;
-#pragma unroll
-    for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][threadIdx.x];
+    const int nw = (blockDim.x + 31) >> 5;
+    for (int wdx = 0; wdx < nw; ++wdx) s += red[wdx][threadIdx.x];
     g_xent_block_sums[blockIdx.x * 12 + threadIdx.x] = s;
     __threadfence();
   }
@@ -663,7 +663,7 @@ int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
   const int blocks = (batch + kXentImgsPerBlock - 1) / kXentImgsPerBlock;
   if (blocks > kXentMaxBlocks) return DDPB_ERR_LIMIT;
-  softmax_xent_kernel<10><<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  softmax_xent_kernel<10><<<blocks, kXentImgsPerBlock * 10, 0, static_cast<cudaStream_t>(stream)>>>(
       partial, S, bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss, batch);
   return static_cast<int>(cudaGetLastError());
 }
