@@ -31,6 +31,7 @@
 
 #include "ptx.cuh"
 #include "api_internal.cuh"
+#include "launch.cuh"
 
 namespace ddpb {
 
@@ -76,7 +77,8 @@ __device__ __forceinline__ void flag_round(const PeerPtrs& pp, int rank, int slo
   __syncthreads();
   if (threadIdx.x < WORLD) {
     const int r = threadIdx.x;
-    __threadfence_system();
+    // st.release.sys is cumulative over everything ordered before it, which the bar.sync above
+    // makes include the whole block's earlier writes: no separate system fence is needed.
     st_release_sys(flag_word(pp.p[r], slot, blockIdx.x, rank), e);
     const uint32_t* mine = flag_word(pp.p[rank], slot, blockIdx.x, r);
     if (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
@@ -115,6 +117,7 @@ __global__ void __launch_bounds__(kCommThreads)
 allreduce_sgd_oneshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
                              long long n4, const float* __restrict__ lr,
                              unsigned long long timeout_ns) {
+  pdl_sync();
   uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
   const uint32_t e = *ep + 1;
   flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
@@ -146,6 +149,7 @@ __global__ void __launch_bounds__(kCommThreads)
 allreduce_sgd_twoshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
                              long long n4, const float* __restrict__ lr,
                              unsigned long long timeout_ns) {
+  pdl_sync();
   uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
   const uint32_t e = *ep + 1;
   flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
@@ -387,11 +391,12 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
   const size_t go = grad_off + kHeaderBytes, po = param_off + kHeaderBytes;
   DDPB_DISPATCH_WORLD(c->world, {
     if (two)
-      allreduce_sgd_twoshot_kernel<WORLD><<<blocks, kCommThreads, 0, st>>>(
-          pp, c->rank, slot, go, po, n4, lr_dev, c->timeout_ns);
-    else
-      allreduce_sgd_oneshot_kernel<WORLD><<<blocks, kCommThreads, 0, st>>>(
-          pp, c->rank, slot, go, po, n4, lr_dev, c->timeout_ns);
+      return static_cast<int>(launch_k(allreduce_sgd_twoshot_kernel<WORLD>, dim3(blocks),
+                                       dim3(kCommThreads), 0, st, pp, c->rank, slot, go, po, n4, lr_dev,
+                                       c->timeout_ns));
+    return static_cast<int>(launch_k(allreduce_sgd_oneshot_kernel<WORLD>, dim3(blocks),
+                                     dim3(kCommThreads), 0, st, pp, c->rank, slot, go, po, n4, lr_dev,
+                                     c->timeout_ns));
   });
   return static_cast<int>(cudaGetLastError());
 }

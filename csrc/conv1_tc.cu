@@ -1,0 +1,423 @@
+// First convolution (Cin = 1, 3x3, pad 1) on the tensor cores.
+//
+// K = 9 is far too thin for a normal tile, but a tcgen05.mma costs ~45 cycles whatever its
+// shape (tools/mma_bench.py), while the CUDA-core version needs 72 FMAs per pixel per 8 channels
+// and was instruction-bound (profiles/).  So:
+//   forward : per 128-pixel tile the producer warps build the im2col rows [128 x 16] (9 taps +
+//             zero padding) in shared memory as TF32 — the precision cuDNN uses for the
+//             reference's convolutions by default — two K=8 MMAs against W1 [32 x 16], epilogue
+//             = bias + ReLU + bf16 planes (same epilogue as conv2).
+//   wgrad   : dW1[c][tap] = sum_p dact1[p][c] * x[p + tap]:  A = the dact1 planes as an MN-major
+//             operand (bulk-copied), B = im2col rows built by the producers as TWO bf16 terms
+//             (x = hi + lo, so the bf16 MMA keeps ~16 mantissa bits of x) plus a column of ones
+//             that yields the bias gradient; M = 64 (32 real channels), N = 32, K = 128 pixels
+//             per tile; per-CTA partial in TMEM, fixed-order reduce.
+// Replaces cuDNN conv fwd / wgrad + ATen relu for reference model.py:9-10 (SURVEY.md K1,K2,K12,K13).
+#include "ptx.cuh"
+#include "layout.cuh"
+#include "api_internal.cuh"
+#include "launch.cuh"
+
+namespace ddpb {
+
+constexpr int kC1Threads = 288;  // warps 0-3 producers, 4 MMA/TMEM, 5-8 epilogue
+constexpr int kC1Stages = 3;
+
+constexpr int kXStages = 3;             // input-image staging ring (prefetch distance in tiles)
+constexpr uint32_t kXStageBytes = 8192;  // two images of up to 32x32 fp32
+
+// A 128-row tile touches at most two consecutive images.  One bulk async copy stages both
+// (clamped to the batch) into shared memory; returns the first staged image index.
+__device__ __forceinline__ int x_stage_first_image(const Geom& g, int tile) {
+  const int img0 = (tile * kTileM) / g.PHW;
+  const int last_start = g.batch >= 2 ? g.batch - 2 : 0;
+  return img0 < last_start ? img0 : last_start;
+}
+__device__ __forceinline__ void x_stage_issue(const float* __restrict__ x, const Geom& g, int tile,
+                                              uint32_t dst_smem, uint32_t bar) {
+  const int first = x_stage_first_image(g, tile);
+  const uint32_t img_bytes = g.H * g.W * 4;
+  const uint32_t bytes = (g.batch >= 2 ? 2 : 1) * img_bytes;
+  mbar_arrive_expect_tx(bar, bytes);
+  bulk_g2s(dst_smem, x + (long long)first * g.H * g.W, bytes, bar);
+}
+__device__ __forceinline__ void taps_from_stage(const float* xs, const Geom& g, int li, int h, int w,
+                                                float (&t)[9]) {
+  const float* xp = xs + li * g.H * g.W;
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int hh = h + r - 1, ww = w + s - 1;
+      t[r * 3 + s] = (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
+    }
+}
+__device__ __forceinline__ void producer_sync() {  // the 128 producer threads only
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+
+// ------------------------------------------------------------------------------------- forward
+struct C1FwdSmem {
+  static constexpr uint32_t b_bytes = 4 * 32 * 16;        // W1 as tf32 [4 kchunks][32 n][4]
+  static constexpr uint32_t a_plane = kTileM * 16;        // one k-chunk of all 128 rows
+  static constexpr uint32_t a_stage = 4 * a_plane;        // 8 KB
+  static constexpr uint32_t off_a = b_bytes;
+  static constexpr uint32_t off_x = off_a + kC1Stages * a_stage;
+  static constexpr uint32_t off_bias = off_x + kXStages * kXStageBytes;
+  static constexpr uint32_t off_bar = off_bias + 32 * 4;
+  static constexpr uint32_t off_tmem = off_bar + (2 * kC1Stages + 4 + kXStages) * 8;
+  static constexpr uint32_t total = off_tmem + 16;
+};
+
+__global__ void __launch_bounds__(kC1Threads, 1)
+conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                    const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, Geom g) {
+  using S = C1FwdSmem;
+  constexpr int CO = 32;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t s_a = s_base + S::off_a;
+  float* s_bias = reinterpret_cast<float*>(smem + S::off_bias);
+  const uint32_t bar_full = s_base + S::off_bar;
+  const uint32_t bar_empty = bar_full + kC1Stages * 8;
+  const uint32_t bar_tfull = bar_empty + kC1Stages * 8;
+  const uint32_t bar_tempty = bar_tfull + 16;
+  const uint32_t bar_x = bar_tempty + 16;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+
+  if (tid == 0) {
+    for (int i = 0; i < kC1Stages; ++i) {
+      mbar_init(bar_full + i * 8, 128);
+      mbar_init(bar_empty + i * 8, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_tfull + i * 8, 1);
+      mbar_init(bar_tempty + i * 8, 128);
+    }
+    for (int i = 0; i < kXStages; ++i) mbar_init(bar_x + i * 8, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(smem_u32(s_tmem), 64);
+    tmem_relinquish();
+  }
+  // The stream predecessor is the previous step's parameter update, which writes w and bias:
+  // nothing global may be read before it has completed.
+  pdl_sync();
+  // W1 [32][9] -> tf32 K-major canonical tile: word (k/4)*128 + n*4 + k%4 ; k >= 9 is zero padding
+  for (int i = tid; i < 32 * 16; i += kC1Threads) {
+    const int n = i >> 4, k = i & 15;
+    reinterpret_cast<float*>(smem)[(k >> 2) * 128 + n * 4 + (k & 3)] = k < 9 ? w[n * 9 + k] : 0.f;
+  }
+  if (tid < CO) s_bias[tid] = bias[tid];
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp < 4) {
+    // ---- producers: one im2col row per thread; the tile's input images arrive by bulk copy
+    if (tid == 0) {
+      int pre = 0;
+      for (int t = blockIdx.x; t < g.ntiles && pre < kXStages; t += gridDim.x, ++pre)
+        x_stage_issue(x, g, t, s_base + S::off_x + pre * kXStageBytes, bar_x + pre * 8);
+    }
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % kC1Stages;
+      const uint32_t phase = (it / kC1Stages) & 1;
+      const int xst = it % kXStages;
+      int img, h, wc;
+      const bool valid = decode_row(g, t * kTileM + tid, img, h, wc);
+      float tp[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) tp[i] = 0.f;
+      mbar_wait(bar_x + xst * 8, (it / kXStages) & 1);
+      if (valid)
+        taps_from_stage(reinterpret_cast<const float*>(smem + S::off_x + xst * kXStageBytes), g,
+                        img - x_stage_first_image(g, t), h, wc, tp);
+      producer_sync();  // every producer has read this x stage: refill it for tile it + kXStages
+      if (tid == 0) {
+        const int tn = t + kXStages * gridDim.x;
+        if (tn < g.ntiles)
+          x_stage_issue(x, g, tn, s_base + S::off_x + xst * kXStageBytes, bar_x + xst * 8);
+      }
+      mbar_wait(bar_empty + stage * 8, phase ^ 1);
+      uint8_t* a = smem + S::off_a + stage * S::a_stage + tid * 16;
+      *reinterpret_cast<float4*>(a) = make_float4(tp[0], tp[1], tp[2], tp[3]);
+      *reinterpret_cast<float4*>(a + S::a_plane) = make_float4(tp[4], tp[5], tp[6], tp[7]);
+      *reinterpret_cast<float4*>(a + 2 * S::a_plane) = make_float4(tp[8], 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(a + 3 * S::a_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
+      fence_proxy_async_smem();
+      mbar_arrive(bar_full + stage * 8);
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_tf32(kTileM, CO);
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % kC1Stages;
+        const uint32_t phase = (it / kC1Stages) & 1;
+        const int acc = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
+        mbar_wait(bar_full + stage * 8, phase);
+        tc_fence_after();
+        const uint32_t a_stage = s_a + stage * S::a_stage;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk)
+          umma_tf32(tmem_base + acc * CO,
+                    umma_smem_desc(a_stage + kk * 2 * S::a_plane, S::a_plane, 128),
+                    umma_smem_desc(s_base + kk * 2 * 512, 512, 128), idesc, kk != 0);
+        umma_commit(bar_empty + stage * 8);
+        umma_commit(bar_tfull + acc * 8);
+      }
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(bar_tfull + acc * 8, aphase);
+      tc_fence_after();
+      const int rel = t * kTileM + q * 32 + lane;
+      int img, h, wc;
+      const bool valid = decode_row(g, rel, img, h, wc);
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * CO, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(bar_tempty + acc * 8);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4 o;
+        uint32_t* op = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float x0 = __uint_as_float(v[j * 8 + 2 * e]) + s_bias[j * 8 + 2 * e];
+          float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + s_bias[j * 8 + 2 * e + 1];
+          x0 = valid ? fmaxf(x0, 0.f) : 0.f;
+          x1 = valid ? fmaxf(x1, 0.f) : 0.f;
+          op[e] = pack_bf16x2(x0, x1);
+        }
+        *reinterpret_cast<uint4*>(out + ((long long)j * g.plane_rows + kGuard + rel) * 8) = o;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem_base, 64);
+}
+
+// ------------------------------------------------------------------------------------- wgrad
+// Accumulator [64 rows (32 real channels)][32 columns]:
+//   columns 0..8 : sum dact * bf16_hi(x tap)     9 : sum dact (bias gradient)
+//   columns 16..24: sum dact * bf16_lo(x tap)    others: zero
+struct C1WgradSmem {
+  static constexpr uint32_t a_plane = kTileM * 16;   // 2048
+  static constexpr uint32_t a_bytes = 8 * a_plane;   // planes 4..7 stay zero (M = 64 needs 8 groups)
+  static constexpr uint32_t b_bytes = 4 * a_plane;   // N = 32 -> 4 groups of 8 columns
+  static constexpr uint32_t stage = a_bytes + b_bytes;
+  static constexpr uint32_t off_x = kC1Stages * stage;
+  static constexpr uint32_t off_bar = off_x + kXStages * kXStageBytes;
+  static constexpr uint32_t off_tmem = off_bar + (3 * kC1Stages + 1 + kXStages) * 8;
+  static constexpr uint32_t total = off_tmem + 16;
+};
+
+__global__ void __launch_bounds__(kC1Threads, 1)
+conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restrict__ x,
+                      float* __restrict__ partial, Geom g) {
+  using S = C1WgradSmem;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s_base = smem_u32(smem);
+  const uint32_t bar_fa = s_base + S::off_bar;            // dact planes landed (TMA tx)
+  const uint32_t bar_fb = bar_fa + kC1Stages * 8;         // im2col rows written (128 arrivals)
+  const uint32_t bar_empty = bar_fb + kC1Stages * 8;
+  const uint32_t bar_done = bar_empty + kC1Stages * 8;
+  const uint32_t bar_x = bar_done + 8;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
+
+  for (int i = tid; i < (int)(kC1Stages * S::stage / 16); i += kC1Threads)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  if (tid == 0) {
+    for (int i = 0; i < kC1Stages; ++i) {
+      mbar_init(bar_fa + i * 8, 1);
+      mbar_init(bar_fb + i * 8, 128);
+      mbar_init(bar_empty + i * 8, 1);
+    }
+    mbar_init(bar_done, 1);
+    for (int i = 0; i < kXStages; ++i) mbar_init(bar_x + i * 8, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(smem_u32(s_tmem), 32);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  pdl_sync();
+
+  if (warp < 4) {
+    if (tid == 0) {
+      int pre = 0;
+      for (int t = blockIdx.x; t < g.ntiles && pre < kXStages; t += gridDim.x, ++pre)
+        x_stage_issue(x, g, t, s_base + S::off_x + pre * kXStageBytes, bar_x + pre * 8);
+    }
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % kC1Stages;
+      const uint32_t phase = (it / kC1Stages) & 1;
+      const int xst = it % kXStages;
+      int img, h, wc;
+      const bool valid = decode_row(g, t * kTileM + tid, img, h, wc);
+      float tp[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) tp[i] = 0.f;
+      mbar_wait(bar_x + xst * 8, (it / kXStages) & 1);
+      if (valid)
+        taps_from_stage(reinterpret_cast<const float*>(smem + S::off_x + xst * kXStageBytes), g,
+                        img - x_stage_first_image(g, t), h, wc, tp);
+      producer_sync();
+      if (tid == 0) {
+        const int tn = t + kXStages * gridDim.x;
+        if (tn < g.ntiles)
+          x_stage_issue(x, g, tn, s_base + S::off_x + xst * kXStageBytes, bar_x + xst * 8);
+      }
+      // x = hi + lo with both terms bf16
+      uint32_t hi[5], lo[5];
+      float hf[9], lf[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        hf[i] = __bfloat162float(__float2bfloat16(tp[i]));
+        lf[i] = tp[i] - hf[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        hi[i] = pack_bf16x2(hf[2 * i], hf[2 * i + 1]);
+        lo[i] = pack_bf16x2(lf[2 * i], lf[2 * i + 1]);
+      }
+      hi[4] = pack_bf16x2(hf[8], 1.0f);  // column 9 = ones -> bias gradient
+      lo[4] = pack_bf16x2(lf[8], 0.f);
+      mbar_wait(bar_empty + stage * 8, phase ^ 1);
+      if (tid == 0) {
+        mbar_arrive_expect_tx(bar_fa + stage * 8, 4 * S::a_plane);
+        const long long rowa = (long long)kGuard + (long long)t * kTileM;
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+          bulk_g2s(s_base + stage * S::stage + p * S::a_plane,
+                   dact + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane, bar_fa + stage * 8);
+      }
+      uint8_t* b = smem + stage * S::stage + S::a_bytes + tid * 16;
+      *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4*>(b + S::a_plane) = make_uint4(hi[4], 0, 0, 0);
+      *reinterpret_cast<uint4*>(b + 2 * S::a_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      *reinterpret_cast<uint4*>(b + 3 * S::a_plane) = make_uint4(lo[4], 0, 0, 0);
+      fence_proxy_async_smem();
+      mbar_arrive(bar_fb + stage * 8);
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(64, 32, 1, 1);
+      int it = 0;
+      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+        const int stage = it % kC1Stages;
+        const uint32_t phase = (it / kC1Stages) & 1;
+        mbar_wait(bar_fa + stage * 8, phase);
+        mbar_wait(bar_fb + stage * 8, phase);
+        tc_fence_after();
+        const uint32_t sa = s_base + stage * S::stage;
+        const uint32_t sb = sa + S::a_bytes;
+#pragma unroll
+        for (int ks = 0; ks < kTileM / 16; ++ks)
+          umma_bf16(tmem_base, umma_smem_desc(sa + ks * 256, 128, S::a_plane),
+                    umma_smem_desc(sb + ks * 256, 128, S::a_plane), idesc, (it | ks) != 0);
+        umma_commit(bar_empty + stage * 8);
+      }
+      umma_commit(bar_done);
+    }
+    __syncwarp();
+  } else {
+    const int q = warp & 3;
+    mbar_wait(bar_done, 0);
+    tc_fence_after();
+    uint32_t v[32];
+    tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16), v);
+    tmem_ld_wait();
+    // M = 64: row m lives in lane (m % 16) + 32 * (m / 16); channels 0..31 are rows 0..31
+    if (q < 2 && lane < 16) {
+      const int c = q * 16 + lane;
+      float* dst = partial + (long long)blockIdx.x * (32 * 9 + 32);
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap)
+        dst[c * 9 + tap] = __uint_as_float(v[tap]) + __uint_as_float(v[16 + tap]);
+      dst[32 * 9 + c] = __uint_as_float(v[9]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc(tmem_base, 32);
+}
+
+}  // namespace ddpb
+
+using namespace ddpb;
+
+extern "C" {
+
+int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out, int cin, int cout,
+                      int batch, int batch_cap, int H, int W, void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
+  static bool configured[64] = {};
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C1FwdSmem::total));
+    configured[dev & 63] = true;
+  }
+  const int sms = ddpb_num_sms();
+  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  return static_cast<int>(launch_k(conv1_fwd_tc_kernel, dim3(grid), dim3(kC1Threads), C1FwdSmem::total,
+                                   static_cast<cudaStream_t>(stream), x, w, b,
+                                   static_cast<__nv_bfloat16*>(out), g));
+}
+
+size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout) {
+  return static_cast<size_t>(ddpb_num_sms()) * (cout * cin * 9 + cout) * sizeof(float);
+}
+
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
+
+// dw_db: cout*cin*9 weight gradients immediately followed by cout bias gradients.
+int ddpb_conv1_wgrad_tc(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
+                        int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  static bool configured[64] = {};
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C1WgradSmem::total));
+    configured[dev & 63] = true;
+  }
+  const int sms = ddpb_num_sms();
+  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  DDPB_CUDA_OK(launch_k(conv1_wgrad_tc_kernel, dim3(grid), dim3(kC1Threads), C1WgradSmem::total,
+                        static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dact), x,
+                        scratch, g));
+  return ddpb_reduce_partials(scratch, grid, (long long)cout * cin * 9 + cout, dw_db, stream);
+}
+
+}  // extern "C"

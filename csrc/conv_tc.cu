@@ -13,6 +13,7 @@
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
+#include "launch.cuh"
 
 namespace ddpb {
 
@@ -131,6 +132,10 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
   if (tid == 0) prof_stamp(prof, 2);
+  // Everything above touched only this CTA's shared memory / TMEM and the layer's weights (last
+  // written by the previous step's update, complete before our stream predecessor even started).
+  // From here on we read what the predecessor wrote.
+  pdl_sync();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -317,6 +322,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
   tc_fence_after();
   const uint32_t tmem_row[3] = {s_tmem[0], s_tmem[1], s_tmem[2]};
   if (tid == 0) prof_stamp(prof, 2);
+  pdl_sync();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -429,6 +435,7 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __rest
   constexpr int ncols = n0 + 2 * n1;
   constexpr int total = CO * ncols;
   __shared__ float sm[8][32];
+  pdl_sync();
   const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
   const int idx = blockIdx.x * 32 + lane;
   float s = 0.f;
@@ -488,10 +495,10 @@ static int launch_conv(const void* in, const float* w, const float* bias, const 
     configured[dev & 63] = true;
   }
   const int grid = g.ntiles < num_sms ? g.ntiles : num_sms;
-  kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(in), w, bias,
-                                             static_cast<const __nv_bfloat16*>(mask),
-                                             static_cast<__nv_bfloat16*>(out), g, g_prof);
-  return static_cast<int>(cudaGetLastError());
+  return static_cast<int>(launch_k(kern, dim3(grid), dim3(kConvThreads), S::total, st,
+                                   static_cast<const __nv_bfloat16*>(in), w, bias,
+                                   static_cast<const __nv_bfloat16*>(mask),
+                                   static_cast<__nv_bfloat16*>(out), g, g_prof));
 }
 
 }  // namespace ddpb
@@ -548,12 +555,12 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
   }
   const int sms = ddpb_num_sms();
   const int grid = g.ntiles < sms ? g.ntiles : sms;
-  kern<<<grid, kConvThreads, S::total, st>>>(static_cast<const __nv_bfloat16*>(dout),
-                                             static_cast<const __nv_bfloat16*>(in), scratch, g, g_prof);
-  DDPB_CUDA_OK(cudaGetLastError());
+  DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kConvThreads), S::total, st,
+                        static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(in),
+                        scratch, g, g_prof));
   const int n = CO * (9 * CI + 8);
-  wgrad_reduce_kernel<CI, CO><<<(n + 31) / 32, 256, 0, st>>>(scratch, grid, dw, db);
-  return static_cast<int>(cudaGetLastError());
+  return static_cast<int>(launch_k(wgrad_reduce_kernel<CI, CO>, dim3((n + 31) / 32), dim3(256), 0, st,
+                                   static_cast<const float*>(scratch), grid, dw, db));
 }
 
 }  // extern "C"

@@ -14,8 +14,19 @@
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
+#include "launch.cuh"
+#include <stdlib.h>
 
 namespace ddpb {
+
+int pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("DDPB_PDL");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v;
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -243,6 +254,7 @@ conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restri
 // out[i] = sum_p part[p*n + i], fixed order => deterministic.
 __global__ void reduce_partials_kernel(const float* __restrict__ part, int nparts, long long n,
                                        float* __restrict__ out) {
+  pdl_sync();
   const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i4 >= n) return;
   if (i4 + 3 < n && (n & 3) == 0) {
@@ -272,6 +284,37 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, int npart
   }
 }
 
+// Same sum (fixed order) when there are many partials of a short vector: 256 threads = 32
+// consecutive outputs x 8 partial groups, group pg adds parts pg, pg+8, ... and the 8 group sums
+// are combined in group order.  Turns a chain of nparts dependent loads into nparts/8.
+__global__ void __launch_bounds__(256)
+reduce_partials_wide_kernel(const float* __restrict__ part, int nparts, long long n,
+                            float* __restrict__ out) {
+  pdl_sync();
+  __shared__ float sm[8][32];
+  const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
+  const long long idx = (long long)blockIdx.x * 32 + lane;
+  float s = 0.f;
+  if (idx < n) {
+    int p = pg;
+    for (; p + 24 < nparts; p += 32) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = part[(long long)(p + 8 * u) * n + idx];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s += v[u];
+    }
+    for (; p < nparts; p += 8) s += part[(long long)p * n + idx];
+  }
+  sm[pg][lane] = s;
+  __syncthreads();
+  if (pg == 0 && idx < n) {
+#pragma unroll
+    for (int u = 1; u < 8; ++u) s += sm[u][lane];
+    out[idx] = s;
+  }
+}
+
 // ------------------------------------------------------------------ linear forward
 // logits[img][j] = sum_k act[img][k] * W[j][k]; k = c*H*W + h*W + w (NCHW flatten order of the
 // reference, model.py:13,16).  grid = (S feature slices, image groups of IMG); writes
@@ -280,6 +323,7 @@ template <int NOUT, int IMG>
 __global__ void __launch_bounds__(256, 1)
 linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ W,
                   float* __restrict__ partial, Geom g, int C, int vec_per_slice) {
+  pdl_sync();
   __shared__ float red[8][IMG * NOUT];
   const int HW = g.H * g.W;
   const int nvec = (C / 8) * HW;
@@ -359,6 +403,7 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
                     const long long* __restrict__ labels, float* __restrict__ logits,
                     float* __restrict__ dlogits, float* __restrict__ dbias,
                     float* __restrict__ loss, int batch) {
+  pdl_sync();
   static_assert(NOUT + 1 <= 12, "block-sum row too small");
   __shared__ float red[(kXentImgsPerBlock * NOUT + 31) / 32][NOUT + 1];
   __shared__ bool is_last;
@@ -453,6 +498,7 @@ __global__ void __launch_bounds__(256, 2)
 linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ dlogits,
                   const float* __restrict__ W, __nv_bfloat16* __restrict__ dact,
                   float* __restrict__ dw_partial, Geom g, int C, int imgs_per_split) {
+  pdl_sync();
   extern __shared__ float sdl[];  // [imgs_per_split][NOUT]
   constexpr int PF = 8;           // image vectors kept in flight per thread
   const int HW = g.H * g.W;
@@ -521,6 +567,7 @@ linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 // the weight-gradient GEMM (which reduces over whole tiles) never sees stale rows after a
 // short tail batch (reference data.py:21-25 uses drop_last=False).
 __global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int nplanes, Geom g) {
+  pdl_sync();
   const int first = g.batch * g.PHW;
   const int nrows = g.ntiles * kTileM - first;
   const long long total = (long long)nplanes * nrows;
@@ -537,6 +584,7 @@ __global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int np
 // p -= lr * g.  lr lives in device memory so a captured graph can be replayed with a new value.
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ grad,
                            const float* __restrict__ lr, long long n) {
+  pdl_sync();
   const float l = *lr;
   const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(grad)) & 15) == 0;
   const long long n4 = vec ? n / 4 : 0;
@@ -651,10 +699,10 @@ int ddpb_linear_fwd(const void* act, const float* Wt, float* partial, int* S_out
   const int nvec = (C / 8) * H * W;
   int S, per, groups;
   linear_fwd_geom(batch, nvec, S, per, groups);
-  linear_fwd_kernel<10, 8><<<dim3(S, groups), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(act), Wt, partial, g, C, per);
   if (S_out) *S_out = S;
-  return static_cast<int>(cudaGetLastError());
+  return static_cast<int>(launch_k(linear_fwd_kernel<10, 8>, dim3(S, groups), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream),
+                                   static_cast<const __nv_bfloat16*>(act), Wt, partial, g, C, per));
 }
 
 int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels,
@@ -663,10 +711,13 @@ int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
   const int blocks = (batch + kXentImgsPerBlock - 1) / kXentImgsPerBlock;
   if (blocks > kXentMaxBlocks) return DDPB_ERR_LIMIT;
-  softmax_xent_kernel<10><<<blocks, kXentImgsPerBlock * 10, 0, static_cast<cudaStream_t>(stream)>>>(
-      partial, S, bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss, batch);
-  return static_cast<int>(cudaGetLastError());
+  return static_cast<int>(launch_k(softmax_xent_kernel<10>, dim3(blocks), dim3(kXentImgsPerBlock * 10), 0,
+                                   static_cast<cudaStream_t>(stream), partial, S, bias,
+                                   static_cast<const long long*>(labels), logits, dlogits, dbias, loss,
+                                   batch));
 }
+
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
 
 static int linear_bwd_imgs_per_split(int batch) {
   // enough splits to fill the GPU at small batch, few enough that partial traffic stays small
@@ -694,25 +745,32 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
   const int ips = linear_bwd_imgs_per_split(batch);
   const int splits = (batch + ips - 1) / ips;
   if (g.ntiles * kTileM > batch * g.PHW) {
-    zero_tail_rows_kernel<<<8, 256, 0, st>>>(static_cast<__nv_bfloat16*>(dact), C / 8, g);
-    DDPB_CUDA_OK(cudaGetLastError());
+    DDPB_CUDA_OK(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0, st,
+                          static_cast<__nv_bfloat16*>(dact), C / 8, g));
   }
-  linear_bwd_kernel<10><<<dim3((nvec + 255) / 256, splits), 256, ips * 10 * sizeof(float), st>>>(
-      static_cast<const __nv_bfloat16*>(act), dlogits, Wt, static_cast<__nv_bfloat16*>(dact),
-      scratch, g, C, ips);
-  DDPB_CUDA_OK(cudaGetLastError());
-  const long long n = (long long)nout * C * H * W;
-  reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, splits,
-                                                                                    n, dW);
-  return static_cast<int>(cudaGetLastError());
+  DDPB_CUDA_OK(launch_k(linear_bwd_kernel<10>, dim3((nvec + 255) / 256, splits), dim3(256),
+                        ips * 10 * sizeof(float), st, static_cast<const __nv_bfloat16*>(act), dlogits,
+                        Wt, static_cast<__nv_bfloat16*>(dact), scratch, g, C, ips));
+  return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
+}
+
+// out[i] = sum_p part[p*n + i] in a fixed order (shared by the split-K style kernels).
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (nparts >= 16 && n <= (1 << 16))
+    return static_cast<int>(launch_k(reduce_partials_wide_kernel, dim3(static_cast<int>((n + 31) / 32)),
+                                     dim3(256), 0, st, part, nparts, n, out));
+  return static_cast<int>(launch_k(reduce_partials_kernel,
+                                   dim3(static_cast<int>((n / 4 + 255) / 256 + 1)), dim3(256), 0, st, part,
+                                   nparts, n, out));
 }
 
 int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream) {
   long long blocks = (n / 4 + 255) / 256;
   if (blocks > 592) blocks = 592;
   if (blocks < 1) blocks = 1;
-  sgd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(p, grad, lr_dev, n);
-  return static_cast<int>(cudaGetLastError());
+  return static_cast<int>(launch_k(sgd_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), p, grad, lr_dev, n));
 }
 
 const char* ddpb_error_string(int code) {

@@ -57,6 +57,17 @@ size_t ddpb_conv1_wgrad_scratch_bytes(int cin, int cout, int batch_cap, int H, i
 int ddpb_conv1_wgrad(const void* dact_planes, const float* x, float* dw_db, float* scratch,
                      int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
 
+/* Tensor-core versions (the step engine uses these): forward = im2col rows built in shared memory
+ * as TF32 + tcgen05.mma kind::tf32; wgrad = dact planes as MN-major A, im2col rows as two bf16
+ * terms (hi + lo) + a ones column for the bias gradient. */
+int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out_planes, int cin,
+                      int cout, int batch, int batch_cap, int H, int W, void* stream);
+size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout);
+int ddpb_conv1_wgrad_tc(const void* dact_planes, const float* x, float* dw_db, float* scratch,
+                        int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+/* out[i] = sum_p part[p*n + i], fixed order. */
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
+
 /* Same result as ddpb_conv1_wgrad, for callers that cannot pass scratch because they cannot
  * allocate device memory (a host that gave all of it to its own pool, or a plug-in barred from
  * cudaMalloc/cudaFree because those stall every stream on the device).  The partial sums live in
@@ -90,7 +101,8 @@ size_t ddpb_linear_fwd_scratch_bytes(int nout, int C, int batch_cap, int H, int 
 int ddpb_linear_fwd(const void* act_planes, const float* W_fl, float* partial, int* S_out,
                     int nout, int C, int batch, int batch_cap, int H, int W, void* stream);
 /* loss = mean CE; dlogits = (softmax - onehot)/batch; dbias = column sums of dlogits;
- * logits may be NULL.  reference train_ddp.py:40,198-199. */
+ * logits [batch][nout] is required (it is also the kernel's staging buffer).
+ * Calls on one device must not overlap.  reference train_ddp.py:40,198-199. */
 int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels_i64,
                       float* logits, float* dlogits, float* dbias, float* loss, int nout,
                       int batch, void* stream);

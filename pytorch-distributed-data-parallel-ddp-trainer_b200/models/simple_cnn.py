@@ -160,7 +160,7 @@ class SimpleCNNB200(_ModelBase):
             self.loss = torch.zeros(1, device=dev)
             self.scr_lin = nat.scratch(nat.linear_bwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
             self.scr_w2 = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(C1, C2), dev)
-            self.scr_w1 = nat.scratch(nat.conv1_wgrad_scratch_bytes(1, C1, batch_cap, H, W), dev)
+            self.scr_w1 = nat.scratch(nat.conv1_wgrad_tc_scratch_bytes(1, C1), dev)
             self.lr_dev = torch.full((1,), 0.01, device=dev)
         a = self.arena
         self.w1, self.b1 = a.view("net.0.weight"), a.view("net.0.bias")
@@ -185,7 +185,7 @@ class SimpleCNNB200(_ModelBase):
         b = int(batch if batch is not None else x.shape[0])
         assert 0 < b <= self.batch_cap
         cap, H, W = self.batch_cap, IMG_H, IMG_W
-        nat.conv1_fwd(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
+        nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W, stream)
         S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, gs["bf"],
@@ -209,7 +209,7 @@ class SimpleCNNB200(_ModelBase):
         nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
         gs = self.grad_sets[parity]
         nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
-        nat.conv1_wgrad(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
+        nat.conv1_wgrad_tc(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
 
     def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""
@@ -250,7 +250,7 @@ class SimpleCNNB200(_ModelBase):
         cap, H, W = self.batch_cap, IMG_H, IMG_W
         y = torch.zeros(b, dtype=torch.int64, device=self.device)
         scratch_db = torch.empty(NCLS, device=self.device)
-        nat.conv1_fwd(x, self.w1, self.b1, self.act1, b, cap, H, W)
+        nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W)
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W)
         S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, scratch_db,

@@ -33,6 +33,9 @@ _SIGNATURES = {
     "ddpb_conv1_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv1_wgrad_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_conv1_wgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_fwd_tc": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_tc_scratch_bytes": (c_size_t, [I, I]),
+    "ddpb_conv1_wgrad_tc": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_wgrad_scratch_bytes": (c_size_t, [I, I]),
@@ -139,6 +142,20 @@ def conv1_wgrad_scratch_bytes(cin, cout, batch_cap, H, W) -> int:
 def conv1_wgrad(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
     check(lib().ddpb_conv1_wgrad(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
                                  batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad")
+
+
+def conv1_fwd_tc(x, w, b, out, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv1_fwd_tc(ptr(x), ptr(w), ptr(b), ptr(out), w.shape[1], w.shape[0], batch,
+                                  batch_cap, H, W, stream_ptr(stream)), "conv1_fwd_tc")
+
+
+def conv1_wgrad_tc_scratch_bytes(cin, cout) -> int:
+    return int(lib().ddpb_conv1_wgrad_tc_scratch_bytes(cin, cout))
+
+
+def conv1_wgrad_tc(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv1_wgrad_tc(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
+                                    batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad_tc")
 
 
 def conv3x3_fwd(inp, w, bias, out, batch, batch_cap, H, W, stream=None):

@@ -1,0 +1,118 @@
+"""Generic bucketed data-parallel wrapper for any CUDA nn.Module, built on the symmetric-memory
+communicator: what DDP's Reducer + NCCL + torch.optim.SGD do (reference train_ddp.py:34,199,200),
+with per-bucket fused all-reduce + 1/W + SGD kernels launched from gradient-ready hooks on a side
+stream, so communication AND the optimizer overlap the rest of backward.
+
+Parameters are re-homed into the peer-mapped arena (so the two-shot kernel can push updated
+slices into every rank), gradients accumulate straight into one of two arena copies (step
+parity, see csrc/comm.cu), buckets are contiguous slices in reverse registration order
+(gradient-ready order), capped by ``bucket_mb``.
+"""
+from __future__ import annotations
+
+import torch
+
+from .comm import ALGO_AUTO, SymmetricComm
+
+
+def _align(n: int, a: int) -> int:
+    return (n + a - 1) // a * a
+
+
+class BucketedDataParallel:
+    def __init__(self, module: torch.nn.Module, rank: int, world_size: int, lr: float = 0.01,
+                 bucket_mb: float = 25.0, algo: int = ALGO_AUTO):
+        self.module, self.rank, self.world_size, self.lr, self.algo = module, rank, world_size, lr, algo
+        params = [p for p in module.parameters() if p.requires_grad]
+        self.device = params[0].device
+        # arena order = reverse registration order, so buckets fill front to back during backward
+        order = list(reversed(params))
+        offs, off = [], 0
+        for p in order:
+            off = _align(off, 4)
+            offs.append(off)
+            off += p.numel()
+        n = _align(off, 4)
+        self.numel = n
+        region = _align(n * 4, 256)
+        self.param_off, self.grad_off = 0, [region, 2 * region]
+        self.comm = SymmetricComm(rank, world_size, 3 * region)
+        self.flat_params = self.comm.tensor(0, n)
+        self.flat_grads = [self.comm.tensor(o, n) for o in self.grad_off]
+        self.flat_params.zero_()
+        for g in self.flat_grads:
+            g.zero_()
+        self._views = []
+        with torch.no_grad():
+            for p, o in zip(order, offs):
+                v = self.flat_params[o:o + p.numel()].view(p.shape)
+                v.copy_(p.data)
+                p.data = v
+                self._views.append((p, o))
+        # buckets: contiguous [start, end) float ranges, multiples of 4 floats
+        cap = int(bucket_mb * (1 << 20) / 4)
+        self.buckets, start, members = [], 0, []
+        for i, (p, o) in enumerate(self._views):
+            members.append(i)
+            end = _align(o + p.numel(), 4)
+            if end - start >= cap or i == len(self._views) - 1:
+                self.buckets.append({"start": start, "n": end - start, "members": members, "pending": 0})
+                start, members = end, []
+        self._bucket_of = {}
+        for b_i, b in enumerate(self.buckets):
+            for m in b["members"]:
+                self._bucket_of[m] = b_i
+        self.lr_dev = torch.full((1,), lr, device=self.device)
+        self.side = torch.cuda.Stream(self.device)
+        self._ready = [torch.cuda.Event() for _ in self.buckets]
+        self._done = torch.cuda.Event()
+        self.step_count = 0
+        self._parity = 0
+        for i, (p, _) in enumerate(self._views):
+            p.register_post_accumulate_grad_hook(self._make_hook(i))
+        self.sync_params()
+
+    def sync_params(self, src: int = 0) -> None:
+        torch.cuda.synchronize(self.device)
+        if self.world_size > 1:
+            self.comm.broadcast(self.param_off, self.numel * 4, root=src, slot=7)
+            torch.cuda.synchronize(self.device)
+
+    def _make_hook(self, idx: int):
+        def hook(_param):
+            b_i = self._bucket_of[idx]
+            b = self.buckets[b_i]
+            b["pending"] -= 1
+            if b["pending"] == 0:
+                self._launch_bucket(b_i)
+        return hook
+
+    def _launch_bucket(self, b_i: int) -> None:
+        b = self.buckets[b_i]
+        cur = torch.cuda.current_stream(self.device)
+        self._ready[b_i].record(cur)
+        self.side.wait_event(self._ready[b_i])
+        goff = self.grad_off[self._parity]
+        self.comm.allreduce_sgd(goff + b["start"] * 4, self.param_off + b["start"] * 4, b["n"],
+                                self.lr_dev, self.algo, slot=b_i % 6, stream=self.side)
+
+    def step(self, x: torch.Tensor, y: torch.Tensor, loss_fn) -> torch.Tensor:
+        """forward + backward (+ per-bucket fused all-reduce/SGD from the grad hooks)."""
+        self._parity = self.step_count & 1
+        g = self.flat_grads[self._parity]
+        g.zero_()
+        for p, o in self._views:  # gradients accumulate in place into this step's arena copy
+            p.grad = g[o:o + p.numel()].view(p.shape)
+        for b in self.buckets:
+            b["pending"] = len(b["members"])
+        loss = loss_fn(self.module(x), y)
+        loss.backward()
+        cur = torch.cuda.current_stream(self.device)
+        self._done.record(self.side)
+        cur.wait_event(self._done)  # parameters are final before the next forward
+        self.step_count += 1
+        return loss.detach()
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        self.comm.close()

@@ -58,6 +58,38 @@ def test_conv1_fwd(nat, batch, cap):
     assert _lay().border_rows_are_zero(out, batch, H, W)
 
 
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (5, 16), (300, 300)])
+def test_conv1_fwd_tcgen05_tf32(nat, batch, cap):
+    torch.manual_seed(10)
+    x = torch.rand(batch, 1, H, W, device="cuda")
+    w = torch.randn(32, 1, 3, 3, device="cuda") * 0.3
+    b = torch.randn(32, device="cuda") * 0.1
+    out = nat.alloc_planes(32, cap, H, W)
+    nat.conv1_fwd_tc(x, w, b, out, batch, cap, H, W)
+    torch.cuda.synchronize()
+    got = _lay().planes_to_nchw(out, batch, 32, H, W)
+    want = F.relu(F.conv2d(x, w, b, padding=1))
+    _report("conv1_fwd_tc", got, want, 1e-2, 1e-2)   # tf32 operands + bf16 stored result
+    assert _lay().border_rows_are_zero(out, batch, H, W)
+
+
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (300, 300)])
+def test_conv1_wgrad_tcgen05(nat, batch, cap):
+    torch.manual_seed(11)
+    x = torch.rand(batch, 1, H, W, device="cuda")
+    dact = torch.randn(batch, 32, H, W, device="cuda") * 0.1
+    dact_p = _lay().nchw_to_planes(dact, cap)
+    out = torch.zeros(32 * 9 + 32, device="cuda")
+    scr = nat.scratch(nat.conv1_wgrad_tc_scratch_bytes(1, 32))
+    nat.conv1_wgrad_tc(dact_p, x, out, scr, 1, 32, batch, cap, H, W)
+    torch.cuda.synchronize()
+    wref = torch.zeros(32, 1, 3, 3, device="cuda", requires_grad=True)
+    bref = torch.zeros(32, device="cuda", requires_grad=True)
+    F.conv2d(x, wref, bref, padding=1).backward(_bf(dact))
+    _report("conv1_wgrad_tc dW", out[:288].view(32, 1, 3, 3), wref.grad, 1e-3 * wref.grad.abs().max().item(), 1e-4)
+    _report("conv1_wgrad_tc db", out[288:], bref.grad, 1e-3 * bref.grad.abs().max().item(), 1e-4)
+
+
 @pytest.mark.parametrize("batch,cap", [(2, 2), (64, 64), (37, 64), (300, 300)])
 def test_conv3x3_fwd_tcgen05(nat, batch, cap):
     torch.manual_seed(1)

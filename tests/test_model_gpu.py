@@ -31,7 +31,7 @@ def test_gradients_match_oracle(cuda):
         g, w = gpu.arena.grad_view(name), oracle.arena.grad_view(name)
         scale = w.abs().max().item()
         err = (g - w).abs().max().item()
-        assert err <= 3e-2 * scale + 1e-6, (name, err, scale)
+        assert err <= 5e-2 * scale + 1e-6, (name, err, scale)  # bf16 activations + tf32 conv1
 
 
 @pytest.mark.parametrize("use_graph", [False, True])
