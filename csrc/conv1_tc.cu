@@ -154,28 +154,29 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
       mbar_arrive(bar_full + stage * 8);
     }
   } else if (warp == 4) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_tf32(kTileM, CO);
-      int it = 0;
-      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
-        const int stage = it % kC1Stages;
-        const uint32_t phase = (it / kC1Stages) & 1;
-        const int acc = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
-        mbar_wait(bar_full + stage * 8, phase);
-        tc_fence_after();
-        const uint32_t a_stage = s_a + stage * S::a_stage;
+    constexpr uint32_t idesc = umma_idesc_tf32(kTileM, CO);
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % kC1Stages;
+      const uint32_t phase = (it / kC1Stages) & 1;
+      const int acc = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
+      mbar_wait(bar_full + stage * 8, phase);
+      tc_fence_after();
+      const uint32_t a_stage = s_a + stage * S::a_stage;
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
-          umma_tf32(tmem_base + acc * CO,
-                    umma_smem_desc(a_stage + kk * 2 * S::a_plane, S::a_plane, 128),
-                    umma_smem_desc(s_base + kk * 2 * 512, 512, 128), idesc, kk != 0);
+      for (int kk = 0; kk < 2; ++kk) {
+        const uint64_t adesc = umma_smem_desc(a_stage + kk * 2 * S::a_plane, S::a_plane, 128);
+        const uint64_t bdesc = umma_smem_desc(s_base + kk * 2 * 512, 512, 128);
+        if (elect_one()) umma_tf32(tmem_base + acc * CO, adesc, bdesc, idesc, kk != 0);
+      }
+      if (elect_one()) {
         umma_commit(bar_empty + stage * 8);
         umma_commit(bar_tfull + acc * 8);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else {
     const int q = warp & 3;
     int it = 0;
@@ -324,25 +325,26 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       mbar_arrive(bar_fb + stage * 8);
     }
   } else if (warp == 4) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(64, 32, 1, 1);
-      int it = 0;
-      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
-        const int stage = it % kC1Stages;
-        const uint32_t phase = (it / kC1Stages) & 1;
-        mbar_wait(bar_fa + stage * 8, phase);
-        mbar_wait(bar_fb + stage * 8, phase);
-        tc_fence_after();
-        const uint32_t sa = s_base + stage * S::stage;
-        const uint32_t sb = sa + S::a_bytes;
+    constexpr uint32_t idesc = umma_idesc_bf16(64, 32, 1, 1);
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % kC1Stages;
+      const uint32_t phase = (it / kC1Stages) & 1;
+      mbar_wait(bar_fa + stage * 8, phase);
+      mbar_wait(bar_fb + stage * 8, phase);
+      tc_fence_after();
+      const uint32_t sa = s_base + stage * S::stage;
+      const uint32_t sb = sa + S::a_bytes;
 #pragma unroll
-        for (int ks = 0; ks < kTileM / 16; ++ks)
-          umma_bf16(tmem_base, umma_smem_desc(sa + ks * 256, 128, S::a_plane),
-                    umma_smem_desc(sb + ks * 256, 128, S::a_plane), idesc, (it | ks) != 0);
-        umma_commit(bar_empty + stage * 8);
+      for (int ks = 0; ks < kTileM / 16; ++ks) {
+        const uint64_t adesc = umma_smem_desc(sa + ks * 256, 128, S::a_plane);
+        const uint64_t bdesc = umma_smem_desc(sb + ks * 256, 128, S::a_plane);
+        if (elect_one()) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
       }
-      umma_commit(bar_done);
+      if (elect_one()) umma_commit(bar_empty + stage * 8);
+      __syncwarp();
     }
+    if (elect_one()) umma_commit(bar_done);
     __syncwarp();
   } else {
     const int q = warp & 3;

@@ -9,7 +9,9 @@
 // Warp roles (192 threads, one CTA per SM, persistent over tiles):
 //   warp 0    bulk-copy producer (one lane)
 //   warp 1    TMEM allocator + MMA issuer (one lane issues tcgen05.mma)
-//   warps 2-5 epilogue: tcgen05.ld the accumulator tile, fuse bias/ReLU/mask, store bf16 planes
+//   warps 2-9 epilogue: tcgen05.ld the accumulator tile, fuse bias/ReLU/mask, store bf16 planes
+//             (two warps per TMEM lane quadrant, each takes half of the columns: the epilogue,
+//             not the MMA, was the per-tile bottleneck with four warps — profiles/)
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
@@ -17,24 +19,28 @@
 
 namespace ddpb {
 
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 320;   // fwd / dgrad: 1 producer + 1 MMA + 8 epilogue warps
+constexpr int kWgradThreads = 192;  // wgrad: 1 producer + 1 MMA + 4 epilogue warps
 constexpr uint32_t kRowBytes = 16;
 constexpr uint32_t kStagePlaneBytes = kStageRows * kRowBytes;  // 3072
 
 template <int CI, int CO, int STAGES>
 struct ConvSmem {
   static constexpr uint32_t KP = CI / 8;
-  static constexpr uint32_t w_tap_bytes = KP * CO * 16;
-  static constexpr uint32_t w_bytes = 9 * w_tap_bytes;
+  // B tile of one tap: [KP k-chunks][CO rows][16 B]; the k-chunk stride (UMMA LBO) is skewed by
+  // 16 B so that the fp32->bf16 conversion below writes shared memory without bank conflicts.
+  static constexpr uint32_t w_lbo = CO * 16 + 16;
+  static constexpr uint32_t w_tap_bytes = KP * w_lbo;
+  static constexpr uint32_t w_bytes = (9 * w_tap_bytes + 127) / 128 * 128;
   static constexpr uint32_t a_stage_bytes = KP * kStagePlaneBytes;
   static constexpr uint32_t off_a = w_bytes;
-  // fp32 master weights are bulk-copied (TMA) into a staging area and converted from there.
-  // It aliases the A-stage ring when that is large enough (the ring is idle during setup).
+  // fp32 master weights are bulk-copied (TMA, one copy) into a staging area and converted from
+  // there.  It aliases the A-stage ring when that is large enough (the ring is idle during setup).
   static constexpr uint32_t wstage_bytes = 9 * CI * CO * 4;
-  static constexpr bool stage_aliases_ring = STAGES * a_stage_bytes >= wstage_bytes;
-  static constexpr uint32_t off_wstage = stage_aliases_ring ? off_a : off_a + STAGES * a_stage_bytes;
-  static constexpr uint32_t off_bias =
-      off_a + STAGES * a_stage_bytes + (stage_aliases_ring ? 0 : wstage_bytes);
+  static constexpr uint32_t ring_bytes = STAGES * a_stage_bytes;
+  static constexpr bool stage_aliases_ring = ring_bytes >= wstage_bytes;
+  static constexpr uint32_t off_wstage = stage_aliases_ring ? off_a : off_a + ring_bytes;
+  static constexpr uint32_t off_bias = off_a + ring_bytes + (stage_aliases_ring ? 0 : wstage_bytes);
   static constexpr uint32_t off_bar = off_bias + CO * 4;
   static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 5) * 8;
   static constexpr uint32_t total = off_tmem + 16;
@@ -84,7 +90,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_tfull + i * 8, 1);
-      mbar_init(bar_tempty + i * 8, 128);
+      mbar_init(bar_tempty + i * 8, 256);
     }
     mbar_init(bar_w, 1);
     fence_mbar_init();
@@ -102,28 +108,46 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
   mbar_wait(bar_w, 0);
   if (tid == 0) prof_stamp(prof, 1);
   // ---- staged fp32 weights -> bf16 UMMA canonical (K-major, no swizzle) B tiles.
-  // B operand of tap t: rows n (GEMM N), 8-element K chunks; 32-bit word index
-  //   ((t*KP + k/8)*CO + n)*4 + (k%8)/2        => LBO = CO*16 B, SBO = 128 B
+  // B operand of tap t: rows n (GEMM N), 8-element K chunks; byte offset
+  //   t*w_tap + (k/8)*w_lbo + n*16 + (k%8)*2          => LBO = w_lbo, SBO = 128
+  // Thread->element maps are chosen so that both the staged reads and the tile writes of a warp
+  // fall into 32 different banks.
   {
     const float* ws = reinterpret_cast<const float*>(smem + S::off_wstage);
-    uint32_t* wd = reinterpret_cast<uint32_t*>(smem);
-#pragma unroll 8
-    for (int widx = tid; widx < 9 * CI * CO / 2; widx += kConvThreads) {
-      const int j = widx & 3;
-      const int n = (widx >> 2) % CO;
-      const int rest = (widx >> 2) / CO;
-      const int kc = rest % KP;
-      const int tap = rest / KP;
-      const int k = kc * 8 + j * 2;
-      float lo, hi;
-      if (MODE == 0) {  // w[n = co][k = ci][tap]
-        lo = ws[(n * CI + k) * 9 + tap];
-        hi = ws[(n * CI + k + 1) * 9 + tap];
-      } else {  // w[k = layer out ch][n = layer in ch][8 - tap]   (taps mirrored)
-        lo = ws[(k * CO + n) * 9 + (8 - tap)];
-        hi = ws[((k + 1) * CO + n) * 9 + (8 - tap)];
+    if (MODE == 0) {
+      // source w[n][k][tap] (tap fastest, then k): a warp covers 16 k-pairs x 2 taps of one n
+      constexpr int kPairs = CI / 2;
+      constexpr int total = CO * 5 * kPairs * 2;  // taps handled in pairs (0,1)..(8,9): 9 is a dummy
+      for (int idx = tid; idx < total; idx += kConvThreads) {
+        const int tl = idx & 1;
+        const int kp = (idx >> 1) % kPairs;
+        const int rest = (idx >> 1) / kPairs;
+        const int tp = rest % 5;
+        const int n = rest / 5;
+        const int tap = tp * 2 + tl;
+        if (tap >= 9) continue;
+        const int k = kp * 2;
+        const float lo = ws[(n * CI + k) * 9 + tap];
+        const float hi = ws[(n * CI + k + 1) * 9 + tap];
+        *reinterpret_cast<uint32_t*>(smem + tap * S::w_tap_bytes + (k >> 3) * S::w_lbo + n * 16 +
+                                     (k & 7) * 2) = pack_bf16x2(lo, hi);
       }
-      wd[widx] = pack_bf16x2(lo, hi);
+    } else {
+      // source w[k = layer out][n = layer in][8 - tap] (taps mirrored): a warp covers 32 n of one
+      // (tap, k-chunk) and each thread writes a whole 16-byte row (8 k values)
+      constexpr int total = 9 * KP * CO;
+      for (int idx = tid; idx < total; idx += kConvThreads) {
+        const int n = idx % CO;
+        const int rest = idx / CO;
+        const int kc = rest % KP;
+        const int tap = rest / KP;
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = ws[((kc * 8 + i) * CO + n) * 9 + (8 - tap)];
+        *reinterpret_cast<uint4*>(smem + tap * S::w_tap_bytes + kc * S::w_lbo + n * 16) =
+            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                       pack_bf16x2(v[6], v[7]));
+      }
     }
   }
   fence_proxy_async_smem();
@@ -155,88 +179,102 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(kTileM, CO, 0, 0);
-      int it = 0;
-      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        const int acc = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
-        mbar_wait(bar_full + stage * 8, phase);
-        tc_fence_after();
-        if (it == 0) prof_stamp(prof, 4);
-        const uint32_t a_stage = s_a + stage * S::a_stage_bytes;
-        const uint32_t d_tmem = tmem_base + acc * CO;
+    // MMA issuer: the whole warp stays converged, one elected lane issues (see elect_one()).
+    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, CO, 0, 0);
+    uint32_t tap_off[9];
 #pragma unroll
-        for (int tap = 0; tap < 9; ++tap) {
-          const int d = (tap / 3 - 1) * g.PW + (tap % 3 - 1);
-          const uint32_t a_tap = a_stage + (kHalo + d) * kRowBytes;
-          const uint32_t b_tap = s_w + tap * S::w_tap_bytes;
+    for (int tap = 0; tap < 9; ++tap)
+      tap_off[tap] = (kHalo + (tap / 3 - 1) * g.PW + (tap % 3 - 1)) * kRowBytes;
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % STAGES;
+      const uint32_t phase = (it / STAGES) & 1;
+      const int acc = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(bar_tempty + acc * 8, aphase ^ 1);
+      mbar_wait(bar_full + stage * 8, phase);
+      tc_fence_after();
+      if (it == 0 && lane == 0) prof_stamp(prof, 4);
+      const uint32_t a_stage = s_a + stage * S::a_stage_bytes;
+      const uint32_t d_tmem = tmem_base + acc * CO;
 #pragma unroll
-          for (int kk = 0; kk < CI / 16; ++kk) {
-            const uint64_t adesc =
-                umma_smem_desc(a_tap + kk * 2 * kStagePlaneBytes, kStagePlaneBytes, 128);
-            const uint64_t bdesc = umma_smem_desc(b_tap + kk * 2 * (CO * 16), CO * 16, 128);
-            umma_bf16(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
-          }
+      for (int tap = 0; tap < 9; ++tap) {
+#pragma unroll
+        for (int kk = 0; kk < CI / 16; ++kk) {
+          const uint64_t adesc = umma_smem_desc(a_stage + tap_off[tap] + kk * 2 * kStagePlaneBytes,
+                                                kStagePlaneBytes, 128);
+          const uint64_t bdesc =
+              umma_smem_desc(s_w + tap * S::w_tap_bytes + kk * 2 * S::w_lbo, S::w_lbo, 128);
+          if (elect_one()) umma_bf16(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
         }
+      }
+      if (elect_one()) {
         umma_commit(bar_empty + stage * 8);
         umma_commit(bar_tfull + acc * 8);
       }
-      prof_stamp(prof, 5);
+      __syncwarp();
     }
-    __syncwarp();
+    if (lane == 0) prof_stamp(prof, 5);
   } else {
-    const int q = warp & 3;  // TMEM lane quadrant this warp may read
+    const int q = warp & 3;            // TMEM lane quadrant this warp may read
+    const int half = (warp - 2) >> 2;  // which half of the CO columns this warp handles
+    constexpr int COLS = CO / 2;       // 32 (fwd) or 16 (dgrad)
+    const int c0 = half * COLS;
     int it = 0;
     for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
       const int acc = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(bar_tfull + acc * 8, aphase);
-      tc_fence_after();
-      if (it == 0 && tid == 64) prof_stamp(prof, 6);
       const int rel = t * kTileM + q * 32 + lane;
       int img, h, wc;
       const bool valid = decode_row(g, rel, img, h, wc);
       const long long row = (long long)kGuard + rel;
+      uint4 mk[COLS / 8];
+      if (MODE == 1) {  // issue the ReLU-mask loads before blocking on the accumulator
 #pragma unroll
-      for (int c0 = 0; c0 < CO; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * CO + c0, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const long long off = ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8;
-          uint4 o;
-          uint32_t* op = reinterpret_cast<uint32_t*>(&o);
-          if (MODE == 0) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              float x0 = __uint_as_float(v[j * 8 + 2 * e]) + s_bias[c0 + j * 8 + 2 * e];
-              float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + s_bias[c0 + j * 8 + 2 * e + 1];
-              x0 = valid ? fmaxf(x0, 0.f) : 0.f;
-              x1 = valid ? fmaxf(x1, 0.f) : 0.f;
-              op[e] = pack_bf16x2(x0, x1);
-            }
-          } else {
-            const uint4 mk = *reinterpret_cast<const uint4*>(mask + off);
-            const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              float x0 = __uint_as_float(v[j * 8 + 2 * e]);
-              float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
-              x0 = (valid && bf16_lo(mp[e]) > 0.f) ? x0 : 0.f;
-              x1 = (valid && bf16_hi(mp[e]) > 0.f) ? x1 : 0.f;
-              op[e] = pack_bf16x2(x0, x1);
-            }
-          }
-          *reinterpret_cast<uint4*>(out + off) = o;
-        }
+        for (int j = 0; j < COLS / 8; ++j)
+          mk[j] = *reinterpret_cast<const uint4*>(
+              mask + ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8);
       }
+      mbar_wait(bar_tfull + acc * 8, aphase);
+      tc_fence_after();
+      if (it == 0 && tid == 64) prof_stamp(prof, 6);
+      uint32_t v[COLS];
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * CO + c0;
+      if constexpr (COLS == 32) tmem_ld32(taddr, v);
+      else tmem_ld16(taddr, v);
+      tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(bar_tempty + acc * 8);
+      mbar_arrive(bar_tempty + acc * 8);  // accumulator is in registers: release it early
+#pragma unroll
+      for (int j = 0; j < COLS / 8; ++j) {
+        const long long off = ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8;
+        uint4 o;
+        uint32_t* op = reinterpret_cast<uint32_t*>(&o);
+        if (MODE == 0) {
+          const float4 b0 = *reinterpret_cast<const float4*>(s_bias + c0 + j * 8);
+          const float4 b1 = *reinterpret_cast<const float4*>(s_bias + c0 + j * 8 + 4);
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x0 = __uint_as_float(v[j * 8 + 2 * e]) + bb[2 * e];
+            float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + bb[2 * e + 1];
+            x0 = valid ? fmaxf(x0, 0.f) : 0.f;
+            x1 = valid ? fmaxf(x1, 0.f) : 0.f;
+            op[e] = pack_bf16x2(x0, x1);
+          }
+        } else {
+          const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk[j]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x0 = __uint_as_float(v[j * 8 + 2 * e]);
+            float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
+            x0 = (valid && bf16_lo(mp[e]) > 0.f) ? x0 : 0.f;
+            x1 = (valid && bf16_hi(mp[e]) > 0.f) ? x1 : 0.f;
+            op[e] = pack_bf16x2(x0, x1);
+          }
+        }
+        *reinterpret_cast<uint4*>(out + off) = o;
+      }
     }
     if (tid == 64) prof_stamp(prof, 7);
   }
@@ -277,7 +315,7 @@ struct WgradSmem {
 };
 
 template <int CI, int CO, int STAGES>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(kWgradThreads, 1)
 conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ in,
                         float* __restrict__ partial, Geom g, unsigned long long* prof) {
   using S = WgradSmem<CI, CO, STAGES>;
@@ -302,7 +340,7 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
   for (int st = 0; st < STAGES; ++st) {
     uint32_t* ones = reinterpret_cast<uint32_t*>(smem + st * S::stage_bytes + S::a_bytes +
                                                  3 * S::BP * kStagePlaneBytes);
-    for (int i = tid; i < (int)kStagePlaneBytes / 4; i += kConvThreads) ones[i] = 0x3f803f80u;
+    for (int i = tid; i < (int)kStagePlaneBytes / 4; i += kWgradThreads) ones[i] = 0x3f803f80u;
   }
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) {
@@ -350,35 +388,37 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc0 = umma_idesc_bf16(CO, S::n0, 1, 1);
-      constexpr uint32_t idesc1 = umma_idesc_bf16(CO, S::n1, 1, 1);
-      int it = 0;
-      for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
-        const int stage = it % STAGES;
-        const uint32_t phase = (it / STAGES) & 1;
-        mbar_wait(bar_full + stage * 8, phase);
-        tc_fence_after();
-        if (it == 0) prof_stamp(prof, 4);
-        const uint32_t sa = s_base + stage * S::stage_bytes;
-        const uint32_t sb = sa + S::a_bytes;
+    constexpr uint32_t idesc0 = umma_idesc_bf16(CO, S::n0, 1, 1);
+    constexpr uint32_t idesc1 = umma_idesc_bf16(CO, S::n1, 1, 1);
+    uint32_t row_off[3];
 #pragma unroll
-        for (int ks = 0; ks < kTileM / 16; ++ks) {
-          const uint32_t accum = (it | ks) != 0;
-          const uint64_t adesc = umma_smem_desc(sa + ks * 16 * kRowBytes, 128, S::a_plane);
+    for (int r = 0; r < 3; ++r) row_off[r] = (kHalo + (r - 1) * g.PW) * kRowBytes;
+    int it = 0;
+    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+      const int stage = it % STAGES;
+      const uint32_t phase = (it / STAGES) & 1;
+      mbar_wait(bar_full + stage * 8, phase);
+      tc_fence_after();
+      if (it == 0 && lane == 0) prof_stamp(prof, 4);
+      const uint32_t sa = s_base + stage * S::stage_bytes;
+      const uint32_t sb = sa + S::a_bytes;
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {  // vertical tap r: start row shifted by (r-1)*PW
-            const uint64_t bdesc = umma_smem_desc(
-                sb + (kHalo + (r - 1) * g.PW + ks * 16) * kRowBytes, 128, kStagePlaneBytes);
-            umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
-          }
+      for (int ks = 0; ks < kTileM / 16; ++ks) {
+        const uint32_t accum = (it | ks) != 0;
+        const uint64_t adesc = umma_smem_desc(sa + ks * 16 * kRowBytes, 128, S::a_plane);
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {  // vertical tap r: start row shifted by (r-1)*PW
+          const uint64_t bdesc =
+              umma_smem_desc(sb + row_off[r] + ks * 16 * kRowBytes, 128, kStagePlaneBytes);
+          if (elect_one()) umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
         }
-        umma_commit(bar_empty + stage * 8);
       }
-      umma_commit(bar_done);
-      prof_stamp(prof, 5);
+      if (elect_one()) umma_commit(bar_empty + stage * 8);
+      __syncwarp();
     }
+    if (elect_one()) umma_commit(bar_done);
     __syncwarp();
+    if (lane == 0) prof_stamp(prof, 5);
   } else {
     const int q = warp & 3;
     mbar_wait(bar_done, 0);
@@ -555,7 +595,7 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
   }
   const int sms = ddpb_num_sms();
   const int grid = g.ntiles < sms ? g.ntiles : sms;
-  DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kConvThreads), S::total, st,
+  DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
                         static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(in),
                         scratch, g, g_prof));
   const int n = CO * (9 * CI + 8);

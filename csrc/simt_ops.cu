@@ -19,13 +19,13 @@
 
 namespace ddpb {
 
+int g_pdl = -1;  // -1: take the default from the environment (DDPB_PDL, default on)
 int pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
+  if (g_pdl < 0) {
     const char* e = getenv("DDPB_PDL");
-    v = (e && e[0] == '1') ? 1 : 0;
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
   }
-  return v;
+  return g_pdl;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -388,87 +388,97 @@ linear_fwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 // z = bias + sum_s partial[s]; loss = mean_i(logsumexp(z_i) - z_i[y_i]);
 // dlogits = (softmax(z) - onehot(y)) / batch; db[j] = sum_i dlogits[i][j].
 // Single block: the work is batch*NOUT*S floats.
-// Multi-block: block b handles images [32b, 32b+32).  Block sums of the loss and of dbias go to
-// a small library-resident array; the block that finishes last (ticket counter) adds them up in
-// block order, so the result is deterministic.  The ticket resets itself; calls on one device must
-// not overlap (the step engine issues one at a time).
-constexpr int kXentImgsPerBlock = 32;  // x NOUT classes = one (image, class) pair per thread
-constexpr int kXentMaxBlocks = 2048;   // batches up to 65536
+// Multi-block: block b handles kXentImgs images.  Phase 1 spreads the sum over the S feature-slice
+// partials across kXentSG thread groups (the tensor-core linear forward produces up to one slice per
+// SM).  Block sums of the loss and of dbias go to a small library-resident array; the block that
+// finishes last (ticket counter) adds them up in a fixed order, so the result is deterministic.
+// The ticket resets itself; calls on one device must not overlap (the step engine issues one at
+// a time).
+constexpr int kXentImgs = 8;
+constexpr int kXentSG = 8;
+constexpr int kXentMaxBlocks = 8192;  // batches up to 65536
 static __device__ float g_xent_block_sums[kXentMaxBlocks * 12];
 static __device__ unsigned int g_xent_ticket;
 
 template <int NOUT>
-__global__ void __launch_bounds__(kXentImgsPerBlock * NOUT)
+__global__ void __launch_bounds__(kXentImgs * NOUT * kXentSG)
 softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
                     const long long* __restrict__ labels, float* __restrict__ logits,
                     float* __restrict__ dlogits, float* __restrict__ dbias,
                     float* __restrict__ loss, int batch) {
-  pdl_sync();
   static_assert(NOUT + 1 <= 12, "block-sum row too small");
-  __shared__ float red[(kXentImgsPerBlock * NOUT + 31) / 32][NOUT + 1];
+  constexpr int NP = kXentImgs * NOUT;  // (image, class) pairs per block
+  __shared__ float sums[kXentSG][NP];
+  __shared__ float red[NOUT + 1][kXentImgs];
   __shared__ bool is_last;
-  const int img0 = blockIdx.x * kXentImgsPerBlock;
-  const int nimg = min(kXentImgsPerBlock, batch - img0);
-  // phase 1: every (image, class) pair in parallel: z = bias + sum of the feature-slice partials
+  pdl_sync();
+  const int img0 = blockIdx.x * kXentImgs;
+  const int nimg = min(kXentImgs, batch - img0);
   const long long npair_all = (long long)batch * NOUT;
-  for (int t = threadIdx.x; t < nimg * NOUT; t += blockDim.x) {
-    const long long gt = (long long)img0 * NOUT + t;
-    float z = bias[t % NOUT];
-    int sidx = 0;
-    for (; sidx + 8 <= S; sidx += 8) {
-      float v[8];
+  // phase 1: thread (pair, sg) adds partial slices sg, sg+SG, ...
+  {
+    const int pair = threadIdx.x % NP, sg = threadIdx.x / NP;
+    float z = 0.f;
+    if (pair < nimg * NOUT) {
+      const long long gt = (long long)img0 * NOUT + pair;
+      int sidx = sg;
+      for (; sidx + 3 * kXentSG < S; sidx += 4 * kXentSG) {
+        float v[4];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = partial[(long long)(sidx + u) * npair_all + gt];
+        for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sidx + u * kXentSG) * npair_all + gt];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) z += v[u];
+        for (int u = 0; u < 4; ++u) z += v[u];
+      }
+      for (; sidx < S; sidx += kXentSG) z += partial[(long long)sidx * npair_all + gt];
     }
-    for (; sidx < S; ++sidx) z += partial[(long long)sidx * npair_all + gt];
-    logits[gt] = z;
+    sums[sg][pair] = z;
   }
   __syncthreads();
-  // phase 2: per-image log-softmax, loss and gradient
-  float lsum = 0.f;
-  float dbl[NOUT];
+  if (threadIdx.x < nimg * NOUT) {
+    float z = bias[threadIdx.x % NOUT];
 #pragma unroll
-  for (int j = 0; j < NOUT; ++j) dbl[j] = 0.f;
-  const float inv = 1.0f / static_cast<float>(batch);
-  for (int li = threadIdx.x; li < nimg; li += blockDim.x) {
-    const long long i = img0 + li;
-    float z[NOUT];
+    for (int u = 0; u < kXentSG; ++u) z += sums[u][threadIdx.x];
+    sums[0][threadIdx.x] = z;
+    logits[(long long)img0 * NOUT + threadIdx.x] = z;
+  }
+  __syncthreads();
+  // phase 2: one thread per image: log-softmax, loss and gradient
+  if (threadIdx.x < kXentImgs) {
+    const int li = threadIdx.x;
+    float lsum = 0.f, d[NOUT];
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) z[j] = logits[i * NOUT + j];
-    float m = z[0];
+    for (int j = 0; j < NOUT; ++j) d[j] = 0.f;
+    if (li < nimg) {
+      const long long i = img0 + li;
+      const float inv = 1.0f / static_cast<float>(batch);
+      float z[NOUT];
 #pragma unroll
-    for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
-    float se = 0.f;
+      for (int j = 0; j < NOUT; ++j) z[j] = sums[0][li * NOUT + j];
+      float m = z[0];
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) se += expf(z[j] - m);
-    const float lse = m + logf(se);
-    const int y = static_cast<int>(labels[i]);
+      for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
+      float se = 0.f;
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j) {
-      const float p = expf(z[j] - lse);
-      const float d = (p - (j == y ? 1.f : 0.f)) * inv;
-      dlogits[i * NOUT + j] = d;
-      dbl[j] += d;
-      if (j == y) lsum += lse - z[j];
+      for (int j = 0; j < NOUT; ++j) se += expf(z[j] - m);
+      const float lse = m + logf(se);
+      const int y = static_cast<int>(labels[i]);
+#pragma unroll
+      for (int j = 0; j < NOUT; ++j) {
+        const float p = expf(z[j] - lse);
+        d[j] = (p - (j == y ? 1.f : 0.f)) * inv;
+        dlogits[i * NOUT + j] = d[j];
+        if (j == y) lsum = lse - z[j];
+      }
     }
-  }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-  for (int j = 0; j < NOUT; ++j) {
-    const float v = warp_sum(dbl[j]);
-    if (lane == 0) red[warp][j] = v;
-  }
-  {
-    const float v = warp_sum(lsum);
-    if (lane == 0) red[warp][NOUT] = v;
+    for (int j = 0; j < NOUT; ++j) red[j][li] = d[j];
+    red[NOUT][li] = lsum;
   }
   __syncthreads();
   if (threadIdx.x <= NOUT) {
     float s = 0.f;
-    const int nw = (blockDim.x + 31) >> 5;
-    for (int wdx = 0; wdx < nw; ++wdx) s += red[wdx][threadIdx.x];
+#pragma unroll
+    for (int li = 0; li < kXentImgs; ++li) s += red[threadIdx.x][li];
     g_xent_block_sums[blockIdx.x * 12 + threadIdx.x] = s;
     __threadfence();
   }
@@ -479,13 +489,20 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
     if (is_last) g_xent_ticket = 0;
   }
   __syncthreads();
-  if (is_last && threadIdx.x <= NOUT) {
-    __threadfence();
+  if (!is_last) return;
+  __threadfence();
+  // warp w (<= NOUT) adds column w of the block sums: lanes take blocks lane, lane+32, ... then a
+  // fixed-shape shuffle tree => deterministic
+  const int wq = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (wq <= NOUT) {
     float s = 0.f;
-    for (unsigned int bk = 0; bk < gridDim.x; ++bk)
-      s += *reinterpret_cast<volatile float*>(&g_xent_block_sums[bk * 12 + threadIdx.x]);
-    if (threadIdx.x < NOUT) dbias[threadIdx.x] = s;
-    else loss[0] = s * inv;
+    for (unsigned int bk = lane; bk < gridDim.x; bk += 32)
+      s += *reinterpret_cast<volatile float*>(&g_xent_block_sums[bk * 12 + wq]);
+    s = warp_sum(s);
+    if (lane == 0) {
+      if (wq < NOUT) dbias[wq] = s;
+      else loss[0] = s / static_cast<float>(batch);
+    }
   }
 }
 
@@ -709,9 +726,9 @@ int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void
                       float* logits, float* dlogits, float* dbias, float* loss, int nout,
                       int batch, void* stream) {
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
-  const int blocks = (batch + kXentImgsPerBlock - 1) / kXentImgsPerBlock;
+  const int blocks = (batch + kXentImgs - 1) / kXentImgs;
   if (blocks > kXentMaxBlocks) return DDPB_ERR_LIMIT;
-  return static_cast<int>(launch_k(softmax_xent_kernel<10>, dim3(blocks), dim3(kXentImgsPerBlock * 10), 0,
+  return static_cast<int>(launch_k(softmax_xent_kernel<10>, dim3(blocks), dim3(kXentImgs * 10 * kXentSG), 0,
                                    static_cast<cudaStream_t>(stream), partial, S, bias,
                                    static_cast<const long long*>(labels), logits, dlogits, dbias, loss,
                                    batch));
@@ -754,6 +771,16 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
   return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
 }
 
+// Zero the rows of `nplanes` planes between the end of the batch and the end of its last tile.
+int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int H, int W,
+                        void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (g.ntiles * kTileM <= batch * g.PHW) return 0;
+  return static_cast<int>(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream),
+                                   static_cast<__nv_bfloat16*>(planes), nplanes, g));
+}
+
 // out[i] = sum_p part[p*n + i] in a fixed order (shared by the split-K style kernels).
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -772,6 +799,12 @@ int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void
   return static_cast<int>(launch_k(sgd_kernel, dim3(static_cast<int>(blocks)), dim3(256), 0,
                                    static_cast<cudaStream_t>(stream), p, grad, lr_dev, n));
 }
+
+// Programmatic dependent launch for the step kernels: 1 = on, 0 = off, -1 = DDPB_PDL / default.
+// It hides launch latency and kernel prologues (a win for small, latency-bound steps) at the price
+// of early-resident CTAs competing for SM resources (a small loss for large, bandwidth-bound ones).
+void ddpb_set_pdl(int on) { ddpb::g_pdl = on; }
+int ddpb_get_pdl() { return ddpb::pdl_enabled(); }
 
 const char* ddpb_error_string(int code) {
   switch (code) {

@@ -154,11 +154,14 @@ class SimpleCNNB200(_ModelBase):
             self.act2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
             self.dact2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
             self.dact1 = nat.alloc_planes(C1, batch_cap, H, W, dev)
-            self.lin_partial = nat.scratch(nat.linear_fwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+            self.lin_partial = nat.scratch(nat.linear_fwd_tc_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+            #: fl.weight pre-packed into bf16 tensor-core tiles (refresh with pack_weights() after
+            #: every change of fl.weight; the step engine does it right after the bucket-0 update)
+            self.lin_packed = torch.zeros(nat.linear_pack_bytes(NCLS, C2, H, W), dtype=torch.uint8,
+                                          device=dev)
             self.logits = torch.zeros(batch_cap, NCLS, device=dev)
             self.dlogits = torch.zeros(batch_cap, NCLS, device=dev)
             self.loss = torch.zeros(1, device=dev)
-            self.scr_lin = nat.scratch(nat.linear_bwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
             self.scr_w2 = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(C1, C2), dev)
             self.scr_w1 = nat.scratch(nat.conv1_wgrad_tc_scratch_bytes(1, C1), dev)
             self.lr_dev = torch.full((1,), 0.01, device=dev)
@@ -178,16 +181,22 @@ class SimpleCNNB200(_ModelBase):
             })
 
     # ------------------------------------------------------------------ step pieces
+    def pack_weights(self, stream=None) -> None:
+        """fl.weight (fp32) -> bf16 tensor-core tiles used by the linear forward and backward."""
+        self.nat.linear_pack(self.wf, self.lin_packed, NCLS, C2, IMG_H, IMG_W, stream)
+
     def forward_loss(self, x: torch.Tensor, y: torch.Tensor, batch: int | None = None, stream=None,
-                     parity: int = 0):
+                     parity: int = 0, pack: bool = True):
         nat = self.nat
         gs = self.grad_sets[parity]
         b = int(batch if batch is not None else x.shape[0])
         assert 0 < b <= self.batch_cap
         cap, H, W = self.batch_cap, IMG_H, IMG_W
+        if pack:
+            self.pack_weights(stream)
         nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W, stream)
-        S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
+        S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, gs["bf"],
                          self.loss, NCLS, b, stream)
         return self.loss
@@ -195,8 +204,8 @@ class SimpleCNNB200(_ModelBase):
     def backward_head(self, batch: int, stream=None, parity: int = 0):
         """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel)."""
         gs = self.grad_sets[parity]
-        self.nat.linear_bwd(self.act2, self.dlogits, self.wf, self.dact2, gs["wf"], self.scr_lin,
-                            NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
+        self.nat.linear_bwd_tc(self.act2, self.dlogits, self.lin_packed, self.dact2, gs["wf"],
+                               NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):
         """conv2 weight + bias gradient (independent of the dgrad chain: may run on its own stream)."""
@@ -228,7 +237,8 @@ class SimpleCNNB200(_ModelBase):
         """Kernels one forward+backward launches (bench.py reports it as part of gpu_launches)."""
         from ..ops import layout as lay
         tail = 1 if lay.tiles_for(batch, IMG_H, IMG_W) * lay.TILE_M > batch * 900 else 0
-        return 4 + (2 + tail) + 2 + 1 + 2
+        # conv1, conv2, linear, loss | (tail zero) linear bwd | wgrad+reduce, dgrad, conv1 wgrad+reduce
+        return 4 + (1 + tail) + 2 + 1 + 2
 
     def sgd_step(self, lr: float | None = None, stream=None) -> None:
         if lr is not None:
@@ -250,9 +260,10 @@ class SimpleCNNB200(_ModelBase):
         cap, H, W = self.batch_cap, IMG_H, IMG_W
         y = torch.zeros(b, dtype=torch.int64, device=self.device)
         scratch_db = torch.empty(NCLS, device=self.device)
+        self.pack_weights()
         nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W)
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W)
-        S = nat.linear_fwd(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W)
+        S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, scratch_db,
                          self.loss, NCLS, b)
         return self.logits[:b]

@@ -43,6 +43,13 @@ _SIGNATURES = {
     "ddpb_linear_fwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_fwd": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_softmax_xent": (I, [P, I, P, P, P, P, P, P, I, I, P]),
+    "ddpb_linear_pack_bytes": (c_size_t, [I, I, I, I]),
+    "ddpb_linear_pack": (I, [P, P, I, I, I, I, P]),
+    "ddpb_linear_fwd_tc_scratch_bytes": (c_size_t, [I, I, I, I, I]),
+    "ddpb_linear_fwd_tc": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_linear_bwd_tc": (I, [P, P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_set_pdl": (None, [I]),
+    "ddpb_get_pdl": (I, []),
     "ddpb_linear_bwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_bwd": (I, [P, P, P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_sgd": (I, [P, P, P, LL, P]),
@@ -187,6 +194,33 @@ def linear_fwd(act, Wfl, partial, nout, C, batch, batch_cap, H, W, stream=None) 
     check(lib().ddpb_linear_fwd(ptr(act), ptr(Wfl), ptr(partial), ctypes.byref(s), nout, C, batch,
                                 batch_cap, H, W, stream_ptr(stream)), "linear_fwd")
     return s.value
+
+
+def linear_pack_bytes(nout, C, H, W) -> int:
+    return int(lib().ddpb_linear_pack_bytes(nout, C, H, W))
+
+
+def linear_pack(Wfl, packed, nout, C, H, W, stream=None):
+    """fp32 linear weights -> bf16 UMMA tiles (hi+lo forward tile, backward tile)."""
+    check(lib().ddpb_linear_pack(ptr(Wfl), ptr(packed), nout, C, H, W, stream_ptr(stream)), "linear_pack")
+
+
+def linear_fwd_tc_scratch_bytes(nout, C, batch_cap, H, W) -> int:
+    return int(lib().ddpb_linear_fwd_tc_scratch_bytes(nout, C, batch_cap, H, W))
+
+
+def linear_fwd_tc(act, packed, partial, nout, C, batch, batch_cap, H, W, stream=None) -> int:
+    """Tensor-core linear forward; returns S, the number of partial slices written."""
+    s = c_int(0)
+    check(lib().ddpb_linear_fwd_tc(ptr(act), ptr(packed), ptr(partial), ctypes.byref(s), nout, C, batch,
+                                   batch_cap, H, W, stream_ptr(stream)), "linear_fwd_tc")
+    return s.value
+
+
+def linear_bwd_tc(act, dlogits, packed, dact, dW, nout, C, batch, batch_cap, H, W, stream=None):
+    """Tensor-core linear backward: dact = relu'(act) * dlogits.W, dW = dlogits^T.act (no scratch)."""
+    check(lib().ddpb_linear_bwd_tc(ptr(act), ptr(dlogits), ptr(packed), ptr(dact), ptr(dW), nout, C,
+                                   batch, batch_cap, H, W, stream_ptr(stream)), "linear_bwd_tc")
 
 
 def softmax_xent(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch, stream=None):

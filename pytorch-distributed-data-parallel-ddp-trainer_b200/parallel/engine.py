@@ -83,6 +83,11 @@ class B200DataParallel(_EngineBase):
         self.batch_cap = int(batch_cap)
         self.use_graph = use_graph
         self.algo = algo
+        # programmatic dependent launch pays off for latency-bound (small-batch) steps only
+        import os
+        from ..ops import native as _nat
+        if "DDPB_PDL" not in os.environ:
+            _nat.lib().ddpb_set_pdl(1 if self.batch_cap <= 512 else 0)
 
         from ..models.arena import ParamArena
         from ..models.simple_cnn import SPECS
@@ -132,11 +137,12 @@ class B200DataParallel(_EngineBase):
         torch.cuda.synchronize(self.device)
         if self.world_size > 1:
             self.comm.broadcast(self.param_off, self._n * 4, root=src, slot=7, stream=self.main)
-            self.main.synchronize()
+        self.model.pack_weights(self.main)
+        self.main.synchronize()
 
     # ------------------------------------------------------------------ the step
     def launches_per_step(self, batch: int) -> int:
-        return self.model.launches_per_step(batch) + 2
+        return self.model.launches_per_step(batch) + 3  # two bucket updates + weight re-pack
 
     def _enqueue(self, b: int, parity: int) -> None:
         """Enqueue one full training step; capturable.  Stream plan:
@@ -149,7 +155,7 @@ class B200DataParallel(_EngineBase):
         x, y = self.x_in[parity][:b], self.y_in[parity][:b]
         (s0, n0), (s1, n1) = self.buckets
         gflat = m.grad_sets[parity]["flat"]
-        m.forward_loss(x, y, b, main, parity)
+        m.forward_loss(x, y, b, main, parity, pack=False)
         m.backward_head(b, main, parity)
         self._ev_fork.record(main)
         self.side.wait_event(self._ev_fork)
@@ -161,6 +167,7 @@ class B200DataParallel(_EngineBase):
                                     self.algo, slot=0, stream=self.side)
         else:
             m.nat.sgd(m.arena.params[s0:s0 + n0], gflat[s0:s0 + n0], m.lr_dev, self.side)
+        m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step, off the critical path
         self._ev_join.record(self.side)
         m.backward_conv2_wgrad(b, self.side2, parity)
         self._ev_join2.record(self.side2)
