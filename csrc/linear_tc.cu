@@ -34,7 +34,7 @@ __device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
 
 // ------------------------------------------------------------------------------------- pack
 // wf [nkc_pad][32][8]  bf16: row n < NOUT = hi(W[n][k]), row 16+n = lo(W[n][k]), k = (chunk*8+e)*HW+pix
-// wb [2][nkc_pad][8][8] bf16: [jg][kc][e][j%8] = bf16(W[jg*8 + j%8][k])                (j >= NOUT: 0)
+// wb [4][nkc_pad][8][8] bf16: [g][kc][e][j%8]: g = 0,1: hi(W[(g&1)*8 + j%8][k]); g = 2,3: lo(...)   (j >= NOUT: 0)
 template <int NOUT>
 __global__ void __launch_bounds__(128)
 pack_linear_weights_kernel(const float* __restrict__ W, __nv_bfloat16* __restrict__ wf,
@@ -43,11 +43,14 @@ pack_linear_weights_kernel(const float* __restrict__ W, __nv_bfloat16* __restric
   const int kc = blockIdx.x * blockDim.x + threadIdx.x;
   if (kc >= nkc_pad) return;
   uint4* wf_row = reinterpret_cast<uint4*>(wf + (long long)kc * 32 * 8);
-  uint4* wb0 = reinterpret_cast<uint4*>(wb + (long long)kc * 64);
-  uint4* wb1 = reinterpret_cast<uint4*>(wb + ((long long)nkc_pad + kc) * 64);
+  uint4* wbg[4];
+#pragma unroll
+  for (int gq = 0; gq < 4; ++gq)
+    wbg[gq] = reinterpret_cast<uint4*>(wb + ((long long)gq * nkc_pad + kc) * 64);
   if (kc >= nkc) {
     for (int n = 0; n < 32; ++n) wf_row[n] = make_uint4(0, 0, 0, 0);
-    for (int e = 0; e < 8; ++e) wb0[e] = wb1[e] = make_uint4(0, 0, 0, 0);
+    for (int e = 0; e < 8; ++e)
+      for (int gq = 0; gq < 4; ++gq) wbg[gq][e] = make_uint4(0, 0, 0, 0);
     return;
   }
   const int chunk = kc / HW, pix = kc - chunk * HW;
@@ -75,13 +78,19 @@ pack_linear_weights_kernel(const float* __restrict__ W, __nv_bfloat16* __restric
   }
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
-    float j8[16];
+    uint32_t hi[8], lo[8];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) j8[j] = j < NOUT ? w[j < NOUT ? j : 0][e] : 0.f;
-    wb0[e] = make_uint4(pack_bf16x2(j8[0], j8[1]), pack_bf16x2(j8[2], j8[3]), pack_bf16x2(j8[4], j8[5]),
-                        pack_bf16x2(j8[6], j8[7]));
-    wb1[e] = make_uint4(pack_bf16x2(j8[8], j8[9]), pack_bf16x2(j8[10], j8[11]),
-                        pack_bf16x2(j8[12], j8[13]), pack_bf16x2(j8[14], j8[15]));
+    for (int q = 0; q < 8; ++q) {
+      const float a = 2 * q < NOUT ? w[2 * q < NOUT ? 2 * q : 0][e] : 0.f;
+      const float b = 2 * q + 1 < NOUT ? w[2 * q + 1 < NOUT ? 2 * q + 1 : 0][e] : 0.f;
+      const float ah = __bfloat162float(__float2bfloat16(a)), bh = __bfloat162float(__float2bfloat16(b));
+      hi[q] = pack_bf16x2(ah, bh);
+      lo[q] = pack_bf16x2(a - ah, b - bh);
+    }
+    wbg[0][e] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    wbg[1][e] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+    wbg[2][e] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    wbg[3][e] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
   }
 }
 
@@ -219,7 +228,7 @@ extern "C" {
 size_t ddpb_linear_pack_bytes(int nout, int C, int H, int W) {
   (void)nout;
   const long long nkc_pad = ((long long)(C / 8) * H * W + kLinKB - 1) / kLinKB * kLinKB;
-  return static_cast<size_t>(nkc_pad) * (512 + 256);
+  return static_cast<size_t>(nkc_pad) * (512 + 512);
 }
 
 int ddpb_linear_pack(const float* Wfl, void* packed, int nout, int C, int H, int W, void* stream) {
@@ -283,20 +292,20 @@ constexpr int kLbStages = 3;
 constexpr uint32_t kLbActBytes = kLbFB * kLinChunkPitch;  // 33,024
 constexpr uint32_t kLbDlBytes = 4 * kTileM * 16;          // 8,192
 constexpr uint32_t kLbStage = kLbActBytes + kLbDlBytes;
-constexpr uint32_t kLbWbBytes = 2 * kLbFB * 128;          // 4,096 per feature block
+constexpr uint32_t kLbWbBytes = 4 * kLbFB * 128;          // 8,192 per feature block (hi, hi, lo, lo)
 
 struct LinBwdSmem {
   static constexpr uint32_t off_wb = kLbStages * kLbStage;          // 2 buffers
   static constexpr uint32_t off_bar = off_wb + 2 * kLbWbBytes;
   // full[ST], empty[ST], wbfull[2], wbfree[2], d1full[2], d1free[2], dwfull, dwfree
-  static constexpr uint32_t nbar = 2 * kLbStages + 10;
+  static constexpr uint32_t nbar = 2 * kLbStages + 12;
   static constexpr uint32_t off_tmem = off_bar + nbar * 8;
   static constexpr uint32_t total = off_tmem + 16;
 };
 
 template <int NOUT>
 __global__ void __launch_bounds__(kLinThreads, 1)
-linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict__ dlogits,
+linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16* __restrict__ dlp,
                      const __nv_bfloat16* __restrict__ wb, __nv_bfloat16* __restrict__ dact,
                      float* __restrict__ dW, Geom g, int HW, int nkc, int nkc_pad, int C) {
   using S = LinBwdSmem;
@@ -310,14 +319,14 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
   const uint32_t bar_d1full = bar_wbfree + 16;
   const uint32_t bar_d1free = bar_d1full + 16;
   const uint32_t bar_dwfull = bar_d1free + 16;
-  const uint32_t bar_dwfree = bar_dwfull + 8;
+  const uint32_t bar_dwfree = bar_dwfull + 16;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + S::off_tmem);
   const int nfb = (nkc + kLbFB - 1) / kLbFB;
   const int mtiles = (g.batch + kTileM - 1) / kTileM;
 
   if (tid == 0) {
     for (int i = 0; i < kLbStages; ++i) {
-      mbar_init(bar_full + i * 8, 256);   // 128 cp.async completions + 128 plain arrivals (dlogits tile)
+      mbar_init(bar_full + i * 8, 129);   // 128 cp.async completions + the dlogits-tile bulk copy
       mbar_init(bar_empty + i * 8, 129);  // MMA commit + 128 epilogue threads (mask read)
     }
     for (int i = 0; i < 2; ++i) {
@@ -326,13 +335,15 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
       mbar_init(bar_d1full + i * 8, 1);
       mbar_init(bar_d1free + i * 8, 128);
     }
-    mbar_init(bar_dwfull, 1);
-    mbar_init(bar_dwfree, 128);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_dwfull + i * 8, 1);
+      mbar_init(bar_dwfree + i * 8, 128);
+    }
     fence_mbar_init();
   }
   if (warp == 4) {
     tmem_alloc(smem_u32(s_tmem), 256);      // dX accumulator, two buffers of 128 columns
-    tmem_alloc(smem_u32(s_tmem + 1), 32);   // dW accumulator
+    tmem_alloc(smem_u32(s_tmem + 1), 64);   // dW accumulator, two buffers of 32 columns
     tmem_relinquish();
   }
   tc_fence_before();
@@ -349,7 +360,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
         const int wbuf = fbi & 1;
         mbar_wait(bar_wbfree + wbuf * 8, ((fbi >> 1) & 1) ^ 1);
         mbar_arrive_expect_tx(bar_wbfull + wbuf * 8, kLbWbBytes);
-        for (int jg = 0; jg < 2; ++jg)
+        for (int jg = 0; jg < 4; ++jg)
           bulk_g2s(s_base + S::off_wb + wbuf * kLbWbBytes + jg * (kLbFB * 128),
                    wb + ((long long)jg * nkc_pad + (long long)fb * kLbFB) * 64, kLbFB * 128,
                    bar_wbfull + wbuf * 8);
@@ -378,28 +389,10 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
           }
         }
         cp_async_arrive(bar_full + stage * 8);
-        // dlogits tile: one image per thread -> [group][image][8] with groups hi0-7, hi8-15, lo0-7, lo8-15
-        {
-          const int img = mt * kTileM + tid;
-          float d[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            d[j] = (j < NOUT && img < g.batch) ? dlogits[(long long)img * NOUT + j] : 0.f;
-          uint32_t hi[8], lo[8];
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float a = d[2 * q], b = d[2 * q + 1];
-            const float ah = __bfloat162float(__float2bfloat16(a)), bh = __bfloat162float(__float2bfloat16(b));
-            hi[q] = pack_bf16x2(ah, bh);
-            lo[q] = pack_bf16x2(a - ah, b - bh);
-          }
-          uint8_t* dl = smem + stage * kLbStage + kLbActBytes + tid * 16;
-          *reinterpret_cast<uint4*>(dl) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          *reinterpret_cast<uint4*>(dl + 2048) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-          *reinterpret_cast<uint4*>(dl + 4096) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-          *reinterpret_cast<uint4*>(dl + 6144) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-          fence_proxy_async_smem();
-          mbar_arrive(bar_full + stage * 8);
+        if (tid == 0) {  // dlogits tile, pre-packed by the loss kernel: [4 groups][128 images][8] bf16
+          mbar_arrive_expect_tx(bar_full + stage * 8, kLbDlBytes);
+          bulk_g2s(sa + kLbActBytes, dlp + (long long)mt * (kLbDlBytes / 2), kLbDlBytes,
+                   bar_full + stage * 8);
         }
       }
     }
@@ -411,9 +404,10 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
     for (int fb = blockIdx.x; fb < nfb; fb += gridDim.x, ++fbi) {
       const int wbuf = fbi & 1;
       mbar_wait(bar_wbfull + wbuf * 8, (fbi >> 1) & 1);
-      mbar_wait(bar_dwfree, (fbi & 1) ^ 1);  // previous block's dW accumulator has been read out
+      mbar_wait(bar_dwfree + wbuf * 8, ((fbi >> 1) & 1) ^ 1);  // this dW buffer has been read out
       tc_fence_after();
       const uint32_t swb = s_base + S::off_wb + wbuf * kLbWbBytes;
+      const uint32_t d_dw = tmem_dw + wbuf * 32;
       for (int mt = 0; mt < mtiles; ++mt, ++it) {
         const int stage = it % kLbStages;
         const uint32_t phase = (it / kLbStages) & 1;
@@ -424,27 +418,31 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
         tc_fence_after();
         const uint32_t sa = s_base + stage * kLbStage;
         const uint32_t sdl = sa + kLbActBytes;
-        // dX = dl_hi . W + dl_lo . W    (A: [4 groups][128 img][16 B], LBO = 2048 between groups)
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          const uint64_t adesc = umma_smem_desc(sdl + half * 4096, 2048, 128);
-          const uint64_t bdesc = umma_smem_desc(swb, kLbFB * 128, 128);
-          if (elect_one()) umma_bf16(tmem_dx + acc * 128, adesc, bdesc, idesc_dx, half);
+        // dX = dl_hi.W_hi + dl_lo.W_hi + dl_hi.W_lo   (operand groups are 2 x [.][16 B], LBO 2048)
+        {
+          const uint64_t a_hi = umma_smem_desc(sdl, 2048, 128), a_lo = umma_smem_desc(sdl + 4096, 2048, 128);
+          const uint64_t b_hi = umma_smem_desc(swb, kLbFB * 128, 128);
+          const uint64_t b_lo = umma_smem_desc(swb + 2 * kLbFB * 128, kLbFB * 128, 128);
+          if (elect_one()) {
+            umma_bf16(tmem_dx + acc * 128, a_hi, b_hi, idesc_dx, 0);
+            umma_bf16(tmem_dx + acc * 128, a_lo, b_hi, idesc_dx, 1);
+            umma_bf16(tmem_dx + acc * 128, a_hi, b_lo, idesc_dx, 1);
+            umma_commit(bar_d1full + acc * 8);
+          }
         }
-        if (elect_one()) umma_commit(bar_d1full + acc * 8);
         // dW += act^T . dl   (K = images, 16 per MMA)
 #pragma unroll
         for (int ks = 0; ks < kTileM / 16; ++ks) {
           const uint64_t adesc = umma_smem_desc(sa + ks * 256, 128, kLinChunkPitch);
           const uint64_t bdesc = umma_smem_desc(sdl + ks * 256, 128, 2048);
-          if (elect_one()) umma_bf16(tmem_dw, adesc, bdesc, idesc_dw, (mt | ks) != 0);
+          if (elect_one()) umma_bf16(d_dw, adesc, bdesc, idesc_dw, (mt | ks) != 0);
         }
         if (elect_one()) umma_commit(bar_empty + stage * 8);
         __syncwarp();
       }
       if (elect_one()) {
         umma_commit(bar_wbfree + wbuf * 8);
-        umma_commit(bar_dwfull);
+        umma_commit(bar_dwfull + wbuf * 8);
       }
       __syncwarp();
     }
@@ -454,6 +452,16 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
     const int row = q * 32 + lane;  // image within the tile (dX) / feature within the block (dW)
     int it = 0, fbi = 0;
     for (int fb = blockIdx.x; fb < nfb; fb += gridDim.x, ++fbi) {
+      // plane offset (in elements) of chunk kl of this block, computed once by lane kl
+      long long my_off = -1;
+      if (lane < kLbFB) {
+        const int kc = fb * kLbFB + lane;
+        if (kc < nkc) {
+          const int chunk = kc / HW, pix = kc - chunk * HW;
+          const int h = pix / g.W, w = pix - h * g.W;
+          my_off = ((long long)chunk * g.plane_rows + kGuard + (long long)(h + 1) * g.PW + (w + 1)) * 8;
+        }
+      }
       for (int mt = 0; mt < mtiles; ++mt, ++it) {
         const int stage = it % kLbStages;
         const int acc = it & 1;
@@ -461,6 +469,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
         mbar_wait(bar_d1full + acc * 8, (it >> 1) & 1);
         tc_fence_after();
         const uint8_t* sact = smem + stage * kLbStage + (row >> 3) * 128 + (row & 7) * 16;
+        __nv_bfloat16* drow = dact + (long long)img * g.PHW * 8;
 #pragma unroll 1
         for (int c0 = 0; c0 < 128; c0 += 32) {
           uint32_t v[32];
@@ -469,7 +478,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int kl = c0 / 8 + j;
-            const int kc = fb * kLbFB + kl;
+            const long long off = __shfl_sync(0xffffffffu, my_off, kl);
             const uint4 mk = *reinterpret_cast<const uint4*>(sact + kl * kLinChunkPitch);
             const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk);
             uint4 o;
@@ -480,13 +489,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
               const float x1 = bf16_hi(mp[e]) > 0.f ? __uint_as_float(v[j * 8 + 2 * e + 1]) : 0.f;
               op[e] = pack_bf16x2(x0, x1);
             }
-            if (kc < nkc && img < g.batch) {
-              const int chunk = kc / HW, pix = kc - chunk * HW;
-              const int h = pix / g.W, w = pix - h * g.W;
-              *reinterpret_cast<uint4*>(
-                  dact + ((long long)chunk * g.plane_rows + kGuard + (long long)img * g.PHW +
-                          (long long)(h + 1) * g.PW + (w + 1)) * 8) = o;
-            }
+            if (off >= 0 && img < g.batch) *reinterpret_cast<uint4*>(drow + off) = o;
           }
         }
         tc_fence_before();
@@ -494,14 +497,15 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
         mbar_arrive(bar_empty + stage * 8);  // done reading the activation tile (mask)
       }
       // dW of this feature block: row = feature kl*8 + e
-      mbar_wait(bar_dwfull, fbi & 1);
+      const int wbuf = fbi & 1;
+      mbar_wait(bar_dwfull + wbuf * 8, (fbi >> 1) & 1);
       tc_fence_after();
       {
         uint32_t v[32];
-        tmem_ld32(tmem_dw + (static_cast<uint32_t>(q * 32) << 16), v);
+        tmem_ld32(tmem_dw + wbuf * 32 + (static_cast<uint32_t>(q * 32) << 16), v);
         tmem_ld_wait();
         tc_fence_before();
-        mbar_arrive(bar_dwfree);
+        mbar_arrive(bar_dwfree + wbuf * 8);
         const int kc = fb * kLbFB + (row >> 3);
         if (kc < nkc) {
           const int chunk = kc / HW, pix = kc - chunk * HW;
@@ -518,7 +522,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
   __syncthreads();
   if (warp == 4) {
     tmem_dealloc(tmem_dx, 256);
-    tmem_dealloc(tmem_dw, 32);
+    tmem_dealloc(tmem_dw, 64);
   }
 }
 
@@ -527,7 +531,8 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const float* __restr
 extern "C" int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int H, int W,
                                    void* stream);
 
-extern "C" int ddpb_linear_bwd_tc(const void* act, const float* dlogits, const void* packed, void* dact,
+// dl_packed: the bf16 hi/lo dlogits tiles written by ddpb_softmax_xent (its dl_packed argument).
+extern "C" int ddpb_linear_bwd_tc(const void* act, const void* dl_packed, const void* packed, void* dact,
                                   float* dW, int nout, int C, int batch, int batch_cap, int H, int W,
                                   void* stream) {
   using namespace ddpb;
@@ -553,6 +558,7 @@ extern "C" int ddpb_linear_bwd_tc(const void* act, const float* dlogits, const v
   const int grid = nfb < sms ? nfb : sms;
   return static_cast<int>(launch_k(linear_bwd_tc_kernel<10>, dim3(grid), dim3(kLinThreads),
                                    LinBwdSmem::total, static_cast<cudaStream_t>(stream),
-                                   static_cast<const __nv_bfloat16*>(act), dlogits, wb,
+                                   static_cast<const __nv_bfloat16*>(act),
+                                   static_cast<const __nv_bfloat16*>(dl_packed), wb,
                                    static_cast<__nv_bfloat16*>(dact), dW, g, H * W, nkc, nkc_pad, C));
 }

@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(kXentImgs * NOUT * kXentSG)
 softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
                     const long long* __restrict__ labels, float* __restrict__ logits,
                     float* __restrict__ dlogits, float* __restrict__ dbias,
-                    float* __restrict__ loss, int batch) {
+                    float* __restrict__ loss, int batch, uint4* __restrict__ dl_packed) {
   static_assert(NOUT + 1 <= 12, "block-sum row too small");
   constexpr int NP = kXentImgs * NOUT;  // (image, class) pairs per block
   __shared__ float sums[kXentSG][NP];
@@ -413,7 +413,8 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
   __shared__ bool is_last;
   pdl_sync();
   const int img0 = blockIdx.x * kXentImgs;
-  const int nimg = min(kXentImgs, batch - img0);
+  const int nimg = max(0, min(kXentImgs, batch - img0));  // 0 for the zero-row blocks past the batch
+  const int tidx = static_cast<int>(threadIdx.x);         // signed: compared with nimg-derived counts
   const long long npair_all = (long long)batch * NOUT;
   // phase 1: thread (pair, sg) adds partial slices sg, sg+SG, ...
   {
@@ -434,12 +435,12 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
     sums[sg][pair] = z;
   }
   __syncthreads();
-  if (threadIdx.x < nimg * NOUT) {
-    float z = bias[threadIdx.x % NOUT];
+  if (tidx < nimg * NOUT) {
+    float z = bias[tidx % NOUT];
 #pragma unroll
-    for (int u = 0; u < kXentSG; ++u) z += sums[u][threadIdx.x];
-    sums[0][threadIdx.x] = z;
-    logits[(long long)img0 * NOUT + threadIdx.x] = z;
+    for (int u = 0; u < kXentSG; ++u) z += sums[u][tidx];
+    sums[0][tidx] = z;
+    logits[(long long)img0 * NOUT + tidx] = z;
   }
   __syncthreads();
   // phase 2: one thread per image: log-softmax, loss and gradient
@@ -468,6 +469,28 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
         d[j] = (p - (j == y ? 1.f : 0.f)) * inv;
         dlogits[i * NOUT + j] = d[j];
         if (j == y) lsum = lse - z[j];
+      }
+    }
+    // bf16 hi/lo tiles of dlogits for the tensor-core linear backward:
+    // tile (image/128): [4 groups: hi j0-7, hi j8-15, lo j0-7, lo j8-15][128 images][8]
+    if (dl_packed != nullptr) {
+      const long long i = img0 + li;
+      const long long padded = ((long long)batch + 127) / 128 * 128;
+      if (i < padded) {  // rows past the batch (up to the end of its last tile) are zero
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int qd = 0; qd < 8; ++qd) {
+          const float a = (li < nimg && 2 * qd < NOUT) ? d[2 * qd < NOUT ? 2 * qd : 0] : 0.f;
+          const float b = (li < nimg && 2 * qd + 1 < NOUT) ? d[2 * qd + 1 < NOUT ? 2 * qd + 1 : 0] : 0.f;
+          const float ah = __bfloat162float(__float2bfloat16(a)), bh = __bfloat162float(__float2bfloat16(b));
+          hi[qd] = pack_bf16x2(ah, bh);
+          lo[qd] = pack_bf16x2(a - ah, b - bh);
+        }
+        uint4* t = dl_packed + (i >> 7) * 512 + (i & 127);
+        t[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        t[128] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        t[256] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        t[384] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
       }
     }
 #pragma unroll
@@ -722,16 +745,38 @@ int ddpb_linear_fwd(const void* act, const float* Wt, float* partial, int* S_out
                                    static_cast<const __nv_bfloat16*>(act), Wt, partial, g, C, per));
 }
 
+static int softmax_xent_launch(const float* partial, int S, const float* bias, const void* labels,
+                               float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                               int batch, void* dl_packed, void* stream);
+
 int ddpb_softmax_xent(const float* partial, int S, const float* bias, const void* labels,
                       float* logits, float* dlogits, float* dbias, float* loss, int nout,
                       int batch, void* stream) {
+  return softmax_xent_launch(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch,
+                             nullptr, stream);
+}
+
+// Same, and also writes dlogits as bf16 hi/lo tiles ((batch rounded up to 128) * 64 bytes) for
+// ddpb_linear_bwd_tc.
+int ddpb_softmax_xent_packed(const float* partial, int S, const float* bias, const void* labels,
+                             float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                             int batch, void* dl_packed, void* stream) {
+  return softmax_xent_launch(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch,
+                             dl_packed, stream);
+}
+
+static int softmax_xent_launch(const float* partial, int S, const float* bias, const void* labels,
+                               float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                               int batch, void* dl_packed, void* stream) {
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
-  const int blocks = (batch + kXentImgs - 1) / kXentImgs;
+  // with packed output the grid also covers the zero rows up to the end of the last 128-image tile
+  const int covered = dl_packed ? (batch + 127) / 128 * 128 : batch;
+  const int blocks = (covered + kXentImgs - 1) / kXentImgs;
   if (blocks > kXentMaxBlocks) return DDPB_ERR_LIMIT;
   return static_cast<int>(launch_k(softmax_xent_kernel<10>, dim3(blocks), dim3(kXentImgs * 10 * kXentSG), 0,
                                    static_cast<cudaStream_t>(stream), partial, S, bias,
                                    static_cast<const long long*>(labels), logits, dlogits, dbias, loss,
-                                   batch));
+                                   batch, static_cast<uint4*>(dl_packed)));
 }
 
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);

@@ -115,6 +115,53 @@ int ddpb_linear_bwd(const void* act_planes, const float* dlogits, const float* W
                     void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,
                     int batch_cap, int H, int W, void* stream);
 
+/* ---- linear layer on the tensor cores (what the step engine uses).
+ * ddpb_linear_pack turns the fp32 weight [nout][C*H*W] into bf16 UMMA tiles (forward tile as
+ * hi+lo pairs, backward tile likewise); call it whenever the weight changed.
+ * Forward: 128-image tiles gathered with cp.async into UMMA core matrices, K split over the SMs,
+ * partial[S][batch][nout] as above.  Backward: one persistent kernel, no scratch: dX with the
+ * ReLU mask fused, dW accumulated in TMEM over all image tiles (one writer per element).
+ * dl_packed = the bf16 hi/lo dlogits tiles ddpb_softmax_xent_packed writes
+ * ((batch_cap rounded up to 128) * 64 bytes). */
+size_t ddpb_linear_pack_bytes(int nout, int C, int H, int W);
+int ddpb_linear_pack(const float* W_fl, void* packed, int nout, int C, int H, int W, void* stream);
+size_t ddpb_linear_fwd_tc_scratch_bytes(int nout, int C, int batch_cap, int H, int W);
+int ddpb_linear_fwd_tc(const void* act_planes, const void* packed, float* partial, int* S_out,
+                       int nout, int C, int batch, int batch_cap, int H, int W, void* stream);
+int ddpb_softmax_xent_packed(const float* partial, int S, const float* bias, const void* labels_i64,
+                             float* logits, float* dlogits, float* dbias, float* loss, int nout,
+                             int batch, void* dl_packed, void* stream);
+int ddpb_linear_bwd_tc(const void* act_planes, const void* dl_packed, const void* packed,
+                       void* dact_planes, float* dW, int nout, int C, int batch, int batch_cap,
+                       int H, int W, void* stream);
+int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int H, int W,
+                        void* stream);
+
+/* ---- symmetric-memory communicator (csrc/comm.cu): one process per GPU, world in {1,2,4,8}.
+ * ddpb_comm_create cudaMallocs this rank's buffer (header + payload, zero-filled);
+ * ddpb_comm_get_handle / ddpb_comm_connect exchange CUDA IPC handles (host side, any transport).
+ * Offsets are byte offsets into the payload, identical on all ranks, 16-byte aligned.
+ * algo: 0 by size, 1 one-shot, 2 two-shot.  slot: independent flag channel in [0, 8).
+ * Replaces ProcessGroupNCCL + the DDP Reducer + torch.optim.SGD, reference train_ddp.py:34,199-200. */
+size_t ddpb_comm_header_bytes(void);
+int ddpb_comm_handle_bytes(void);
+int ddpb_comm_create(int rank, int world, size_t payload_bytes, void** comm_out);
+int ddpb_comm_get_handle(void* comm, void* handle_out /* host */);
+int ddpb_comm_connect(void* comm, const void* all_handles /* host, world * handle_bytes */);
+void* ddpb_comm_local_ptr(void* comm);
+void* ddpb_comm_peer_ptr(void* comm, int rank);
+size_t ddpb_comm_payload_bytes(void* comm);
+void ddpb_comm_set_timeout_ms(void* comm, long long ms);
+int ddpb_comm_status(void* comm, unsigned int* status_out /* host */);
+int ddpb_comm_destroy(void* comm);
+/* params[slice] -= lr/world * sum_over_ranks(grads[slice]) in ONE kernel (in-kernel flags). */
+int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long n_floats,
+                       const float* lr_dev, int algo, int slot, void* stream);
+/* plain sum all-reduce, dtype 0 = fp32, 1 = bf16; out_off must not overlap in_off. */
+int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, int dtype, int algo,
+                   int slot, void* stream);
+int ddpb_broadcast(void* comm, size_t off, long long nbytes, int root, int slot, void* stream);
+
 /* ---- p -= lr*g with lr read from device memory (single-GPU path; multi-GPU runs fuse the
  * update into the all-reduce).  reference train_ddp.py:41,200. */
 int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream);

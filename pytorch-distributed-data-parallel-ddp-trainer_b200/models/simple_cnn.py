@@ -161,6 +161,7 @@ class SimpleCNNB200(_ModelBase):
                                           device=dev)
             self.logits = torch.zeros(batch_cap, NCLS, device=dev)
             self.dlogits = torch.zeros(batch_cap, NCLS, device=dev)
+            self.dl_packed = torch.zeros(nat.dl_packed_bytes(batch_cap), dtype=torch.uint8, device=dev)
             self.loss = torch.zeros(1, device=dev)
             self.scr_w2 = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(C1, C2), dev)
             self.scr_w1 = nat.scratch(nat.conv1_wgrad_tc_scratch_bytes(1, C1), dev)
@@ -180,6 +181,10 @@ class SimpleCNNB200(_ModelBase):
                 "wf": a.view("fl.weight", gbuf), "bf": a.view("fl.bias", gbuf),
             })
 
+    def load_state_dict(self, sd, strict: bool = True) -> None:
+        super().load_state_dict(sd, strict=strict)
+        self.pack_weights()  # the tensor-core tiles of fl.weight must follow the new values
+
     # ------------------------------------------------------------------ step pieces
     def pack_weights(self, stream=None) -> None:
         """fl.weight (fp32) -> bf16 tensor-core tiles used by the linear forward and backward."""
@@ -198,13 +203,13 @@ class SimpleCNNB200(_ModelBase):
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W, stream)
         S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, gs["bf"],
-                         self.loss, NCLS, b, stream)
+                         self.loss, NCLS, b, stream, dl_packed=self.dl_packed)
         return self.loss
 
     def backward_head(self, batch: int, stream=None, parity: int = 0):
         """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel)."""
         gs = self.grad_sets[parity]
-        self.nat.linear_bwd_tc(self.act2, self.dlogits, self.lin_packed, self.dact2, gs["wf"],
+        self.nat.linear_bwd_tc(self.act2, self.dl_packed, self.lin_packed, self.dact2, gs["wf"],
                                NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):

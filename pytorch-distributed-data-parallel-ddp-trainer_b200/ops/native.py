@@ -43,6 +43,7 @@ _SIGNATURES = {
     "ddpb_linear_fwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_fwd": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_softmax_xent": (I, [P, I, P, P, P, P, P, P, I, I, P]),
+    "ddpb_softmax_xent_packed": (I, [P, I, P, P, P, P, P, P, I, I, P, P]),
     "ddpb_linear_pack_bytes": (c_size_t, [I, I, I, I]),
     "ddpb_linear_pack": (I, [P, P, I, I, I, I, P]),
     "ddpb_linear_fwd_tc_scratch_bytes": (c_size_t, [I, I, I, I, I]),
@@ -217,16 +218,28 @@ def linear_fwd_tc(act, packed, partial, nout, C, batch, batch_cap, H, W, stream=
     return s.value
 
 
-def linear_bwd_tc(act, dlogits, packed, dact, dW, nout, C, batch, batch_cap, H, W, stream=None):
-    """Tensor-core linear backward: dact = relu'(act) * dlogits.W, dW = dlogits^T.act (no scratch)."""
-    check(lib().ddpb_linear_bwd_tc(ptr(act), ptr(dlogits), ptr(packed), ptr(dact), ptr(dW), nout, C,
+def linear_bwd_tc(act, dl_packed, packed, dact, dW, nout, C, batch, batch_cap, H, W, stream=None):
+    """Tensor-core linear backward: dact = relu'(act) * dlogits.W, dW = dlogits^T.act (no scratch).
+    ``dl_packed`` is the tile buffer written by softmax_xent(dl_packed=...)."""
+    check(lib().ddpb_linear_bwd_tc(ptr(act), ptr(dl_packed), ptr(packed), ptr(dact), ptr(dW), nout, C,
                                    batch, batch_cap, H, W, stream_ptr(stream)), "linear_bwd_tc")
 
 
-def softmax_xent(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch, stream=None):
-    check(lib().ddpb_softmax_xent(ptr(partial), S, ptr(bias), ptr(labels), ptr(logits),
-                                  ptr(dlogits), ptr(dbias), ptr(loss), nout, batch,
-                                  stream_ptr(stream)), "softmax_xent")
+def dl_packed_bytes(batch_cap: int) -> int:
+    """Size of the bf16 hi/lo dlogits tile buffer softmax_xent(dl_packed=...) writes."""
+    return (batch_cap + 127) // 128 * 128 * 64
+
+
+def softmax_xent(partial, S, bias, labels, logits, dlogits, dbias, loss, nout, batch, stream=None,
+                 dl_packed=None):
+    if dl_packed is None:
+        check(lib().ddpb_softmax_xent(ptr(partial), S, ptr(bias), ptr(labels), ptr(logits),
+                                      ptr(dlogits), ptr(dbias), ptr(loss), nout, batch,
+                                      stream_ptr(stream)), "softmax_xent")
+    else:
+        check(lib().ddpb_softmax_xent_packed(ptr(partial), S, ptr(bias), ptr(labels), ptr(logits),
+                                             ptr(dlogits), ptr(dbias), ptr(loss), nout, batch,
+                                             ptr(dl_packed), stream_ptr(stream)), "softmax_xent_packed")
 
 
 def linear_bwd_scratch_bytes(nout, C, batch_cap, H, W) -> int:

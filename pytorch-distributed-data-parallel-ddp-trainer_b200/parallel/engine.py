@@ -101,8 +101,13 @@ class B200DataParallel(_EngineBase):
         self.model = SimpleCNNB200(batch_cap, self.device, params=params, grads=grads[0],
                                    alt_grads=grads[1])
         self.model.lr_dev.fill_(self.lr)
-        # bucket slices rounded to whole float4 (the arena tail is zero padding)
-        self.buckets = [(b.start, _align(b.numel, 4)) for b in self.model.buckets()]
+        # gradient buckets = contiguous arena slices (whole float4; the arena tail is zero padding),
+        # one per point of the backward pass at which a group of gradients becomes complete
+        a = self.model.arena
+        self.bucket_fl = self._slice(a, ("fl.weight", "fl.bias"))
+        self.bucket_conv2 = self._slice(a, ("net.2.weight", "net.2.bias"))
+        self.bucket_conv1 = self._slice(a, ("net.0.weight", "net.0.bias"))
+        self.buckets = [self.bucket_fl, self.bucket_conv2, self.bucket_conv1]
         assert all(s % 4 == 0 and s + m <= n for s, m in self.buckets)
 
         self.main = torch.cuda.Stream(self.device)
@@ -124,6 +129,11 @@ class B200DataParallel(_EngineBase):
         self.sync_params()
 
     # ------------------------------------------------------------------ parameters
+    @staticmethod
+    def _slice(arena, names):
+        start, numel = arena.slice_of(names)
+        return start, _align(numel, 4)
+
     @property
     def flat_params(self) -> torch.Tensor:
         return self.model.arena.params
@@ -142,42 +152,44 @@ class B200DataParallel(_EngineBase):
 
     # ------------------------------------------------------------------ the step
     def launches_per_step(self, batch: int) -> int:
-        return self.model.launches_per_step(batch) + 3  # two bucket updates + weight re-pack
+        return self.model.launches_per_step(batch) + 4  # three bucket updates + weight re-pack
+
+    def _update(self, bucket, parity: int, slot: int, stream) -> None:
+        """Fused all-reduce + 1/W + SGD of one gradient bucket (plain SGD kernel when W == 1)."""
+        m = self.model
+        start, n = bucket
+        if self.world_size > 1:
+            goff = self.grad_off[parity]
+            self.comm.allreduce_sgd(goff + start * 4, self.param_off + start * 4, n, m.lr_dev,
+                                    self.algo, slot=slot, stream=stream)
+        else:
+            m.nat.sgd(m.arena.params[start:start + n], m.grad_sets[parity]["flat"][start:start + n],
+                      m.lr_dev, stream)
 
     def _enqueue(self, b: int, parity: int) -> None:
-        """Enqueue one full training step; capturable.  Stream plan:
+        """Enqueue one full training step; capturable.  Stream plan (each update is launched as
+        soon as its gradients are complete, so only the tiny conv1 bucket is left at the end):
 
-            main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad | bucket-1 update
-            side : (after linear bwd)    bucket-0 all-reduce+SGD      (overlaps the conv backward)
-            side2: (after linear bwd)    conv2 wgrad                  (independent of the dgrad chain)
+            main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad -> update {net.0.*}
+            side : (after linear bwd)    update {fl.*} -> re-pack fl.weight tiles
+            side2: (after linear bwd)    conv2 wgrad -> update {net.2.*}
         """
         m, main = self.model, self.main
         x, y = self.x_in[parity][:b], self.y_in[parity][:b]
-        (s0, n0), (s1, n1) = self.buckets
-        gflat = m.grad_sets[parity]["flat"]
         m.forward_loss(x, y, b, main, parity, pack=False)
         m.backward_head(b, main, parity)
         self._ev_fork.record(main)
         self.side.wait_event(self._ev_fork)
         self.side2.wait_event(self._ev_fork)
-        # bucket 0 (fl.weight, fl.bias) is complete: update it while the conv backward runs
-        if self.world_size > 1:
-            goff = self.grad_off[parity]
-            self.comm.allreduce_sgd(goff + s0 * 4, self.param_off + s0 * 4, n0, m.lr_dev,
-                                    self.algo, slot=0, stream=self.side)
-        else:
-            m.nat.sgd(m.arena.params[s0:s0 + n0], gflat[s0:s0 + n0], m.lr_dev, self.side)
-        m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step, off the critical path
+        self._update(self.bucket_fl, parity, 0, self.side)
+        m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
         m.backward_conv2_wgrad(b, self.side2, parity)
+        self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
         m.backward_dgrad_conv1(x, b, main, parity)
+        self._update(self.bucket_conv1, parity, 1, main)
         main.wait_event(self._ev_join2)
-        if self.world_size > 1:
-            self.comm.allreduce_sgd(goff + s1 * 4, self.param_off + s1 * 4, n1, m.lr_dev,
-                                    self.algo, slot=1, stream=main)
-        else:
-            m.nat.sgd(m.arena.params[s1:s1 + n1], gflat[s1:s1 + n1], m.lr_dev, main)
         main.wait_event(self._ev_join)
 
     def acquire_inputs(self):

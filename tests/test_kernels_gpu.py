@@ -246,22 +246,32 @@ def test_linear_bwd_tcgen05(nat, batch, cap):
     K = C * H * W
     act = torch.relu(torch.randn(batch, C, H, W, device="cuda"))
     Wfl = torch.randn(10, K, device="cuda") * 0.01
-    dl = torch.randn(batch, 10, device="cuda") * (0.1 / batch)
+    bfl = torch.randn(10, device="cuda") * 0.1
+    y = torch.randint(0, 10, (batch,), device="cuda")
     act_p = _lay().nchw_to_planes(act, cap)
     packed = torch.empty(nat.linear_pack_bytes(10, C, H, W), dtype=torch.uint8, device="cuda")
     nat.linear_pack(Wfl, packed, 10, C, H, W)
+    # dlogits (fp32 and the packed bf16 hi/lo tiles) come from the loss kernel
+    part = nat.scratch(nat.linear_fwd_tc_scratch_bytes(10, C, cap, H, W))
+    S = nat.linear_fwd_tc(act_p, packed, part, 10, C, batch, cap, H, W)
+    logits = torch.zeros(batch, 10, device="cuda")
+    dl = torch.zeros(batch, 10, device="cuda")
+    dbias = torch.zeros(10, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    dlp = torch.full((nat.dl_packed_bytes(cap),), 0x7f, dtype=torch.uint8, device="cuda")  # garbage
+    nat.softmax_xent(part, S, bfl, y, logits, dl, dbias, loss, 10, batch, dl_packed=dlp)
     dact = nat.alloc_planes(C, cap, H, W)
     lay = _lay()
     first = lay.GUARD + batch * 900
     last = lay.GUARD + lay.tiles_for(batch, H, W) * 128
     dact[:, first:last] = 7.0
     dW = torch.full((10, K), float("nan"), device="cuda")
-    nat.linear_bwd_tc(act_p, dl, packed, dact, dW, 10, C, batch, cap, H, W)
+    nat.linear_bwd_tc(act_p, dlp, packed, dact, dW, 10, C, batch, cap, H, W)
     torch.cuda.synchronize()
     a = _bf(act).reshape(batch, K)
     want_dW = dl.t() @ a
     _report("dW_fl (tensor cores)", dW, want_dW, 2e-3 * want_dW.abs().max().item() + 1e-8, 2e-3)
-    want_dact = ((dl @ _bf(Wfl)).reshape(batch, C, H, W)) * (_bf(act) > 0)
+    want_dact = ((dl @ Wfl).reshape(batch, C, H, W)) * (_bf(act) > 0)
     got_dact = lay.planes_to_nchw(dact, batch, C, H, W)
     _report("dact2 (tensor cores)", got_dact, want_dact, 1e-2 * want_dact.abs().max().item(), 1e-2)
     assert (dact[:, first:last].float() == 0).all()

@@ -42,6 +42,7 @@ def test_training_tracks_oracle_and_short_batches(cuda, use_graph):
     oracle = SimpleCNN(device=cuda)
     eng = B200DataParallel(0, 1, cuda, batch_cap=32, lr=0.05, use_graph=use_graph)
     eng.model.load_state_dict(oracle.state_dict())
+    init = {n: oracle.arena.view(n).detach().clone() for n in ("fl.weight", "net.2.weight", "net.0.weight")}
     torch.manual_seed(2)
     xs = torch.rand(8, 32, 1, 28, 28, device=cuda)
     ys = torch.randint(0, 10, (8, 32), device=cuda)
@@ -58,9 +59,12 @@ def test_training_tracks_oracle_and_short_batches(cuda, use_graph):
     for a, b in zip(losses_o, losses_g):
         assert abs(a - b) < 2e-2 * max(1.0, abs(a)), (losses_o, losses_g)
     assert losses_g[-1] < losses_g[0]
+    # the accumulated parameter UPDATE of the bf16/tf32 tensor-core path must stay within a few
+    # percent of the fp32 oracle's update (an absolute bound would depend on gradient magnitudes)
     for name in ("fl.weight", "net.2.weight", "net.0.weight"):
         p, q = eng.model.arena.view(name), oracle.arena.view(name).detach()
-        assert (p - q).abs().max().item() < 5e-3, name
+        rel = ((p - q).norm() / (q - init[name]).norm()).item()
+        assert rel < 5e-2, (name, rel, (p - q).abs().max().item())
     eng.close()
 
 
