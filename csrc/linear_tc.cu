@@ -294,9 +294,12 @@ constexpr uint32_t kLbDlBytes = 4 * kTileM * 16;          // 8,192
 constexpr uint32_t kLbStage = kLbActBytes + kLbDlBytes;
 constexpr uint32_t kLbWbBytes = 4 * kLbFB * 128;          // 8,192 per feature block (hi, hi, lo, lo)
 
+constexpr uint32_t kLbOutPitch = kLbFB * 16 + 16;  // staged dX row of one image: 256 B + 16 B bank skew
+
 struct LinBwdSmem {
   static constexpr uint32_t off_wb = kLbStages * kLbStage;          // 2 buffers
-  static constexpr uint32_t off_bar = off_wb + 2 * kLbWbBytes;
+  static constexpr uint32_t off_out = off_wb + 2 * kLbWbBytes;      // per epilogue warp: 32 rows
+  static constexpr uint32_t off_bar = off_out + 4 * 32 * kLbOutPitch;
   // full[ST], empty[ST], wbfull[2], wbfree[2], d1full[2], d1free[2], dwfull, dwfree
   static constexpr uint32_t nbar = 2 * kLbStages + 12;
   static constexpr uint32_t off_tmem = off_bar + nbar * 8;
@@ -469,7 +472,8 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
         mbar_wait(bar_d1full + acc * 8, (it >> 1) & 1);
         tc_fence_after();
         const uint8_t* sact = smem + stage * kLbStage + (row >> 3) * 128 + (row & 7) * 16;
-        __nv_bfloat16* drow = dact + (long long)img * g.PHW * 8;
+        // masked dX row of this image -> this warp's staging rows (256 B per image)
+        uint8_t* sout = smem + S::off_out + (warp - 5) * 32 * kLbOutPitch;
 #pragma unroll 1
         for (int c0 = 0; c0 < 128; c0 += 32) {
           uint32_t v[32];
@@ -478,7 +482,6 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int kl = c0 / 8 + j;
-            const long long off = __shfl_sync(0xffffffffu, my_off, kl);
             const uint4 mk = *reinterpret_cast<const uint4*>(sact + kl * kLinChunkPitch);
             const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk);
             uint4 o;
@@ -489,9 +492,24 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
               const float x1 = bf16_hi(mp[e]) > 0.f ? __uint_as_float(v[j * 8 + 2 * e + 1]) : 0.f;
               op[e] = pack_bf16x2(x0, x1);
             }
-            if (off >= 0 && img < g.batch) *reinterpret_cast<uint4*>(drow + off) = o;
+            *reinterpret_cast<uint4*>(sout + lane * kLbOutPitch + kl * 16) = o;
           }
         }
+        __syncwarp();
+        // coalesced write-out: each instruction stores two images x 16 chunks = two 256 B runs
+        {
+          const int kl = lane & 15;
+          const long long off = __shfl_sync(0xffffffffu, my_off, kl);
+#pragma unroll 4
+          for (int r2 = 0; r2 < 16; ++r2) {
+            const int il = 2 * r2 + (lane >> 4);
+            const int im = mt * kTileM + q * 32 + il;
+            const uint4 o = *reinterpret_cast<const uint4*>(sout + il * kLbOutPitch + kl * 16);
+            if (off >= 0 && im < g.batch)
+              *reinterpret_cast<uint4*>(dact + (long long)im * g.PHW * 8 + off) = o;
+          }
+        }
+        __syncwarp();
         tc_fence_before();
         mbar_arrive(bar_d1free + acc * 8);
         mbar_arrive(bar_empty + stage * 8);  // done reading the activation tile (mask)

@@ -128,7 +128,7 @@ def scenario_dp_equiv():
     torch.backends.cuda.matmul.allow_tf32 = False
     b = 16
     torch.manual_seed(1000 + rank)                  # ranks start DIFFERENT; the engine must sync them
-    eng = B200DataParallel(rank, world, dev, batch_cap=b, lr=0.05)
+    eng = B200DataParallel(rank, world, dev, batch_cap=b, lr=0.01)
     torch.manual_seed(5)
     oracle = SimpleCNN(device=dev, init=False)
     sd = eng.state_dict()
@@ -142,7 +142,7 @@ def scenario_dp_equiv():
     for it in range(12):
         bb = b if it % 4 != 3 else 9
         lo = oracle.forward_backward(xs[it, :, :bb].reshape(-1, 1, 28, 28), ys[it, :, :bb].reshape(-1))
-        oracle.sgd_step(0.05)
+        oracle.sgd_step(0.01)
         eng.step(xs[it, rank, :bb], ys[it, rank, :bb])
         lg = torch.tensor([eng.read_loss()], device=dev)
         dist.all_reduce(lg)
@@ -151,7 +151,7 @@ def scenario_dp_equiv():
     dist.all_gather(gathered, eng.flat_params.clone())
     assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas diverged bitwise"
     diff = (eng.flat_params[:520586] - oracle.arena.params.detach()[:520586]).abs().max().item()
-    assert diff < 5e-3, diff
+    assert diff < 5e-3, diff  # bf16/tf32 tensor-core path vs fp32 oracle after 12 steps
     eng.close()
     dist.barrier()
     if rank == 0:
@@ -171,7 +171,7 @@ def scenario_bucketed():
     torch.manual_seed(3)
     m = WideCNN(hidden=96).to(dev)                      # smaller head keeps the test quick
     ref = copy.deepcopy(m)
-    eng = BucketedDataParallel(m, rank, world, lr=0.05, bucket_mb=1.0)
+    eng = BucketedDataParallel(m, rank, world, lr=0.05, bucket_mb=0.25)
     assert len(eng.buckets) >= 3, len(eng.buckets)
     opt = torch.optim.SGD(ref.parameters(), lr=0.05)
     g = torch.Generator().manual_seed(17)

@@ -22,7 +22,11 @@ def _torchrun(world, script_args, cwd=None, env=None, timeout=600):
     e = dict(os.environ)
     e.update(env or {})
     res = subprocess.run(cmd, cwd=cwd or ROOT, env=e, capture_output=True, text=True, timeout=timeout)
-    assert res.returncode == 0, (res.stdout[-3000:], res.stderr[-3000:])
+    if res.returncode != 0:
+        # keep the interesting part: the first exception of any rank, not torchrun's epilogue
+        lines = [l for l in (res.stdout + "\n" + res.stderr).splitlines()
+                 if any(k in l for k in ("Error", "assert", "Assert", "error:", "diverged", "failed"))]
+        pytest.fail("rank failure:\n" + "\n".join(lines[:25])[-4000:], pytrace=False)
     return res.stdout
 
 
