@@ -40,8 +40,13 @@ constexpr int kSlots = 8;
 constexpr int kMaxBlocks = 160;
 constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * kMaxWorld;
 constexpr size_t kEpochWords = (size_t)kSlots * kMaxBlocks;
-// header: flags | epochs | status word, rounded up
-constexpr size_t kHeaderBytes = ((kFlagWords + kEpochWords + 64) * 4 + 4095) / 4096 * 4096;
+// Flag-carrying ("LL") staging lines for the latency-bound tiny buckets: per slot, two epochs
+// (double buffer) x source rank x kLLMaxN 8-byte {epoch, fp32 payload} words.
+constexpr int kLLMaxN = 32 * kMaxBlocks;
+constexpr size_t kLLWordsPerSlot = 2ull * kMaxWorld * kLLMaxN;
+constexpr size_t kLLOffset = ((kFlagWords + kEpochWords + 64) * 4 + 255) / 256 * 256;
+// header: flags | epochs | status word | LL lines, rounded up
+constexpr size_t kHeaderBytes = (kLLOffset + (size_t)kSlots * kLLWordsPerSlot * 8 + 4095) / 4096 * 4096;
 constexpr int kCommThreads = 512;
 
 struct Comm {
@@ -66,6 +71,10 @@ __device__ __forceinline__ uint32_t* epoch_word(uint8_t* base, int slot, int blo
 }
 __device__ __forceinline__ uint32_t* status_word(uint8_t* base) {
   return reinterpret_cast<uint32_t*>(base) + kFlagWords + kEpochWords;
+}
+__device__ __forceinline__ uint64_t* ll_line(uint8_t* base, int slot, uint32_t epoch, int src) {
+  return reinterpret_cast<uint64_t*>(base + kLLOffset) +
+         ((size_t)slot * 2 + (epoch & 1)) * kMaxWorld * kLLMaxN + (size_t)src * kLLMaxN;
 }
 
 // One flag round for this block: tell every peer "block `blockIdx.x` of rank `rank` reached
@@ -114,7 +123,7 @@ __device__ __forceinline__ void st_f4(float* p, const float4& v) {
 // n4 = number of float4 elements in the bucket (buckets are 16-byte aligned slices).
 template <int WORLD>
 __global__ void __launch_bounds__(kCommThreads)
-allreduce_sgd_oneshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
+allreduce_sgd_oneshot_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
                              long long n4, const float* __restrict__ lr,
                              unsigned long long timeout_ns) {
   pdl_sync();
@@ -146,7 +155,7 @@ allreduce_sgd_oneshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, s
 
 template <int WORLD>
 __global__ void __launch_bounds__(kCommThreads)
-allreduce_sgd_twoshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
+allreduce_sgd_twoshot_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, size_t grad_off, size_t param_off,
                              long long n4, const float* __restrict__ lr,
                              unsigned long long timeout_ns) {
   pdl_sync();
@@ -182,6 +191,135 @@ allreduce_sgd_twoshot_kernel(PeerPtrs pp, int rank, int slot, size_t grad_off, s
   if (threadIdx.x == 0) *ep = e + 1;
 }
 
+// ---------------------------------------------------------------- split-K reduce + all-reduce + SGD
+// The last gradient bucket of the step (conv1, 320 floats) sits on the critical path, and its
+// gradients come out of the tensor-core kernel as one partial per CTA.  This kernel does, in one
+// launch: (1) the fixed-order sum of the local partials, (2) publishes the local gradient in the
+// peer-mapped arena, (3) the flag round, (4) the rank-ordered sum over all peers' gradients and
+// (5) the SGD update — compute + collective + optimizer, no intermediate kernels.
+// 256 threads = 32 consecutive outputs x 8 partial groups; one block per 32 outputs.
+template <int WORLD>
+__global__ void __launch_bounds__(256)
+reduce_allreduce_sgd_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, const float* __restrict__ partials,
+                            int nparts, int n, size_t grad_off, size_t param_off,
+                            const float* __restrict__ lr, unsigned long long timeout_ns) {
+  __shared__ float sm[8][32];
+  pdl_sync();
+  const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
+  const int idx = blockIdx.x * 32 + lane;
+  float s = 0.f;
+  if (idx < n) {
+    int p = pg;
+    for (; p + 24 < nparts; p += 32) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = partials[(long long)(p + 8 * u) * n + idx];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s += v[u];
+    }
+    for (; p < nparts; p += 8) s += partials[(long long)p * n + idx];
+  }
+  sm[pg][lane] = s;
+  __syncthreads();
+  float* my_grads = reinterpret_cast<float*>(pp.p[rank] + grad_off);
+  if (pg == 0 && idx < n) {
+#pragma unroll
+    for (int u = 1; u < 8; ++u) s += sm[u][lane];
+    my_grads[idx] = s;
+  }
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  if (threadIdx.x < 8) {
+    const int i4 = blockIdx.x * 8 + threadIdx.x;  // float4 index
+    if (i4 * 4 < n) {
+      const float scale = -(*lr) * (1.0f / WORLD);
+      float4 acc = ld_f4(reinterpret_cast<const float*>(pp.p[0] + grad_off) + i4 * 4);
+#pragma unroll
+      for (int r = 1; r < WORLD; ++r) {
+        const float4 v = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i4 * 4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      float4* pr = reinterpret_cast<float4*>(pp.p[rank] + param_off) + i4;
+      float4 p = *pr;
+      p.x = fmaf(scale, acc.x, p.x);
+      p.y = fmaf(scale, acc.y, p.y);
+      p.z = fmaf(scale, acc.z, p.z);
+      p.w = fmaf(scale, acc.w, p.w);
+      *pr = p;
+    }
+  }
+  if (threadIdx.x == 0) *ep = e;
+}
+
+// Same operation, push-based with flag-carrying words (the idea of NCCL's LL protocol): every
+// rank writes {epoch, value} 8-byte words straight into each peer's staging line for this epoch
+// and then polls its own lines.  No fence, no separate flag, no remote load: the critical path
+// is one one-way NVLink store latency instead of a flag hop plus a remote-load round trip.
+// Staging lines are double-buffered by epoch parity; a rank can only be one call ahead of a peer
+// (call e+1 cannot finish without that peer's words of e+1, which the peer sends after it has
+// finished reading e), so a line is never overwritten while it is still being read.
+template <int WORLD>
+__global__ void __launch_bounds__(256)
+reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, const float* __restrict__ partials,
+                               int nparts, int n, size_t grad_off, size_t param_off,
+                               const float* __restrict__ lr, unsigned long long timeout_ns) {
+  __shared__ float sm[8][32];
+  pdl_sync();
+  const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
+  const int idx = blockIdx.x * 32 + lane;
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  float s = 0.f;
+  if (idx < n) {
+    int p = pg;
+    for (; p + 24 < nparts; p += 32) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = partials[(long long)(p + 8 * u) * n + idx];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s += v[u];
+    }
+    for (; p < nparts; p += 8) s += partials[(long long)p * n + idx];
+  }
+  sm[pg][lane] = s;
+  __syncthreads();
+  // every warp forms the same fixed-order total; warp r sends it to rank r
+  float tot = sm[0][lane];
+#pragma unroll
+  for (int u = 1; u < 8; ++u) tot += sm[u][lane];
+  if (pg < WORLD && idx < n)
+    st_relaxed_sys_u64(ll_line(pp.p[pg], slot, e, rank) + idx,
+                       (static_cast<uint64_t>(e) << 32) | __float_as_uint(tot));
+  if (pg == 0 && idx < n) reinterpret_cast<float*>(pp.p[rank] + grad_off)[idx] = tot;
+  __syncthreads();  // sm is reused below
+  if (pg < WORLD && idx < n) {
+    const uint64_t* src = ll_line(pp.p[rank], slot, e, pg) + idx;
+    uint64_t v = ld_relaxed_sys_u64(src);
+    if (static_cast<uint32_t>(v >> 32) != e) {
+      const uint64_t t0 = global_timer_ns();
+      uint32_t spins = 0;
+      while (static_cast<uint32_t>((v = ld_relaxed_sys_u64(src)) >> 32) != e) {
+        if ((++spins & 0xff) == 0 && global_timer_ns() - t0 > timeout_ns) {
+          *status_word(pp.p[rank]) = 0xdead0000u | static_cast<uint32_t>(pg);
+          __threadfence_system();
+          __trap();
+        }
+      }
+    }
+    sm[pg][lane] = __uint_as_float(static_cast<uint32_t>(v));
+  }
+  __syncthreads();
+  if (pg == 0 && idx < n) {
+    float acc = sm[0][lane];
+#pragma unroll
+    for (int r = 1; r < WORLD; ++r) acc += sm[r][lane];
+    float* pr = reinterpret_cast<float*>(pp.p[rank] + param_off) + idx;
+    *pr = fmaf(-(*lr) * (1.0f / WORLD), acc, *pr);
+  }
+  if (threadIdx.x == 0) *ep = e;
+}
+
 // ---------------------------------------------------------------- plain all-reduce (sum)
 template <typename T>
 struct Vec16;
@@ -211,7 +349,7 @@ struct Vec16<__nv_bfloat16> {
 // mode 1: two-shot (rank r reduces slice r and stores it into every rank's `out`)
 template <typename T, int WORLD, int MODE>
 __global__ void __launch_bounds__(kCommThreads)
-allreduce_kernel(PeerPtrs pp, int rank, int slot, size_t in_off, size_t out_off, long long nvec,
+allreduce_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, size_t in_off, size_t out_off, long long nvec,
                  unsigned long long timeout_ns) {
   uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
   const uint32_t e = *ep + 1;
@@ -247,7 +385,7 @@ allreduce_kernel(PeerPtrs pp, int rank, int slot, size_t in_off, size_t out_off,
 // Every rank copies root's region into its own buffer (pull), bracketed by flag rounds.
 template <int WORLD>
 __global__ void __launch_bounds__(kCommThreads)
-broadcast_kernel(PeerPtrs pp, int rank, int slot, int root, size_t off, long long nvec,
+broadcast_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, int root, size_t off, long long nvec,
                  unsigned long long timeout_ns) {
   uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
   const uint32_t e = *ep + 1;
@@ -262,12 +400,14 @@ broadcast_kernel(PeerPtrs pp, int rank, int slot, int root, size_t off, long lon
   if (threadIdx.x == 0) *ep = e + 1;
 }
 
+// Remote loads over NVLink cost ~4-5 us of latency per dependent round, so the grid is sized for
+// ONE grid-stride iteration per thread wherever the block cap allows (measured: 2 MB two-shot on
+// 8 GPUs took 43 us with 4 iterations per thread).
 static int blocks_for(long long nvec, int world, bool twoshot) {
   long long work = twoshot ? (nvec + world - 1) / world : nvec;
-  long long b = (work + 4 * kCommThreads - 1) / (4 * kCommThreads);
+  long long b = (work + kCommThreads - 1) / kCommThreads;
   if (b < 1) b = 1;
-  const long long cap = nvec * 16 <= (8ll << 20) ? 48 : kMaxBlocks;
-  if (b > cap) b = cap;
+  if (b > kMaxBlocks) b = kMaxBlocks;
   return static_cast<int>(b);
 }
 
@@ -396,6 +536,36 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
                                        c->timeout_ns));
     return static_cast<int>(launch_k(allreduce_sgd_oneshot_kernel<WORLD>, dim3(blocks),
                                      dim3(kCommThreads), 0, st, pp, c->rank, slot, go, po, n4, lr_dev,
+                                     c->timeout_ns));
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+// grads[slice] = fixed-order sum of `nparts` partial vectors (each n floats, n % 4 == 0), then
+// params[slice] -= lr/world * sum_over_ranks(grads[slice]); one kernel.  n <= 32 * kMaxBlocks.
+// algo: 0 or 3 = push with flag-carrying words (lowest latency), 1 = flag round + pull.
+int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
+                              size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                              int slot, void* stream) {
+  Comm* c = static_cast<Comm*>(comm);
+  if (!c->connected) return DDPB_ERR_STATE;
+  const long long blocks = (n + 31) / 32;
+  if ((n & 3) || (grad_off & 15) || (param_off & 15) || slot < 0 || slot >= kSlots || nparts < 1 ||
+      !(algo == 0 || algo == 1 || algo == 3))
+    return DDPB_ERR_SHAPE;
+  if (blocks > kMaxBlocks) return DDPB_ERR_LIMIT;
+  const PeerPtrs pp = peer_ptrs(c);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t go = grad_off + kHeaderBytes, po = param_off + kHeaderBytes;
+  DDPB_DISPATCH_WORLD(c->world, {
+    if (algo == 1)
+      return static_cast<int>(launch_k(reduce_allreduce_sgd_kernel<WORLD>,
+                                       dim3(static_cast<int>(blocks)), dim3(256), 0, st, pp, c->rank,
+                                       slot, partials, nparts, static_cast<int>(n), go, po, lr_dev,
+                                       c->timeout_ns));
+    return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD>,
+                                     dim3(static_cast<int>(blocks)), dim3(256), 0, st, pp, c->rank,
+                                     slot, partials, nparts, static_cast<int>(n), go, po, lr_dev,
                                      c->timeout_ns));
   });
   return static_cast<int>(cudaGetLastError());

@@ -400,9 +400,30 @@ size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout) {
 
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
 
+static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratch, int* nparts, int cin,
+                                 int cout, int batch, int batch_cap, int H, int W, void* stream);
+
+// Partials only: scratch[nparts][cout*cin*9 + cout]; *nparts_out (host) receives the partial count.
+// Feed them to ddpb_reduce_allreduce_sgd (fused split-K reduce + all-reduce + SGD).
+int ddpb_conv1_wgrad_tc_partials(const void* dact, const float* x, float* scratch, int* nparts_out,
+                                 int cin, int cout, int batch, int batch_cap, int H, int W,
+                                 void* stream) {
+  return conv1_wgrad_tc_launch(dact, x, scratch, nparts_out, cin, cout, batch, batch_cap, H, W, stream);
+}
+
 // dw_db: cout*cin*9 weight gradients immediately followed by cout bias gradients.
 int ddpb_conv1_wgrad_tc(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
                         int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  int grid = 0;
+  const int rc = conv1_wgrad_tc_launch(dact, x, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
+  if (rc != 0) return rc;
+  return ddpb_reduce_partials(scratch, grid, (long long)cout * cin * 9 + cout, dw_db, stream);
+}
+
+}  // extern "C"
+
+static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratch, int* nparts, int cin,
+                                 int cout, int batch, int batch_cap, int H, int W, void* stream) {
   if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
   if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
@@ -419,7 +440,6 @@ int ddpb_conv1_wgrad_tc(const void* dact, const float* x, float* dw_db, float* s
   DDPB_CUDA_OK(launch_k(conv1_wgrad_tc_kernel, dim3(grid), dim3(kC1Threads), C1WgradSmem::total,
                         static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dact), x,
                         scratch, g));
-  return ddpb_reduce_partials(scratch, grid, (long long)cout * cin * 9 + cout, dw_db, stream);
+  *nparts = grid;
+  return 0;
 }
-
-}  // extern "C"

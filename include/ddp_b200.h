@@ -68,6 +68,11 @@ int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out_
 size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout);
 int ddpb_conv1_wgrad_tc(const void* dact_planes, const float* x, float* dw_db, float* scratch,
                         int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+/* Same kernel, but the split-K partials stay in scratch[nparts][cout*cin*9 + cout] and *nparts_out
+ * (host) receives their count: feed them to ddpb_reduce_allreduce_sgd. */
+int ddpb_conv1_wgrad_tc_partials(const void* dact_planes, const float* x, float* scratch,
+                                 int* nparts_out, int cin, int cout, int batch, int batch_cap, int H,
+                                 int W, void* stream);
 /* out[i] = sum_p part[p*n + i], fixed order. */
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
 
@@ -157,6 +162,14 @@ int ddpb_comm_destroy(void* comm);
 /* params[slice] -= lr/world * sum_over_ranks(grads[slice]) in ONE kernel (in-kernel flags). */
 int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long n_floats,
                        const float* lr_dev, int algo, int slot, void* stream);
+/* Split-K reduce + all-reduce + SGD in ONE kernel for a latency-bound bucket (n <= 5120 floats,
+ * n % 4 == 0): grads[slice] = fixed-order sum of nparts local partial vectors of n floats, then
+ * params[slice] -= lr/world * sum_over_ranks(grads[slice]).  algo 0/3 = push exchange (8-byte
+ * {epoch, value} words stored straight into the peers' staging lines, one one-way NVLink latency),
+ * 1 = flag round followed by peer loads. */
+int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
+                              size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                              int slot, void* stream);
 /* plain sum all-reduce, dtype 0 = fp32, 1 = bf16; out_off must not overlap in_off. */
 int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, int dtype, int algo,
                    int slot, void* stream);

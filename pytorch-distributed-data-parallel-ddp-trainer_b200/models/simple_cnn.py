@@ -225,6 +225,13 @@ class SimpleCNNB200(_ModelBase):
         nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
         nat.conv1_wgrad_tc(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
 
+    def backward_dgrad_conv1_partials(self, x: torch.Tensor, batch: int, stream=None) -> int:
+        """Like backward_dgrad_conv1 but leaves the conv1 gradient as per-CTA partials in
+        ``self.scr_w1`` (returns their count) for the fused reduce + all-reduce + SGD kernel."""
+        nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
+        nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
+        return nat.conv1_wgrad_tc_partials(self.dact1, x, self.scr_w1, 1, C1, batch, cap, H, W, stream)
+
     def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""
         self.backward_conv2_wgrad(batch, stream, parity)
@@ -242,8 +249,9 @@ class SimpleCNNB200(_ModelBase):
         """Kernels one forward+backward launches (bench.py reports it as part of gpu_launches)."""
         from ..ops import layout as lay
         tail = 1 if lay.tiles_for(batch, IMG_H, IMG_W) * lay.TILE_M > batch * 900 else 0
-        # conv1, conv2, linear, loss | (tail zero) linear bwd | wgrad+reduce, dgrad, conv1 wgrad+reduce
-        return 4 + (1 + tail) + 2 + 1 + 2
+        # conv1, conv2, linear, loss | (tail zero) linear bwd | wgrad+reduce, dgrad, conv1 wgrad
+        # (its split-K reduce is fused into the bucket update kernel)
+        return 4 + (1 + tail) + 2 + 1 + 1
 
     def sgd_step(self, lr: float | None = None, stream=None) -> None:
         if lr is not None:

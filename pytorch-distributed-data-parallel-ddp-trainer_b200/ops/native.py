@@ -36,6 +36,7 @@ _SIGNATURES = {
     "ddpb_conv1_fwd_tc": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv1_wgrad_tc_scratch_bytes": (c_size_t, [I, I]),
     "ddpb_conv1_wgrad_tc": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_tc_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_conv3x3_fwd": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_wgrad_scratch_bytes": (c_size_t, [I, I]),
@@ -164,6 +165,15 @@ def conv1_wgrad_tc_scratch_bytes(cin, cout) -> int:
 def conv1_wgrad_tc(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
     check(lib().ddpb_conv1_wgrad_tc(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
                                     batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad_tc")
+
+
+def conv1_wgrad_tc_partials(dact, x, scr, cin, cout, batch, batch_cap, H, W, stream=None) -> int:
+    """Per-CTA partial gradients only (scr[nparts][cout*cin*9 + cout]); returns nparts."""
+    n = c_int(0)
+    check(lib().ddpb_conv1_wgrad_tc_partials(ptr(dact), ptr(x), ptr(scr), ctypes.byref(n), cin, cout,
+                                             batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv1_wgrad_tc_partials")
+    return n.value
 
 
 def conv3x3_fwd(inp, w, bias, out, batch, batch_cap, H, W, stream=None):

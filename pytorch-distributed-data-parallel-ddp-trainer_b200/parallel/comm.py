@@ -35,12 +35,13 @@ for _name, _res, _args in (
     ("ddpb_comm_status", I, [P, POINTER(c_uint)]),
     ("ddpb_comm_destroy", I, [P]),
     ("ddpb_allreduce_sgd", I, [P, SZ, SZ, LL, P, I, I, P]),
+    ("ddpb_reduce_allreduce_sgd", I, [P, P, I, LL, SZ, SZ, P, I, I, P]),
     ("ddpb_allreduce", I, [P, SZ, SZ, LL, I, I, I, P]),
     ("ddpb_broadcast", I, [P, SZ, LL, I, I, P]),
 ):
     nat.declare(_name, _res, _args)
 
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH = 0, 1, 2, 3
 DTYPE_CODES = {torch.float32: 0, torch.bfloat16: 1}
 
 
@@ -93,6 +94,17 @@ class SymmetricComm:
         nat.check(self.lib.ddpb_allreduce_sgd(self._h, grad_off, param_off, n_floats,
                                               nat.ptr(lr_dev), algo, slot, nat.stream_ptr(stream)),
                   "allreduce_sgd")
+
+    def reduce_allreduce_sgd(self, partials: torch.Tensor, nparts: int, n_floats: int, grad_off: int,
+                             param_off: int, lr_dev: torch.Tensor, algo: int = ALGO_AUTO,
+                             slot: int = 0, stream=None) -> None:
+        """One kernel: grads[slice] = sum of ``nparts`` local partial vectors (fixed order), then
+        params[slice] -= lr * mean_over_ranks(grads[slice]).  ``algo``: ALGO_PUSH (default; every
+        rank stores flag-carrying words straight into its peers' staging lines) or ALGO_ONESHOT
+        (flag round, then pull)."""
+        nat.check(self.lib.ddpb_reduce_allreduce_sgd(self._h, nat.ptr(partials), nparts, n_floats,
+                                                     grad_off, param_off, nat.ptr(lr_dev), algo, slot,
+                                                     nat.stream_ptr(stream)), "reduce_allreduce_sgd")
 
     def allreduce(self, in_off: int, out_off: int, nbytes: int, dtype=torch.float32,
                   algo: int = ALGO_AUTO, slot: int = 0, stream=None) -> None:

@@ -75,7 +75,12 @@ class CpuDataParallel(_EngineBase):
 
 class B200DataParallel(_EngineBase):
     def __init__(self, rank: int, world_size: int, device, batch_cap: int, lr: float = 0.01,
-                 use_graph: bool = True, algo: int = 0, timeout_ms: int | None = None):
+                 use_graph: bool = True, algo: int = 0, timeout_ms: int | None = None,
+                 tail_update: str | None = None):
+        """``tail_update`` selects how the last (conv1) bucket of the step is updated:
+        "push" (default) / "pull" = split-K reduce + all-reduce + SGD in one kernel with the push or
+        pull exchange, "split" = separate reduce kernel followed by the generic bucket update.
+        Environment override: DDPB_TAIL_UPDATE."""
         from .comm import SymmetricComm
         self.rank, self.world_size, self.lr = rank, world_size, float(lr)
         self.device = torch.device(device)
@@ -83,8 +88,11 @@ class B200DataParallel(_EngineBase):
         self.batch_cap = int(batch_cap)
         self.use_graph = use_graph
         self.algo = algo
-        # programmatic dependent launch pays off for latency-bound (small-batch) steps only
         import os
+        self.tail_update = tail_update or os.environ.get("DDPB_TAIL_UPDATE", "push")
+        if self.tail_update not in ("push", "pull", "split"):
+            raise ValueError(f"tail_update must be push, pull or split, got {self.tail_update!r}")
+        # programmatic dependent launch pays off for latency-bound (small-batch) steps only
         from ..ops import native as _nat
         if "DDPB_PDL" not in os.environ:
             _nat.lib().ddpb_set_pdl(1 if self.batch_cap <= 512 else 0)
@@ -152,7 +160,8 @@ class B200DataParallel(_EngineBase):
 
     # ------------------------------------------------------------------ the step
     def launches_per_step(self, batch: int) -> int:
-        return self.model.launches_per_step(batch) + 4  # three bucket updates + weight re-pack
+        # three bucket updates + weight re-pack (+ the separate conv1 split-K reduce in "split" mode)
+        return self.model.launches_per_step(batch) + 4 + (1 if self.tail_update == "split" else 0)
 
     def _update(self, bucket, parity: int, slot: int, stream) -> None:
         """Fused all-reduce + 1/W + SGD of one gradient bucket (plain SGD kernel when W == 1)."""
@@ -170,7 +179,7 @@ class B200DataParallel(_EngineBase):
         """Enqueue one full training step; capturable.  Stream plan (each update is launched as
         soon as its gradients are complete, so only the tiny conv1 bucket is left at the end):
 
-            main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad -> update {net.0.*}
+            main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad -> reduce+update {net.0.*} (one kernel)
             side : (after linear bwd)    update {fl.*} -> re-pack fl.weight tiles
             side2: (after linear bwd)    conv2 wgrad -> update {net.2.*}
         """
@@ -187,8 +196,18 @@ class B200DataParallel(_EngineBase):
         m.backward_conv2_wgrad(b, self.side2, parity)
         self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
-        m.backward_dgrad_conv1(x, b, main, parity)
-        self._update(self.bucket_conv1, parity, 1, main)
+        if self.tail_update == "split":
+            m.backward_dgrad_conv1(x, b, main, parity)
+            self._update(self.bucket_conv1, parity, 1, main)
+        else:
+            from .comm import ALGO_ONESHOT, ALGO_PUSH
+            nparts = m.backward_dgrad_conv1_partials(x, b, main)
+            s1, n1 = self.bucket_conv1
+            # split-K reduce of the conv1 partials + all-reduce + 1/W + SGD in ONE kernel: this
+            # bucket is the tail of the step's critical path
+            self.comm.reduce_allreduce_sgd(
+                m.scr_w1, nparts, n1, self.grad_off[parity] + s1 * 4, self.param_off + s1 * 4, m.lr_dev,
+                algo=ALGO_PUSH if self.tail_update == "push" else ALGO_ONESHOT, slot=1, stream=main)
         main.wait_event(self._ev_join2)
         main.wait_event(self._ev_join)
 

@@ -82,6 +82,57 @@ def scenario_fused_sgd():
         for r in range(world):
             assert torch.equal(gathered[r], gathered[0]), f"rank {r} diverged bitwise at it {it}"
         dist.barrier()
+    # split-K reduce + all-reduce + SGD in one kernel (the conv1 bucket path of the engine)
+    from ddp_b200.parallel.comm import ALGO_PUSH
+    n2, nparts = 320, 37
+    p2 = comm.tensor(0, n2)
+    g2 = comm.tensor(region, n2)
+
+    def parts_of(seed, r):
+        return _rank_data(seed, r, nparts * n2, torch.float32, dev).view(nparts, n2).contiguous()
+
+    for ai, algo in enumerate((ALGO_PUSH, ALGO_ONESHOT)):
+        for it in range(3):
+            p2.copy_(_rank_data(50 + it, 0, n2, torch.float32, dev))
+            start = p2.clone()
+            parts = parts_of(200 + it, rank)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.reduce_allreduce_sgd(parts, nparts, n2, region, 0, lr, algo=algo, slot=3 + ai)
+            torch.cuda.synchronize()
+            assert torch.allclose(g2, parts.sum(0), rtol=1e-5, atol=1e-5), "local gradient not published"
+            tot = torch.zeros(n2, device=dev)
+            for r in range(world):
+                tot += parts_of(200 + it, r).sum(0)
+            want2 = start - 0.01 * tot / world
+            assert torch.allclose(p2, want2, rtol=1e-4, atol=1e-4), (algo, it, (p2 - want2).abs().max().item())
+            gathered = [torch.empty_like(p2) for _ in range(world)]
+            dist.all_gather(gathered, p2.clone())
+            assert all(torch.equal(t, gathered[0]) for t in gathered), "reduce_allreduce_sgd diverged bitwise"
+            dist.barrier()
+        # back-to-back calls with no host synchronisation in between: exercises the epoch double
+        # buffer of the push variant (ranks run ahead of each other by up to one call)
+        reps = 64
+        p2.copy_(_rank_data(60, 0, n2, torch.float32, dev))
+        start = p2.clone()
+        all_parts = [parts_of(300 + k, rank) for k in range(reps)]
+        torch.cuda.synchronize()
+        dist.barrier()
+        for k in range(reps):
+            comm.reduce_allreduce_sgd(all_parts[k], nparts, n2, region, 0, lr, algo=algo, slot=3 + ai)
+            if rank == k % world:
+                torch.cuda._sleep(200000)  # skew the ranks against each other
+        torch.cuda.synchronize()
+        tot = torch.zeros(n2, device=dev, dtype=torch.float64)
+        for k in range(reps):
+            for r in range(world):
+                tot += parts_of(300 + k, r).sum(0).double()
+        want2 = start.double() - 0.01 * tot / world
+        assert torch.allclose(p2.double(), want2, rtol=1e-4, atol=1e-3), (algo, (p2 - want2).abs().max().item())
+        gathered = [torch.empty_like(p2) for _ in range(world)]
+        dist.all_gather(gathered, p2.clone())
+        assert all(torch.equal(t, gathered[0]) for t in gathered), "back-to-back calls diverged bitwise"
+        dist.barrier()
     comm.close()
     if rank == 0:
         print("fused_sgd ok", flush=True)

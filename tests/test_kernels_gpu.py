@@ -301,3 +301,28 @@ def test_gather_u8(nat):
     # ToTensor semantics = true division on the CPU (CUDA's scalar div multiplies by 1/255)
     assert torch.equal(x.cpu(), imgs[idx].cpu().float().div(255).unsqueeze(1))
     assert torch.equal(y, labels[idx])
+
+
+@pytest.mark.parametrize("algo_name", ["push", "pull"])
+@pytest.mark.parametrize("nparts,n", [(1, 320), (37, 320), (148, 320), (5, 4096)])
+def test_reduce_allreduce_sgd_single_rank(nat, algo_name, nparts, n):
+    """Fused split-K reduce + all-reduce + SGD kernel at world size 1 (the exchange degenerates to
+    this rank's own staging lines / flags); the multi-rank case is tests/test_multi_gpu.py."""
+    from ddp_b200.parallel.comm import ALGO_ONESHOT, ALGO_PUSH, SymmetricComm
+    algo = ALGO_PUSH if algo_name == "push" else ALGO_ONESHOT
+    torch.manual_seed(8)
+    region = (n * 4 + 255) // 256 * 256
+    comm = SymmetricComm(0, 1, 2 * region)
+    try:
+        p, g = comm.tensor(0, n), comm.tensor(region, n)
+        lr = torch.tensor([0.05], device="cuda")
+        p.copy_(torch.randn(n, device="cuda"))
+        for it in range(3):  # consecutive epochs reuse the staging lines
+            parts = torch.randn(nparts, n, device="cuda")
+            want = p - 0.05 * parts.sum(0)
+            comm.reduce_allreduce_sgd(parts, nparts, n, region, 0, lr, algo=algo, slot=2)
+            torch.cuda.synchronize()
+            assert torch.allclose(g, parts.sum(0), atol=1e-4, rtol=1e-5)
+            assert torch.allclose(p, want, atol=1e-5, rtol=1e-5), (it, (p - want).abs().max().item())
+    finally:
+        comm.close()
