@@ -5,6 +5,7 @@
 #define DDPB_ERR_SHAPE 9001   // unsupported shape / argument
 #define DDPB_ERR_STATE 9002   // call made in the wrong state (e.g. communicator not connected)
 #define DDPB_ERR_LIMIT 9003   // size beyond a documented fixed limit
+#define DDPB_ERR_UNSUPPORTED 9004  // feature not available on this driver / system (e.g. multicast)
 
 #define DDPB_CUDA_OK(expr)                              \
   do {                                                  \

@@ -23,10 +23,12 @@
 // their own copy with ld.acquire.sys and a wall-clock bound: a dead peer becomes a trap (a CUDA
 // error on the host), never a hung GPU.  Gradient buckets are double-buffered by step parity, so
 // a single flag round per bucket also protects buffer reuse.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <string.h>
+#include <unistd.h>
 #include <new>
 
 #include "ptx.cuh"
@@ -57,6 +59,14 @@ struct Comm {
   bool opened[kMaxWorld] = {};
   bool connected = false;
   unsigned long long timeout_ns = 20ull * 1000 * 1000 * 1000;
+  // VMM + multicast (NVLS) variant: the buffer is a cuMemCreate allocation mapped by every peer
+  // through an exported file descriptor and bound to one multicast object; `mc` is the multicast
+  // address of the same bytes (multimem.ld_reduce / multimem.st go through the NVSwitch).
+  bool vmm = false;
+  size_t map_bytes = 0, align = 0;
+  CUmemGenericAllocationHandle mem = 0, peer_mem[kMaxWorld] = {}, mc_handle = 0;
+  bool mc_created = false, mc_bound = false;
+  uint8_t* mc = nullptr;
 };
 
 struct PeerPtrs {
@@ -400,6 +410,93 @@ broadcast_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, int ro
   if (threadIdx.x == 0) *ep = e + 1;
 }
 
+// ---------------------------------------------------------------- NVLS (multimem) kernels
+// With the buffer bound to a multicast object, `mc + off` addresses the same offset of EVERY
+// rank's buffer at once: multimem.ld_reduce returns the sum over all ranks computed inside the
+// NVSwitch (one request instead of W-1 peer loads), multimem.st stores to all ranks at once.
+// Each element is reduced by exactly one rank and broadcast, so all replicas stay bit-identical
+// (the switch's summation order is its own, but there is only one sum per element).
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const uint8_t* mc_addr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const uint8_t* mc_addr) {
+  uint4 v;
+  asm volatile(
+      "multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+      : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+      : "l"(mc_addr)
+      : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(uint8_t* mc_addr, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr),
+               "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x8(uint8_t* mc_addr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr),
+               "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// two-shot through the switch: rank r owns slice r; in-switch sum -> SGD -> multicast store of
+// the updated parameters into every rank's arena.
+template <int WORLD>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_sgd_nvls_kernel(const __grid_constant__ PeerPtrs pp, uint8_t* mc, int rank, int slot,
+                          size_t grad_off, size_t param_off, long long n4,
+                          const float* __restrict__ lr, unsigned long long timeout_ns) {
+  pdl_sync();
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  const float scale = -(*lr) * (1.0f / WORLD);
+  const long long per = (n4 + WORLD - 1) / WORLD;
+  const long long lo = per * rank;
+  const long long hi = lo + per < n4 ? lo + per : n4;
+  const float* params = reinterpret_cast<const float*>(pp.p[rank] + param_off);
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float4 s = multimem_ld_reduce_f32x4(mc + grad_off + i * 16);
+    float4 p = *reinterpret_cast<const float4*>(params + i * 4);
+    p.x = fmaf(scale, s.x, p.x);
+    p.y = fmaf(scale, s.y, p.y);
+    p.z = fmaf(scale, s.z, p.z);
+    p.w = fmaf(scale, s.w, p.w);
+    multimem_st_f32x4(mc + param_off + i * 16, p);
+  }
+  flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
+  if (threadIdx.x == 0) *ep = e + 1;
+}
+
+// plain sum all-reduce through the switch (fp32 or bf16 with fp32 accumulation in the switch)
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_nvls_kernel(const __grid_constant__ PeerPtrs pp, uint8_t* mc, int rank, int slot,
+                      size_t in_off, size_t out_off, long long nvec, unsigned long long timeout_ns) {
+  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
+  const uint32_t e = *ep + 1;
+  flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
+  const long long per = (nvec + WORLD - 1) / WORLD;
+  const long long lo = per * rank;
+  const long long hi = lo + per < nvec ? lo + per : nvec;
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    if (sizeof(T) == 4) {
+      multimem_st_f32x4(mc + out_off + i * 16, multimem_ld_reduce_f32x4(mc + in_off + i * 16));
+    } else {
+      multimem_st_bf16x8(mc + out_off + i * 16, multimem_ld_reduce_bf16x8(mc + in_off + i * 16));
+    }
+  }
+  flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
+  if (threadIdx.x == 0) *ep = e + 1;
+}
+
 // Remote loads over NVLink cost ~4-5 us of latency per dependent round, so the grid is sized for
 // ONE grid-stride iteration per thread wherever the block cap allows (measured: 2 MB two-shot on
 // 8 GPUs took 43 us with 4 iterations per thread).
@@ -415,6 +512,117 @@ static PeerPtrs peer_ptrs(const Comm* c) {
   PeerPtrs pp;
   for (int r = 0; r < kMaxWorld; ++r) pp.p[r] = r < c->world ? c->peer[r] : c->peer[c->rank];
   return pp;
+}
+
+// ---------------------------------------------------------------- driver API (VMM + multicast)
+// Resolved at run time through the runtime's cudaGetDriverEntryPoint so the library has no link
+// dependency on libcuda (it must still load on a machine without a driver, e.g. for CPU tests).
+struct DrvApi {
+  decltype(&cuDeviceGet) DeviceGet = nullptr;
+  decltype(&cuDeviceGetAttribute) DeviceGetAttribute = nullptr;
+  decltype(&cuMemCreate) MemCreate = nullptr;
+  decltype(&cuMemRelease) MemRelease = nullptr;
+  decltype(&cuMemAddressReserve) AddressReserve = nullptr;
+  decltype(&cuMemAddressFree) AddressFree = nullptr;
+  decltype(&cuMemMap) Map = nullptr;
+  decltype(&cuMemUnmap) Unmap = nullptr;
+  decltype(&cuMemSetAccess) SetAccess = nullptr;
+  decltype(&cuMemGetAllocationGranularity) GetGranularity = nullptr;
+  decltype(&cuMemExportToShareableHandle) Export = nullptr;
+  decltype(&cuMemImportFromShareableHandle) Import = nullptr;
+  decltype(&cuMulticastCreate) McCreate = nullptr;
+  decltype(&cuMulticastAddDevice) McAddDevice = nullptr;
+  decltype(&cuMulticastBindMem) McBindMem = nullptr;
+  decltype(&cuMulticastUnbind) McUnbind = nullptr;
+  decltype(&cuMulticastGetGranularity) McGetGranularity = nullptr;
+  bool ok = false;
+};
+
+template <class F>
+static bool drv_load(const char* name, F* out) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+  if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess || fn == nullptr) {
+    cudaGetLastError();
+    return false;
+  }
+  *out = reinterpret_cast<F>(fn);
+  return true;
+}
+
+static const DrvApi* drv() {
+  static DrvApi api;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    DrvApi a;
+    bool ok = drv_load("cuDeviceGet", &a.DeviceGet);
+    ok = ok && drv_load("cuDeviceGetAttribute", &a.DeviceGetAttribute);
+    ok = ok && drv_load("cuMemCreate", &a.MemCreate);
+    ok = ok && drv_load("cuMemRelease", &a.MemRelease);
+    ok = ok && drv_load("cuMemAddressReserve", &a.AddressReserve);
+    ok = ok && drv_load("cuMemAddressFree", &a.AddressFree);
+    ok = ok && drv_load("cuMemMap", &a.Map);
+    ok = ok && drv_load("cuMemUnmap", &a.Unmap);
+    ok = ok && drv_load("cuMemSetAccess", &a.SetAccess);
+    ok = ok && drv_load("cuMemGetAllocationGranularity", &a.GetGranularity);
+    ok = ok && drv_load("cuMemExportToShareableHandle", &a.Export);
+    ok = ok && drv_load("cuMemImportFromShareableHandle", &a.Import);
+    ok = ok && drv_load("cuMulticastCreate", &a.McCreate);
+    ok = ok && drv_load("cuMulticastAddDevice", &a.McAddDevice);
+    ok = ok && drv_load("cuMulticastBindMem", &a.McBindMem);
+    ok = ok && drv_load("cuMulticastUnbind", &a.McUnbind);
+    ok = ok && drv_load("cuMulticastGetGranularity", &a.McGetGranularity);
+    a.ok = ok;
+    api = a;
+  }
+  return api.ok ? &api : nullptr;
+}
+
+#define DDPB_CU_OK(expr)                                 \
+  do {                                                   \
+    CUresult _r = (expr);                                \
+    if (_r != CUDA_SUCCESS) return static_cast<int>(_r); \
+  } while (0)
+
+static CUmemAllocationProp vmm_alloc_prop(int device) {
+  CUmemAllocationProp prop;
+  memset(&prop, 0, sizeof(prop));
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = device;
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  return prop;
+}
+
+// Reserve a VA range, map `handle` into it and give THIS device read/write access.
+static int vmm_map(const DrvApi* d, CUmemGenericAllocationHandle handle, size_t bytes, size_t align,
+                   int device, uint8_t** out) {
+  CUdeviceptr va = 0;
+  DDPB_CU_OK(d->AddressReserve(&va, bytes, align, 0, 0));
+  CUresult r = d->Map(va, bytes, 0, handle, 0);
+  if (r == CUDA_SUCCESS) {
+    CUmemAccessDesc acc;
+    memset(&acc, 0, sizeof(acc));
+    acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+    acc.location.id = device;
+    acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+    r = d->SetAccess(va, bytes, &acc, 1);
+    if (r != CUDA_SUCCESS) d->Unmap(va, bytes);
+  }
+  if (r != CUDA_SUCCESS) {
+    d->AddressFree(va, bytes);
+    return static_cast<int>(r);
+  }
+  *out = reinterpret_cast<uint8_t*>(va);
+  return 0;
+}
+
+static void vmm_unmap(const DrvApi* d, uint8_t* p, size_t bytes) {
+  if (!p) return;
+  d->Unmap(reinterpret_cast<CUdeviceptr>(p), bytes);
+  d->AddressFree(reinterpret_cast<CUdeviceptr>(p), bytes);
 }
 
 #define DDPB_DISPATCH_WORLD(W, ...)                   \
@@ -461,8 +669,190 @@ int ddpb_comm_create(int rank, int world, size_t payload_bytes, void** out) {
   return 0;
 }
 
+// ---------------------------------------------------------------- VMM / multicast communicator
+// Same buffer layout and kernels as the IPC communicator, but the memory is a cuMemCreate
+// allocation shared through POSIX file descriptors (the caller moves the descriptors between
+// the processes, e.g. over an AF_UNIX socket) so that it can ALSO be bound to a multicast
+// object.  Call order on every rank:
+//   create_vmm -> export_fd / import_peer_fd (all peers) ->
+//   [rank 0: mc_create, others: mc_import] -> mc_add_device -> (barrier) -> mc_bind -> (barrier)
+//   -> set_connected.
+// Every step returns 0 or a CUDA/driver error code; nothing here aborts, so the caller can agree
+// with its peers to fall back to the IPC communicator.
+
+// 1 if the current device can take part in a multicast object, 0 if not, < 0 if the driver API
+// is not available.
+int ddpb_multicast_supported() {
+  const DrvApi* d = drv();
+  if (!d) return -1;
+  int dev = 0, flag = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  CUdevice cudev;
+  if (d->DeviceGet(&cudev, dev) != CUDA_SUCCESS) return -1;
+  if (d->DeviceGetAttribute(&flag, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cudev) != CUDA_SUCCESS)
+    return -1;
+  return flag ? 1 : 0;
+}
+
+int ddpb_comm_create_vmm(int rank, int world, size_t payload_bytes, void** out) {
+  if (!(world == 1 || world == 2 || world == 4 || world == 8) || rank < 0 || rank >= world)
+    return DDPB_ERR_SHAPE;
+  const DrvApi* d = drv();
+  if (!d) return DDPB_ERR_UNSUPPORTED;
+  Comm* c = new (std::nothrow) Comm();
+  if (!c) return static_cast<int>(cudaErrorMemoryAllocation);
+  c->rank = rank;
+  c->world = world;
+  c->vmm = true;
+  int rc = static_cast<int>(cudaGetDevice(&c->device));
+  if (rc == 0) rc = static_cast<int>(cudaFree(nullptr));  // make sure the primary context exists
+  size_t gran = 0, mc_gran = 0;
+  const CUmemAllocationProp prop = vmm_alloc_prop(c->device);
+  if (rc == 0) rc = static_cast<int>(d->GetGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  if (rc == 0 && ddpb_multicast_supported() == 1) {
+    CUmulticastObjectProp mp;
+    memset(&mp, 0, sizeof(mp));
+    mp.numDevices = static_cast<unsigned>(world);
+    mp.size = gran;
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t rec = 0, mn = 0;
+    if (d->McGetGranularity(&mn, &mp, CU_MULTICAST_GRANULARITY_MINIMUM) == CUDA_SUCCESS) mc_gran = mn;
+    // the recommended granularity can be very large; take it only while it stays modest
+    if (d->McGetGranularity(&rec, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) == CUDA_SUCCESS &&
+        rec <= (32u << 20) && rec > mc_gran)
+      mc_gran = rec;
+  }
+  if (rc == 0) {
+    size_t align = gran > mc_gran ? gran : mc_gran;
+    if (align == 0) align = 2u << 20;
+    c->bytes = kHeaderBytes + (payload_bytes + 255) / 256 * 256;
+    c->map_bytes = (c->bytes + align - 1) / align * align;
+    c->align = align;
+    rc = static_cast<int>(d->MemCreate(&c->mem, c->map_bytes, &prop, 0));
+  }
+  if (rc == 0) {
+    rc = vmm_map(d, c->mem, c->map_bytes, c->align, c->device, &c->local);
+    if (rc != 0) d->MemRelease(c->mem);
+  }
+  if (rc == 0) rc = static_cast<int>(cudaMemset(c->local, 0, c->map_bytes));
+  if (rc == 0) rc = static_cast<int>(cudaDeviceSynchronize());
+  if (rc != 0) {
+    cudaGetLastError();
+    delete c;
+    return rc;
+  }
+  c->peer[rank] = c->local;
+  c->connected = false;
+  *out = c;
+  return 0;
+}
+
+// A new file descriptor naming this rank's allocation; the caller sends it to the peers and
+// closes it.
+int ddpb_comm_export_fd(void* comm, int* fd_out) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->vmm) return DDPB_ERR_STATE;
+  int fd = -1;
+  DDPB_CU_OK(d->Export(&fd, c->mem, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  *fd_out = fd;
+  return 0;
+}
+
+// Maps rank r's allocation from a descriptor received from r (the descriptor stays the caller's).
+int ddpb_comm_import_peer_fd(void* comm, int r, int fd) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->vmm || r < 0 || r >= c->world || r == c->rank || c->opened[r]) return DDPB_ERR_STATE;
+  CUmemGenericAllocationHandle h = 0;
+  DDPB_CU_OK(d->Import(&h, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)),
+                       CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+  uint8_t* p = nullptr;
+  const int rc = vmm_map(d, h, c->map_bytes, c->align, c->device, &p);
+  if (rc != 0) {
+    d->MemRelease(h);
+    return rc;
+  }
+  c->peer_mem[r] = h;
+  c->peer[r] = p;
+  c->opened[r] = true;
+  return 0;
+}
+
+// Rank 0 creates the multicast object and exports a descriptor for the others.
+int ddpb_comm_mc_create(void* comm, int* fd_out) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->vmm || c->mc_created) return DDPB_ERR_STATE;
+  if (ddpb_multicast_supported() != 1) return DDPB_ERR_UNSUPPORTED;
+  CUmulticastObjectProp mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.numDevices = static_cast<unsigned>(c->world);
+  mp.size = c->map_bytes;
+  mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  DDPB_CU_OK(d->McCreate(&c->mc_handle, &mp));
+  c->mc_created = true;
+  int fd = -1;
+  DDPB_CU_OK(d->Export(&fd, c->mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  *fd_out = fd;
+  return 0;
+}
+
+int ddpb_comm_mc_import(void* comm, int fd) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->vmm || c->mc_created) return DDPB_ERR_STATE;
+  if (ddpb_multicast_supported() != 1) return DDPB_ERR_UNSUPPORTED;
+  DDPB_CU_OK(d->Import(&c->mc_handle, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)),
+                       CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+  c->mc_created = true;
+  return 0;
+}
+
+int ddpb_comm_mc_add_device(void* comm) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->mc_created) return DDPB_ERR_STATE;
+  CUdevice cudev;
+  DDPB_CU_OK(d->DeviceGet(&cudev, c->device));
+  DDPB_CU_OK(d->McAddDevice(c->mc_handle, cudev));
+  return 0;
+}
+
+// Binds this rank's memory to the multicast object and maps the multicast address range.  The
+// driver blocks here until EVERY rank has called mc_add_device: only call it once all ranks
+// reported success for that step.
+int ddpb_comm_mc_bind(void* comm) {
+  Comm* c = static_cast<Comm*>(comm);
+  const DrvApi* d = drv();
+  if (!d || !c->mc_created || c->mc_bound) return DDPB_ERR_STATE;
+  DDPB_CU_OK(d->McBindMem(c->mc_handle, 0, c->mem, 0, c->map_bytes, 0));
+  c->mc_bound = true;
+  uint8_t* p = nullptr;
+  const int rc = vmm_map(d, c->mc_handle, c->map_bytes, c->align, c->device, &p);
+  if (rc != 0) return rc;
+  c->mc = p;
+  return 0;
+}
+
+int ddpb_comm_set_connected(void* comm) {
+  Comm* c = static_cast<Comm*>(comm);
+  for (int r = 0; r < c->world; ++r)
+    if (!c->peer[r]) return DDPB_ERR_STATE;
+  c->connected = true;
+  return 0;
+}
+
+int ddpb_comm_has_multicast(void* comm) { return static_cast<Comm*>(comm)->mc != nullptr ? 1 : 0; }
+// multicast alias of ddpb_comm_local_ptr (nullptr without multicast)
+void* ddpb_comm_multicast_ptr(void* comm) {
+  Comm* c = static_cast<Comm*>(comm);
+  return c->mc ? c->mc + kHeaderBytes : nullptr;
+}
+
 int ddpb_comm_get_handle(void* comm, void* handle_out) {
   Comm* c = static_cast<Comm*>(comm);
+  if (c->vmm) return DDPB_ERR_STATE;  // VMM allocations are shared by file descriptor, not IPC
   cudaIpcMemHandle_t h;
   DDPB_CUDA_OK(cudaIpcGetMemHandle(&h, c->local));
   memcpy(handle_out, &h, sizeof(h));
@@ -472,6 +862,7 @@ int ddpb_comm_get_handle(void* comm, void* handle_out) {
 // all_handles: world * ddpb_comm_handle_bytes() bytes (host), rank-major.
 int ddpb_comm_connect(void* comm, const void* all_handles) {
   Comm* c = static_cast<Comm*>(comm);
+  if (c->vmm) return DDPB_ERR_STATE;
   const uint8_t* hs = static_cast<const uint8_t*>(all_handles);
   for (int r = 0; r < c->world; ++r) {
     if (r == c->rank) continue;
@@ -507,6 +898,29 @@ int ddpb_comm_destroy(void* comm) {
   Comm* c = static_cast<Comm*>(comm);
   if (!c) return 0;
   cudaDeviceSynchronize();
+  if (c->vmm) {
+    const DrvApi* d = drv();
+    if (d) {
+      if (c->mc) vmm_unmap(d, c->mc, c->map_bytes);
+      if (c->mc_bound) {
+        CUdevice cudev;
+        if (d->DeviceGet(&cudev, c->device) == CUDA_SUCCESS)
+          d->McUnbind(c->mc_handle, cudev, 0, c->map_bytes);
+      }
+      if (c->mc_created) d->MemRelease(c->mc_handle);
+      for (int r = 0; r < c->world; ++r)
+        if (c->opened[r]) {
+          vmm_unmap(d, c->peer[r], c->map_bytes);
+          d->MemRelease(c->peer_mem[r]);
+        }
+      if (c->local) {
+        vmm_unmap(d, c->local, c->map_bytes);
+        d->MemRelease(c->mem);
+      }
+    }
+    delete c;
+    return 0;
+  }
   for (int r = 0; r < c->world; ++r)
     if (c->opened[r]) cudaIpcCloseMemHandle(c->peer[r]);
   if (c->local) cudaFree(c->local);
@@ -515,7 +929,8 @@ int ddpb_comm_destroy(void* comm) {
 }
 
 // Offsets below are byte offsets into the payload (i.e. relative to ddpb_comm_local_ptr),
-// 16-byte aligned, identical on every rank.  algo: 1 = one-shot, 2 = two-shot, 0 = by size.
+// 16-byte aligned, identical on every rank.  algo: 1 = one-shot, 2 = two-shot, 4 = two-shot through
+// the switch (multimem; needs a multicast-bound communicator), 0 = by size.
 int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long n_floats,
                        const float* lr_dev, int algo, int slot, void* stream) {
   Comm* c = static_cast<Comm*>(comm);
@@ -523,13 +938,18 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
   if ((n_floats & 3) || (grad_off & 15) || (param_off & 15) || slot < 0 || slot >= kSlots)
     return DDPB_ERR_SHAPE;
   const long long n4 = n_floats / 4;
-  if (algo == 0) algo = (c->world <= 2 || n_floats * 4 <= (256 << 10)) ? 1 : 2;
-  const bool two = algo == 2;
+  if (algo == 0) algo = (c->world <= 2 || n_floats * 4 <= (256 << 10)) ? 1 : (c->mc ? 4 : 2);
+  if (algo == 4 && !c->mc) return DDPB_ERR_STATE;
+  const bool two = algo == 2 || algo == 4;
   const int blocks = blocks_for(n4, c->world, two);
   const PeerPtrs pp = peer_ptrs(c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t go = grad_off + kHeaderBytes, po = param_off + kHeaderBytes;
   DDPB_DISPATCH_WORLD(c->world, {
+    if (algo == 4)
+      return static_cast<int>(launch_k(allreduce_sgd_nvls_kernel<WORLD>, dim3(blocks),
+                                       dim3(kCommThreads), 0, st, pp, c->mc, c->rank, slot, go, po, n4,
+                                       lr_dev, c->timeout_ns));
     if (two)
       return static_cast<int>(launch_k(allreduce_sgd_twoshot_kernel<WORLD>, dim3(blocks),
                                        dim3(kCommThreads), 0, st, pp, c->rank, slot, go, po, n4, lr_dev,
@@ -579,14 +999,19 @@ int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, 
   if ((nbytes & 15) || (in_off & 15) || (out_off & 15) || slot < 0 || slot >= kSlots)
     return DDPB_ERR_SHAPE;
   const long long nvec = nbytes / 16;
-  if (algo == 0) algo = (c->world <= 2 || nbytes <= (256 << 10)) ? 1 : 2;
-  const bool two = algo == 2;
+  if (algo == 0) algo = (c->world <= 2 || nbytes <= (256 << 10)) ? 1 : (c->mc ? 4 : 2);
+  if (algo == 4 && !c->mc) return DDPB_ERR_STATE;
+  const bool two = algo == 2 || algo == 4;
   const int blocks = blocks_for(nvec, c->world, two);
   const PeerPtrs pp = peer_ptrs(c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t io = in_off + kHeaderBytes, oo = out_off + kHeaderBytes;
   DDPB_DISPATCH_WORLD(c->world, {
-    if (dtype == 0) {
+    if (algo == 4) {
+      if (dtype == 0) allreduce_nvls_kernel<float, WORLD><<<blocks, kCommThreads, 0, st>>>(pp, c->mc, c->rank, slot, io, oo, nvec, c->timeout_ns);
+      else if (dtype == 1) allreduce_nvls_kernel<__nv_bfloat16, WORLD><<<blocks, kCommThreads, 0, st>>>(pp, c->mc, c->rank, slot, io, oo, nvec, c->timeout_ns);
+      else return DDPB_ERR_SHAPE;
+    } else if (dtype == 0) {
       if (two) allreduce_kernel<float, WORLD, 1><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
       else allreduce_kernel<float, WORLD, 0><<<blocks, kCommThreads, 0, st>>>(pp, c->rank, slot, io, oo, nvec, c->timeout_ns);
     } else if (dtype == 1) {

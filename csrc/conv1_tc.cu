@@ -13,6 +13,8 @@
 //             that yields the bias gradient; M = 64 (32 real channels), N = 32, K = 128 pixels
 //             per tile; per-CTA partial in TMEM, fixed-order reduce.
 // Replaces cuDNN conv fwd / wgrad + ATen relu for reference model.py:9-10 (SURVEY.md K1,K2,K12,K13).
+#include <stdlib.h>
+
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
@@ -29,7 +31,9 @@ constexpr uint32_t kXStageBytes = 8192;  // two images of up to 32x32 fp32
 // A 128-row tile touches at most two consecutive images.  One bulk async copy stages both
 // (clamped to the batch) into shared memory; returns the first staged image index.
 __device__ __forceinline__ int x_stage_first_image(const Geom& g, int tile) {
-  const int img0 = (tile * kTileM) / g.PHW;
+  const uint32_t row0 = static_cast<uint32_t>(tile * kTileM);
+  const int img0 = g.mul_phw ? static_cast<int>(__umulhi(row0, g.mul_phw) >> g.sh_phw)
+                             : static_cast<int>(row0 / g.PHW);
   const int last_start = g.batch >= 2 ? g.batch - 2 : 0;
   return img0 < last_start ? img0 : last_start;
 }
@@ -54,6 +58,9 @@ __device__ __forceinline__ void taps_from_stage(const float* xs, const Geom& g, 
 }
 __device__ __forceinline__ void producer_sync() {  // the 128 producer threads only
   asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+__device__ __forceinline__ void producer_group_sync(int grp) {  // 128 threads of producer group grp
+  asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
 }
 
 // ------------------------------------------------------------------------------------- forward
@@ -266,19 +273,25 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
   const uint32_t tmem_base = *s_tmem;
   pdl_sync();
 
-  if (warp < 4) {
+  if (warp != 4) {
+    // ---- producers: TWO groups of 128 threads (warps 0-3 and 5-8) take alternate tiles, so two
+    // tiles' im2col rows are being built at any time; group 1 also runs the epilogue at the end.
+    const int grp = warp < 4 ? 0 : 1;
+    const int ptid = grp ? tid - 160 : tid;
     if (tid == 0) {
       int pre = 0;
       for (int t = blockIdx.x; t < g.ntiles && pre < kXStages; t += gridDim.x, ++pre)
         x_stage_issue(x, g, t, s_base + S::off_x + pre * kXStageBytes, bar_x + pre * 8);
     }
-    int it = 0;
-    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+    for (int it = grp;; it += 2) {
+      const long long tl = (long long)blockIdx.x + (long long)it * gridDim.x;
+      if (tl >= g.ntiles) break;
+      const int t = static_cast<int>(tl);
       const int stage = it % kC1Stages;
       const uint32_t phase = (it / kC1Stages) & 1;
       const int xst = it % kXStages;
       int img, h, wc;
-      const bool valid = decode_row(g, t * kTileM + tid, img, h, wc);
+      const bool valid = decode_row(g, t * kTileM + ptid, img, h, wc);
       float tp[9];
 #pragma unroll
       for (int i = 0; i < 9; ++i) tp[i] = 0.f;
@@ -286,11 +299,12 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       if (valid)
         taps_from_stage(reinterpret_cast<const float*>(smem + S::off_x + xst * kXStageBytes), g,
                         img - x_stage_first_image(g, t), h, wc, tp);
-      producer_sync();
-      if (tid == 0) {
-        const int tn = t + kXStages * gridDim.x;
+      producer_group_sync(grp);  // the whole group has read this x stage: refill it
+      if (ptid == 0) {
+        const long long tn = tl + (long long)kXStages * gridDim.x;
         if (tn < g.ntiles)
-          x_stage_issue(x, g, tn, s_base + S::off_x + xst * kXStageBytes, bar_x + xst * 8);
+          x_stage_issue(x, g, static_cast<int>(tn), s_base + S::off_x + xst * kXStageBytes,
+                        bar_x + xst * 8);
       }
       // x = hi + lo with both terms bf16
       uint32_t hi[5], lo[5];
@@ -308,7 +322,7 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       hi[4] = pack_bf16x2(hf[8], 1.0f);  // column 9 = ones -> bias gradient
       lo[4] = pack_bf16x2(lf[8], 0.f);
       mbar_wait(bar_empty + stage * 8, phase ^ 1);
-      if (tid == 0) {
+      if (ptid == 0) {
         mbar_arrive_expect_tx(bar_fa + stage * 8, 4 * S::a_plane);
         const long long rowa = (long long)kGuard + (long long)t * kTileM;
 #pragma unroll
@@ -316,7 +330,7 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
           bulk_g2s(s_base + stage * S::stage + p * S::a_plane,
                    dact + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane, bar_fa + stage * 8);
       }
-      uint8_t* b = smem + stage * S::stage + S::a_bytes + tid * 16;
+      uint8_t* b = smem + stage * S::stage + S::a_bytes + ptid * 16;
       *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
       *reinterpret_cast<uint4*>(b + S::a_plane) = make_uint4(hi[4], 0, 0, 0);
       *reinterpret_cast<uint4*>(b + 2 * S::a_plane) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
@@ -324,7 +338,25 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       fence_proxy_async_smem();
       mbar_arrive(bar_fb + stage * 8);
     }
-  } else if (warp == 4) {
+    if (grp == 1) {
+      // ---- epilogue (after this group's last tile): accumulator -> this CTA's partial
+      const int q = warp & 3;
+      mbar_wait(bar_done, 0);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16), v);
+      tmem_ld_wait();
+      // M = 64: row m lives in lane (m % 16) + 32 * (m / 16); channels 0..31 are rows 0..31
+      if (q < 2 && lane < 16) {
+        const int c = q * 16 + lane;
+        float* dst = partial + (long long)blockIdx.x * (32 * 9 + 32);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap)
+          dst[c * 9 + tap] = __uint_as_float(v[tap]) + __uint_as_float(v[16 + tap]);
+        dst[32 * 9 + c] = __uint_as_float(v[9]);
+      }
+    }
+  } else {
     constexpr uint32_t idesc = umma_idesc_bf16(64, 32, 1, 1);
     int it = 0;
     for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
@@ -346,22 +378,6 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
     }
     if (elect_one()) umma_commit(bar_done);
     __syncwarp();
-  } else {
-    const int q = warp & 3;
-    mbar_wait(bar_done, 0);
-    tc_fence_after();
-    uint32_t v[32];
-    tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16), v);
-    tmem_ld_wait();
-    // M = 64: row m lives in lane (m % 16) + 32 * (m / 16); channels 0..31 are rows 0..31
-    if (q < 2 && lane < 16) {
-      const int c = q * 16 + lane;
-      float* dst = partial + (long long)blockIdx.x * (32 * 9 + 32);
-#pragma unroll
-      for (int tap = 0; tap < 9; ++tap)
-        dst[c * 9 + tap] = __uint_as_float(v[tap]) + __uint_as_float(v[16 + tap]);
-      dst[32 * 9 + c] = __uint_as_float(v[9]);
-    }
   }
   tc_fence_before();
   __syncthreads();
@@ -371,6 +387,27 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
 }  // namespace ddpb
 
 using namespace ddpb;
+
+// Both kernels are latency-bound with one 9-warp CTA per SM (ncu: issue slots 19-33 % busy, 2.25
+// active warps per scheduler); their shared memory (51 / 98 KB) and TMEM (64 / 32 columns) leave
+// room for two co-resident CTAs, which doubles the loads in flight.  DDPB_C1_CTAS=1 restores one.
+constexpr int kC1MaxCtasPerSm = 2;
+static int c1_ctas_per_sm() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("DDPB_C1_CTAS");
+    v = (e && e[0] == '1') ? 1 : kC1MaxCtasPerSm;
+  }
+  return v;
+}
+// Two CTAs per SM only when every CTA still gets a few tiles (measured: B=4096 step 1.243 ->
+// 1.122 ms, but at B=64 = 450 tiles the extra start-up cost makes the step slightly slower).
+static int c1_grid(int ntiles) {
+  const int sms = ddpb_num_sms();
+  const int per_sm = ntiles >= 4 * kC1MaxCtasPerSm * sms ? c1_ctas_per_sm() : 1;
+  const int slots = sms * per_sm;
+  return ntiles < slots ? ntiles : slots;
+}
 
 extern "C" {
 
@@ -387,15 +424,14 @@ int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out,
                                       C1FwdSmem::total));
     configured[dev & 63] = true;
   }
-  const int sms = ddpb_num_sms();
-  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  const int grid = c1_grid(g.ntiles);
   return static_cast<int>(launch_k(conv1_fwd_tc_kernel, dim3(grid), dim3(kC1Threads), C1FwdSmem::total,
                                    static_cast<cudaStream_t>(stream), x, w, b,
                                    static_cast<__nv_bfloat16*>(out), g));
 }
 
 size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout) {
-  return static_cast<size_t>(ddpb_num_sms()) * (cout * cin * 9 + cout) * sizeof(float);
+  return static_cast<size_t>(ddpb_num_sms()) * kC1MaxCtasPerSm * (cout * cin * 9 + cout) * sizeof(float);
 }
 
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
@@ -435,8 +471,7 @@ static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratc
                                       C1WgradSmem::total));
     configured[dev & 63] = true;
   }
-  const int sms = ddpb_num_sms();
-  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  const int grid = c1_grid(g.ntiles);
   DDPB_CUDA_OK(launch_k(conv1_wgrad_tc_kernel, dim3(grid), dim3(kC1Threads), C1WgradSmem::total,
                         static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dact), x,
                         scratch, g));

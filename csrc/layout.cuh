@@ -30,6 +30,11 @@ struct Geom {
   int PW, PHW;    // padded width (W+2) and padded pixels per image (H+2)*(W+2)
   int ntiles;     // ceil(batch*PHW / kTileM)
   long long plane_rows;  // rows per plane (capacity), see plane_rows_for()
+  // exact division by PHW / PW as multiply-high (decode_row runs once per row in every producer
+  // and epilogue; the generic integer division was ~70 instructions of it): for n < 2^31,
+  // n / PHW == umulhi(n, mul_phw) >> sh_phw ; for n < PHW, n / PW == umulhi(n, mul_pw).
+  // mul_phw == 0 (PHW a power of two) selects the plain division.
+  uint32_t mul_phw, sh_phw, mul_pw;
 };
 
 __host__ __device__ inline int tiles_for(int batch, int H, int W) {
@@ -47,15 +52,27 @@ __host__ inline Geom make_geom(int batch, int batch_cap, int H, int W) {
   g.PHW = (H + 2) * (W + 2);
   g.ntiles = tiles_for(batch, H, W);
   g.plane_rows = plane_rows_for(batch_cap, H, W);
+  uint32_t sh = 0;
+  while ((2u << sh) <= (uint32_t)g.PHW) ++sh;  // floor(log2(PHW))
+  const unsigned long long m = ((1ull << (32 + sh)) + g.PHW - 1) / g.PHW;
+  g.sh_phw = sh;
+  g.mul_phw = m < (1ull << 32) ? (uint32_t)m : 0u;
+  g.mul_pw = (uint32_t)(((1ull << 32) + g.PW - 1) / g.PW);
   return g;
 }
 
 // Decode a row index relative to kGuard.  Returns true for a real (interior) pixel of an image
 // that is part of this step's batch.
 __device__ __forceinline__ bool decode_row(const Geom& g, int rel, int& img, int& h, int& w) {
+#ifdef __CUDA_ARCH__
+  img = g.mul_phw ? (int)(__umulhi((uint32_t)rel, g.mul_phw) >> g.sh_phw) : rel / g.PHW;
+  int pos = rel - img * g.PHW;
+  int hp = (int)__umulhi((uint32_t)pos, g.mul_pw);
+#else
   img = rel / g.PHW;
   int pos = rel - img * g.PHW;
   int hp = pos / g.PW;
+#endif
   int wp = pos - hp * g.PW;
   h = hp - 1;
   w = wp - 1;

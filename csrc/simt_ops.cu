@@ -856,6 +856,7 @@ const char* ddpb_error_string(int code) {
     case DDPB_ERR_SHAPE: return "ddp_b200: unsupported shape or argument";
     case DDPB_ERR_STATE: return "ddp_b200: call made in the wrong state";
     case DDPB_ERR_LIMIT: return "ddp_b200: size exceeds a fixed limit of this entry point";
+    case DDPB_ERR_UNSUPPORTED: return "ddp_b200: not supported by this driver or system";
     default: return cudaGetErrorString(static_cast<cudaError_t>(code));
   }
 }

@@ -99,6 +99,11 @@ def check(code: int, what: str = "") -> None:
         raise NativeError(f"{what or 'native call'} failed: [{code}] {msg.decode() if msg else '?'}")
 
 
+def error_string(code: int) -> str:
+    msg = lib().ddpb_error_string(int(code))
+    return f"[{code}] {msg.decode() if msg else '?'}"
+
+
 def ptr(t) -> int | None:
     """Device/host pointer of a tensor (None passes NULL)."""
     if t is None:

@@ -6,11 +6,26 @@ ProcessGroupNCCL + the c10d Reducer (reference utils.py:7-11, train_ddp.py:34,19
 SURVEY.md §2.5 X13, X16, §5.9).  torch.distributed is used once, as plumbing, to exchange the
 64-byte CUDA IPC handles.
 
+Two ways of sharing the buffer:
+
+* CUDA IPC (default): ``cudaMalloc`` + ``cudaIpcGetMemHandle``; peers open the handle.
+* VMM + multicast (``multicast=True`` or ``DDPB_NVLS=1``): the buffer is a ``cuMemCreate``
+  allocation exported as a POSIX file descriptor; descriptors travel between the rank processes
+  over AF_UNIX sockets (SCM_RIGHTS), every rank maps every peer, and all the allocations are bound
+  to ONE multicast object so that ``multimem.ld_reduce`` / ``multimem.st`` reduce and broadcast
+  inside the NVSwitch (NVLS, ``ALGO_NVLS``).  Every set-up stage is agreed on by all ranks; if any
+  rank fails a stage, all of them fall back to the IPC communicator.
+
 All ranks must issue the same sequence of collective calls per flag slot.
 """
 from __future__ import annotations
 
 import ctypes
+import os
+import socket
+import threading
+import uuid
+import warnings
 from ctypes import c_int, c_longlong, c_size_t, c_uint, c_void_p, POINTER
 
 import torch
@@ -34,6 +49,17 @@ for _name, _res, _args in (
     ("ddpb_comm_set_timeout_ms", None, [P, LL]),
     ("ddpb_comm_status", I, [P, POINTER(c_uint)]),
     ("ddpb_comm_destroy", I, [P]),
+    ("ddpb_multicast_supported", I, []),
+    ("ddpb_comm_create_vmm", I, [I, I, SZ, POINTER(c_void_p)]),
+    ("ddpb_comm_export_fd", I, [P, POINTER(c_int)]),
+    ("ddpb_comm_import_peer_fd", I, [P, I, I]),
+    ("ddpb_comm_mc_create", I, [P, POINTER(c_int)]),
+    ("ddpb_comm_mc_import", I, [P, I]),
+    ("ddpb_comm_mc_add_device", I, [P]),
+    ("ddpb_comm_mc_bind", I, [P]),
+    ("ddpb_comm_set_connected", I, [P]),
+    ("ddpb_comm_has_multicast", I, [P]),
+    ("ddpb_comm_multicast_ptr", c_void_p, [P]),
     ("ddpb_allreduce_sgd", I, [P, SZ, SZ, LL, P, I, I, P]),
     ("ddpb_reduce_allreduce_sgd", I, [P, P, I, LL, SZ, SZ, P, I, I, P]),
     ("ddpb_allreduce", I, [P, SZ, SZ, LL, I, I, I, P]),
@@ -41,7 +67,7 @@ for _name, _res, _args in (
 ):
     nat.declare(_name, _res, _args)
 
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH = 0, 1, 2, 3
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH, ALGO_NVLS = 0, 1, 2, 3, 4
 DTYPE_CODES = {torch.float32: 0, torch.bfloat16: 1}
 
 
@@ -54,30 +80,188 @@ class _RawCudaBuffer:
         }
 
 
+def exchange_fds(rank: int, world_size: int, fds: list[int], token: str) -> list[list[int]]:
+    """All-to-all hand-over of open file descriptors between the rank processes of one node.
+
+    Every rank serves ``fds`` (possibly empty) on an abstract-namespace AF_UNIX socket named after
+    ``token`` and its rank, and fetches every peer's list.  Returns ``got[r]`` = descriptors
+    received from rank r (new numbers in this process; ``got[rank]`` is empty).  The caller closes
+    what it receives.  Needs an initialised torch.distributed group for the two barriers."""
+    name = lambda r: f"\0ddpb-{token}-{r}"
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(name(rank))
+    srv.listen(world_size)
+    err: list[BaseException] = []
+
+    def serve():
+        try:
+            for _ in range(world_size - 1):
+                conn, _addr = srv.accept()
+                with conn:
+                    # one data byte carries the count; the descriptors ride along as SCM_RIGHTS
+                    socket.send_fds(conn, [bytes([len(fds)])], fds)
+        except BaseException as e:  # surfaced by the caller after join()
+            err.append(e)
+
+    th = threading.Thread(target=serve, daemon=True)
+    th.start()
+    dist.barrier()  # every socket is listening
+    got: list[list[int]] = [[] for _ in range(world_size)]
+    try:
+        for r in range(world_size):
+            if r == rank:
+                continue
+            with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+                c.settimeout(60)
+                c.connect(name(r))
+                msg, rfds, _flags, _addr = socket.recv_fds(c, 1, 16)
+                if len(msg) != 1 or msg[0] != len(rfds):
+                    for fd in rfds:
+                        os.close(fd)
+                    raise RuntimeError(f"descriptor hand-over from rank {r} was truncated")
+                got[r] = list(rfds)
+    finally:
+        th.join(timeout=60)
+        srv.close()
+    if err:
+        raise err[0]
+    dist.barrier()
+    return got
+
+
+def _all_ok(ok: bool, world_size: int) -> bool:
+    """True only if every rank passes True (one tiny collective per set-up stage)."""
+    if world_size == 1:
+        return ok
+    flags = [None] * world_size
+    dist.all_gather_object(flags, bool(ok))
+    return all(flags)
+
+
 class SymmetricComm:
-    def __init__(self, rank: int, world_size: int, payload_bytes: int, timeout_ms: int | None = None):
+    def __init__(self, rank: int, world_size: int, payload_bytes: int, timeout_ms: int | None = None,
+                 multicast: bool | None = None):
         lib = nat.lib()
         self.lib = lib
         self.rank, self.world_size = rank, world_size
-        handle = c_void_p()
-        nat.check(lib.ddpb_comm_create(rank, world_size, payload_bytes, ctypes.byref(handle)),
-                  "comm_create")
-        self._h = handle
+        self._h = None
+        self.multicast = False
+        if multicast is None:
+            multicast = os.environ.get("DDPB_NVLS", "0") == "1"
+        if multicast and world_size > 1:
+            self._h = self._create_vmm(rank, world_size, payload_bytes)
+        if self._h is None:
+            self._h = self._create_ipc(rank, world_size, payload_bytes)
         if timeout_ms is not None:
             lib.ddpb_comm_set_timeout_ms(self._h, int(timeout_ms))
-        if world_size > 1:
-            hb = lib.ddpb_comm_handle_bytes()
-            mine = ctypes.create_string_buffer(hb)
-            nat.check(lib.ddpb_comm_get_handle(self._h, mine), "comm_get_handle")
-            gathered = [None] * world_size
-            dist.all_gather_object(gathered, bytes(mine.raw))
-            blob = b"".join(gathered)
-            nat.check(lib.ddpb_comm_connect(self._h, blob), "comm_connect (CUDA IPC open)")
-            dist.barrier()
         self.payload_bytes = int(lib.ddpb_comm_payload_bytes(self._h))
         self._base_ptr = int(lib.ddpb_comm_local_ptr(self._h))
         self._keep = _RawCudaBuffer(self._base_ptr, self.payload_bytes)
         self.buffer = torch.as_tensor(self._keep, device=torch.device("cuda", torch.cuda.current_device()))
+
+    # ------------------------------------------------------------------ set-up
+    def _create_ipc(self, rank: int, world_size: int, payload_bytes: int):
+        lib = self.lib
+        handle = c_void_p()
+        nat.check(lib.ddpb_comm_create(rank, world_size, payload_bytes, ctypes.byref(handle)),
+                  "comm_create")
+        if world_size > 1:
+            hb = lib.ddpb_comm_handle_bytes()
+            mine = ctypes.create_string_buffer(hb)
+            nat.check(lib.ddpb_comm_get_handle(handle, mine), "comm_get_handle")
+            gathered = [None] * world_size
+            dist.all_gather_object(gathered, bytes(mine.raw))
+            blob = b"".join(gathered)
+            nat.check(lib.ddpb_comm_connect(handle, blob), "comm_connect (CUDA IPC open)")
+            dist.barrier()
+        return handle
+
+    def _create_vmm(self, rank: int, world_size: int, payload_bytes: int):
+        """VMM allocation + descriptor exchange + multicast bind.  Returns the native handle, or
+        None (after releasing everything) when any rank failed any stage."""
+        lib = self.lib
+        why = ""
+        handle = c_void_p()
+        rc = lib.ddpb_comm_create_vmm(rank, world_size, payload_bytes, ctypes.byref(handle))
+        ok = rc == 0 and lib.ddpb_multicast_supported() == 1
+        if rc != 0:
+            why = f"create_vmm: {nat.error_string(rc)}"
+            handle = None
+        elif not ok:
+            why = "device does not support multicast objects"
+
+        def give_up(reason: str):
+            if handle is not None:
+                lib.ddpb_comm_destroy(handle)
+            if rank == 0:
+                warnings.warn(f"ddp_b200: multicast communicator unavailable ({reason or 'a peer failed'}); "
+                              "using the CUDA IPC communicator", RuntimeWarning, stacklevel=3)
+            return None
+
+        if not _all_ok(ok, world_size):
+            return give_up(why)
+        tok = [uuid.uuid4().hex if rank == 0 else None]
+        dist.broadcast_object_list(tok, src=0)
+        received: list[int] = []
+        try:
+            # stage 1: every rank maps every peer's allocation
+            fd = c_int(-1)
+            rc = lib.ddpb_comm_export_fd(handle, ctypes.byref(fd))
+            ok, why = rc == 0, (f"export_fd: {nat.error_string(rc)}" if rc else "")
+            mine = [fd.value] if ok else []
+            got = exchange_fds(rank, world_size, mine, tok[0] + "m")
+            for f in mine:
+                os.close(f)
+            for r, lst in enumerate(got):
+                received += lst
+                if r == rank:
+                    continue
+                if len(lst) != 1:
+                    ok, why = False, why or f"rank {r} exported no descriptor"
+                    continue
+                rc = lib.ddpb_comm_import_peer_fd(handle, r, lst[0])
+                if rc != 0:
+                    ok, why = False, why or f"import_peer_fd({r}): {nat.error_string(rc)}"
+            if not _all_ok(ok, world_size):
+                return give_up(why)
+            # stage 2: rank 0 creates the multicast object, the others import it
+            mcfd = c_int(-1)
+            if rank == 0:
+                rc = lib.ddpb_comm_mc_create(handle, ctypes.byref(mcfd))
+                ok, why = rc == 0, (f"mc_create: {nat.error_string(rc)}" if rc else "")
+            mine = [mcfd.value] if (rank == 0 and ok) else []
+            got = exchange_fds(rank, world_size, mine, tok[0] + "c")
+            for f in mine:
+                os.close(f)
+            for lst in got:
+                received += lst
+            if rank != 0:
+                if len(got[0]) != 1:
+                    ok, why = False, "rank 0 could not create the multicast object"
+                else:
+                    rc = lib.ddpb_comm_mc_import(handle, got[0][0])
+                    ok, why = rc == 0, (f"mc_import: {nat.error_string(rc)}" if rc else "")
+            if not _all_ok(ok, world_size):
+                return give_up(why)
+            # stage 3: every device joins the team; binding blocks until all have, so agree first
+            rc = lib.ddpb_comm_mc_add_device(handle)
+            ok, why = rc == 0, (f"mc_add_device: {nat.error_string(rc)}" if rc else "")
+            if not _all_ok(ok, world_size):
+                return give_up(why)
+            rc = lib.ddpb_comm_mc_bind(handle)
+            ok, why = rc == 0, (f"mc_bind: {nat.error_string(rc)}" if rc else "")
+            if not _all_ok(ok, world_size):
+                return give_up(why)
+            nat.check(lib.ddpb_comm_set_connected(handle), "comm_set_connected")
+            dist.barrier()
+            self.multicast = bool(lib.ddpb_comm_has_multicast(handle))
+            return handle
+        finally:
+            for f in received:
+                try:
+                    os.close(f)
+                except OSError:
+                    pass
 
     # ------------------------------------------------------------------ memory
     def tensor(self, offset_bytes: int, numel: int, dtype=torch.float32) -> torch.Tensor:

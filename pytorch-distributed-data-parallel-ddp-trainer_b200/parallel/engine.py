@@ -18,6 +18,7 @@ import torch.distributed as dist
 
 from ..models.simple_cnn import IMG_H, IMG_W, SimpleCNN, SimpleCNNB200
 from ..utils.checkpoint import sgd_state_dict
+from ..utils.trace import nvtx_range
 
 
 def _align(n: int, a: int) -> int:
@@ -76,11 +77,13 @@ class CpuDataParallel(_EngineBase):
 class B200DataParallel(_EngineBase):
     def __init__(self, rank: int, world_size: int, device, batch_cap: int, lr: float = 0.01,
                  use_graph: bool = True, algo: int = 0, timeout_ms: int | None = None,
-                 tail_update: str | None = None):
+                 tail_update: str | None = None, multicast: bool | None = None):
         """``tail_update`` selects how the last (conv1) bucket of the step is updated:
         "push" (default) / "pull" = split-K reduce + all-reduce + SGD in one kernel with the push or
         pull exchange, "split" = separate reduce kernel followed by the generic bucket update.
-        Environment override: DDPB_TAIL_UPDATE."""
+        Environment override: DDPB_TAIL_UPDATE.  ``multicast`` (default: DDPB_NVLS=1) asks for the
+        VMM + multicast communicator; with it, buckets above 256 KB on more than two GPUs are
+        reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
         from .comm import SymmetricComm
         self.rank, self.world_size, self.lr = rank, world_size, float(lr)
         self.device = torch.device(device)
@@ -103,7 +106,8 @@ class B200DataParallel(_EngineBase):
         self._n = n
         region = _align(n * 4, 256)
         self.param_off, self.grad_off = 0, [region, 2 * region]
-        self.comm = SymmetricComm(rank, world_size, 3 * region, timeout_ms=timeout_ms)
+        self.comm = SymmetricComm(rank, world_size, 3 * region, timeout_ms=timeout_ms,
+                                  multicast=multicast)
         params = self.comm.tensor(self.param_off, n)
         grads = [self.comm.tensor(off, n) for off in self.grad_off]
         self.model = SimpleCNNB200(batch_cap, self.device, params=params, grads=grads[0],
@@ -185,29 +189,35 @@ class B200DataParallel(_EngineBase):
         """
         m, main = self.model, self.main
         x, y = self.x_in[parity][:b], self.y_in[parity][:b]
-        m.forward_loss(x, y, b, main, parity, pack=False)
-        m.backward_head(b, main, parity)
+        with nvtx_range("fwd+loss"):
+            m.forward_loss(x, y, b, main, parity, pack=False)
+        with nvtx_range("bwd linear"):
+            m.backward_head(b, main, parity)
         self._ev_fork.record(main)
         self.side.wait_event(self._ev_fork)
         self.side2.wait_event(self._ev_fork)
-        self._update(self.bucket_fl, parity, 0, self.side)
-        m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
+        with nvtx_range("bucket fl: all-reduce+sgd, re-pack"):
+            self._update(self.bucket_fl, parity, 0, self.side)
+            m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
-        m.backward_conv2_wgrad(b, self.side2, parity)
-        self._update(self.bucket_conv2, parity, 2, self.side2)
+        with nvtx_range("bwd conv2 wgrad + bucket net.2"):
+            m.backward_conv2_wgrad(b, self.side2, parity)
+            self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
-        if self.tail_update == "split":
-            m.backward_dgrad_conv1(x, b, main, parity)
-            self._update(self.bucket_conv1, parity, 1, main)
-        else:
-            from .comm import ALGO_ONESHOT, ALGO_PUSH
-            nparts = m.backward_dgrad_conv1_partials(x, b, main)
-            s1, n1 = self.bucket_conv1
-            # split-K reduce of the conv1 partials + all-reduce + 1/W + SGD in ONE kernel: this
-            # bucket is the tail of the step's critical path
-            self.comm.reduce_allreduce_sgd(
-                m.scr_w1, nparts, n1, self.grad_off[parity] + s1 * 4, self.param_off + s1 * 4, m.lr_dev,
-                algo=ALGO_PUSH if self.tail_update == "push" else ALGO_ONESHOT, slot=1, stream=main)
+        with nvtx_range("bwd conv2 dgrad, conv1 wgrad + bucket net.0"):
+            if self.tail_update == "split":
+                m.backward_dgrad_conv1(x, b, main, parity)
+                self._update(self.bucket_conv1, parity, 1, main)
+            else:
+                from .comm import ALGO_ONESHOT, ALGO_PUSH
+                nparts = m.backward_dgrad_conv1_partials(x, b, main)
+                s1, n1 = self.bucket_conv1
+                # split-K reduce of the conv1 partials + all-reduce + 1/W + SGD in ONE kernel: this
+                # bucket is the tail of the step's critical path
+                self.comm.reduce_allreduce_sgd(
+                    m.scr_w1, nparts, n1, self.grad_off[parity] + s1 * 4, self.param_off + s1 * 4,
+                    m.lr_dev, algo=ALGO_PUSH if self.tail_update == "push" else ALGO_ONESHOT, slot=1,
+                    stream=main)
         main.wait_event(self._ev_join2)
         main.wait_event(self._ev_join)
 
@@ -256,7 +266,7 @@ class B200DataParallel(_EngineBase):
                 with torch.cuda.graph(g, stream=self.main):
                     self._enqueue(b, parity)
                 self._graphs[key] = g
-            with torch.cuda.stream(self.main):
+            with torch.cuda.stream(self.main), nvtx_range("step graph replay"):
                 g.replay()
         else:
             with torch.cuda.stream(self.main):

@@ -18,6 +18,7 @@ from .parallel.engine import make_engine
 from .parallel.process_group import cleanup, control_device, setup
 from .utils import checkpoint as ckpt
 from .utils.data import get_dataloader
+from .utils.trace import StepTimer, TraceWriter, nvtx_range
 
 LEARNING_RATE = 0.01   # reference train_ddp.py:41
 LOG_INTERVAL = 100     # reference train_ddp.py:201
@@ -31,6 +32,7 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
     batch_size: per-rank batch (reference train_ddp.py:17-25)."""
     device = setup(rank=rank, world_size=world_size, backend=backend)
     engine = None
+    trace = TraceWriter(rank=rank)
     try:
         print(f"Rank {rank} initialized", flush=True)
         engine = make_engine(rank, world_size, device, batch_cap=batch_size, lr=lr)
@@ -52,21 +54,30 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
             engine.set_lr(holder["lr"])
             print(f"Rank {rank}: Resumed from checkpoint, next epoch {start_epoch}", flush=True)
 
+        timer = StepTimer(device)
+        step_stream = getattr(engine, "main", None)
         for epoch in range(start_epoch, epochs):
             sampler.set_epoch(epoch)
             print(f"Rank {rank}: Starting epoch {epoch}", flush=True)
             t0 = time.perf_counter()
             seen = 0
-            for batch_idx, (images, labels) in enumerate(loader):
-                if max_batches is not None and batch_idx >= max_batches:
-                    break
-                loss = engine.step(images, labels)
-                seen += int(images.shape[0])
-                if rank == 0 and batch_idx % log_interval == 0:
-                    print(f"Epoch {epoch} | Batch {batch_idx} | Loss: {engine.read_loss(loss):.4f}",
-                          flush=True)
+            with trace.span(f"epoch {epoch}"):
+                for batch_idx, (images, labels) in enumerate(loader):
+                    if max_batches is not None and batch_idx >= max_batches:
+                        break
+                    timer.begin(step_stream)
+                    with nvtx_range("step"):
+                        loss = engine.step(images, labels)
+                    timer.end(step_stream)
+                    seen += int(images.shape[0])
+                    if rank == 0 and batch_idx % log_interval == 0:
+                        # the only host<-device read in the loop, at the reference's cadence
+                        value = engine.read_loss(loss)
+                        print(f"Epoch {epoch} | Batch {batch_idx} | Loss: {value:.4f}", flush=True)
+                        trace.counter("loss", loss=value)
             if device.type == "cuda":
                 engine.synchronize()
+            step_stats = timer.summary(world_size, cdev)
             dt = torch.tensor([time.perf_counter() - t0, float(seen)], dtype=torch.float64, device=cdev)
             if world_size > 1:
                 tmax = dt[:1].clone()
@@ -77,9 +88,12 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
             if rank == 0:
                 secs, imgs = float(dt[0]), float(dt[1])
                 print(f"Epoch {epoch} done | {imgs / max(secs, 1e-9):.0f} img/s | "
-                      f"{secs * 1e3 / max(1, len(loader)):.3f} ms/step (max over ranks)", flush=True)
+                      f"{secs * 1e3 / max(1, len(loader)):.3f} ms/step wall, "
+                      f"{step_stats['ms_mean']:.3f} ms/step on device (max over ranks)", flush=True)
+                trace.counter("throughput", img_per_s=imgs / max(secs, 1e-9))
                 if stats is not None:
                     stats.setdefault("img_per_s", []).append(imgs / max(secs, 1e-9))
+                    stats.setdefault("device_ms_per_step", []).append(step_stats["ms_mean"])
                 ckpt.save_checkpoint(epoch, engine.state_dict(), engine.optimizer_state_dict(), ckpt_dir)
     finally:
         if engine is not None:
@@ -87,4 +101,5 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
                 engine.close()
             except Exception as e:  # pragma: no cover - best effort on an already failing path
                 print(f"Rank {rank}: engine close failed: {e}", flush=True)
+        trace.close()
         cleanup()

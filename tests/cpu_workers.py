@@ -47,3 +47,38 @@ def ours_loop_worker(rank, world_size, out_path, epochs, batch, seed, data_root)
     if rank == 0:
         torch.save({"losses": losses, "model": eng.state_dict()}, out_path)
     cleanup()
+
+
+def fd_exchange_worker(rank, world_size, out_path):
+    """Each rank hands every peer the read end of a pipe it has written its rank into."""
+    import torch.distributed as dist
+    from ddp_b200.parallel.comm import exchange_fds
+    from ddp_b200.parallel.process_group import cleanup, setup
+    setup(rank, world_size, backend="gloo")
+    tok = ["tok-%d" % os.getpid() if rank == 0 else None]
+    dist.broadcast_object_list(tok, src=0)
+    r, w = os.pipe()
+    os.write(w, f"hello from {rank}".encode() * (world_size - 1))
+    os.close(w)
+    got = exchange_fds(rank, world_size, [r], tok[0])
+    os.close(r)
+    seen = {}
+    for src, fds in enumerate(got):
+        assert (len(fds) == 1) == (src != rank), (src, fds)
+        for fd in fds:
+            seen[src] = os.read(fd, len(f"hello from {src}")).decode()
+            os.close(fd)
+    # a second round on a fresh token where only rank 0 has something to give (the multicast case)
+    r2, w2 = os.pipe()
+    os.write(w2, b"mc" * world_size)
+    os.close(w2)
+    got = exchange_fds(rank, world_size, [r2] if rank == 0 else [], tok[0] + "c")
+    os.close(r2)
+    for src, fds in enumerate(got):
+        assert len(fds) == (1 if (src == 0 and rank != 0) else 0), (rank, src, fds)
+        for fd in fds:
+            seen["mc"] = os.read(fd, 2).decode()
+            os.close(fd)
+    with open(f"{out_path}.{rank}", "w") as f:
+        f.write(repr(sorted((str(k), v) for k, v in seen.items())))
+    cleanup()

@@ -247,8 +247,121 @@ def scenario_bucketed():
         print("bucketed ok", flush=True)
 
 
+def scenario_nvls():
+    """VMM + multicast communicator: descriptor exchange, multicast bind, then the in-switch
+    (multimem.ld_reduce / multimem.st) all-reduce and fused all-reduce+SGD.  Prints
+    "nvls unavailable" (the test then skips) when the box cannot create multicast objects."""
+    import warnings
+    from ddp_b200.parallel.comm import ALGO_NVLS, ALGO_TWOSHOT, SymmetricComm
+    rank, world, dev = _init()
+    n = 1 << 20
+    region = n * 4
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        comm = SymmetricComm(rank, world, 3 * region, multicast=True)
+    if not comm.multicast:
+        if rank == 0:
+            why = "; ".join(str(w.message) for w in caught) or "no reason given"
+            print(f"nvls unavailable: {why}", flush=True)
+        # the fallback communicator must still work
+        lr = torch.tensor([0.01], device=dev)
+        comm.tensor(0, n).fill_(1.0)
+        comm.tensor(region, n).fill_(float(rank + 1))
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_sgd(region, 0, n, lr, algo=ALGO_TWOSHOT, slot=0)
+        torch.cuda.synchronize()
+        want = 1.0 - 0.01 * sum(range(1, world + 1)) / world
+        assert torch.allclose(comm.tensor(0, n), torch.full((n,), want, device=dev), atol=1e-6)
+        comm.close()
+        return
+    # plain all-reduce through the switch, fp32 and bf16, several sizes incl. a ragged one
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2)):
+        esize = 4 if dtype == torch.float32 else 2
+        for nbytes in (4096, 75264, 1 << 20, region):
+            m = nbytes // esize
+            src = comm.tensor(0, m, dtype)
+            out = comm.tensor(region, m, dtype)
+            for it in range(2):
+                src.copy_(_rank_data(11 + it, rank, m, dtype, dev))
+                torch.cuda.synchronize()
+                dist.barrier()
+                comm.allreduce(0, region, nbytes, dtype, ALGO_NVLS, slot=1)
+                torch.cuda.synchronize()
+                want = torch.zeros(m, device=dev, dtype=torch.float32)
+                for r in range(world):
+                    want += _rank_data(11 + it, r, m, dtype, dev).float()
+                err = (out.float() - want).abs().max().item()
+                assert err <= tol * max(1.0, want.abs().max().item()), (dtype, nbytes, err)
+                gathered = [torch.empty_like(out) for _ in range(world)]
+                dist.all_gather(gathered, out.clone())
+                assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas differ after NVLS all-reduce"
+                dist.barrier()
+    # fused all-reduce + 1/W + SGD through the switch
+    p = comm.tensor(0, n)
+    gr = comm.tensor(region, n)
+    lr = torch.tensor([0.01], device=dev)
+    p.copy_(_rank_data(7, 0, n, torch.float32, dev))
+    want = p.clone()
+    for it in range(4):
+        gr.copy_(_rank_data(100 + it, rank, n, torch.float32, dev))
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_sgd(region, 0, n, lr, algo=ALGO_NVLS, slot=2)
+        torch.cuda.synchronize()
+        tot = torch.zeros(n, device=dev)
+        for r in range(world):
+            tot += _rank_data(100 + it, r, n, torch.float32, dev)
+        want = want - 0.01 * (tot / world)
+        assert torch.allclose(p, want, rtol=1e-5, atol=1e-5), (it, (p - want).abs().max().item())
+        gathered = [torch.empty_like(p) for _ in range(world)]
+        dist.all_gather(gathered, p.clone())
+        assert all(torch.equal(t, gathered[0]) for t in gathered), f"replicas differ at it {it}"
+        dist.barrier()
+    comm.close()
+    if rank == 0:
+        print("nvls ok", flush=True)
+
+
+def scenario_dead_peer():
+    """Failure detection: the last rank never joins the collective; every other
+    rank's kernel must give up after the communicator's timeout and surface a CUDA error on the
+    host instead of spinning forever.  The trapped contexts are unusable afterwards, so every
+    rank leaves with os._exit."""
+    import time
+    from ddp_b200.parallel.comm import SymmetricComm
+    rank, world, dev = _init()
+    n = 4096
+    comm = SymmetricComm(rank, world, 2 * n * 4, timeout_ms=300)
+    lr = torch.tensor([0.01], device=dev)
+    comm.allreduce_sgd(n * 4, 0, n, lr, slot=0)       # a healthy round first
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == world - 1:
+        time.sleep(6.0)                                # "dead": never launches the second round
+        os._exit(0)
+    t0 = time.perf_counter()
+    failed = False
+    try:
+        comm.allreduce_sgd(n * 4, 0, n, lr, slot=0)
+        torch.cuda.synchronize()
+    except Exception as e:  # torch.AcceleratorError / RuntimeError depending on the torch version
+        failed = True
+        msg = str(e).splitlines()[0][:120]
+    dt = time.perf_counter() - t0
+    if not failed:
+        print(f"rank {rank}: collective with a dead peer returned normally: assert failed", flush=True)
+        os._exit(1)
+    if dt > 5.0:
+        print(f"rank {rank}: timeout took {dt:.1f}s: assert failed", flush=True)
+        os._exit(1)
+    if rank == 0:
+        print(f"dead_peer ok ({dt * 1e3:.0f} ms, {msg})", flush=True)
+    os._exit(0)
+
+
 if __name__ == "__main__":
-    {"bucketed": scenario_bucketed, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
+    {"dead_peer": scenario_dead_peer, "nvls": scenario_nvls, "bucketed": scenario_bucketed, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
      "dp_equiv": scenario_dp_equiv}[sys.argv[1]]()
     if dist.is_initialized():
         dist.destroy_process_group()

@@ -159,3 +159,20 @@ def test_patched_reference_resumes_from_our_checkpoint(tmp_path):
                str(work), env)
     assert out.count("Starting epoch 5") == 2 and "Starting epoch 4" not in out
     assert (work / "checkpoints" / "epoch_5.pt").exists()
+
+
+def test_fd_exchange_between_rank_processes(tmp_path):
+    """The descriptor hand-over used by the VMM/multicast communicator (AF_UNIX + SCM_RIGHTS),
+    exercised on CPU with pipes standing in for the exported allocations."""
+    from torch.multiprocessing.spawn import spawn
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import cpu_workers
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(_free_port())
+    out = str(tmp_path / "fds")
+    spawn(cpu_workers.fd_exchange_worker, args=(3, out), nprocs=3)
+    for rank in range(3):
+        seen = dict(eval(open(f"{out}.{rank}").read()))
+        for src in range(3):
+            if src != rank:
+                assert seen[str(src)] == f"hello from {src}"
+        assert (seen.get("mc") == "mc") == (rank != 0)

@@ -39,6 +39,21 @@ def test_scenario(world, scenario):
 
 
 @pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("world", WORLDS or [2])
+def test_multicast_communicator(world):
+    out = _torchrun(world, [os.path.join(ROOT, "tests", "mp_workers.py"), "nvls"], timeout=300)
+    if "nvls unavailable" in out:
+        pytest.skip(next(l for l in out.splitlines() if "nvls unavailable" in l)[:300])
+    assert "nvls ok" in out
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
+def test_dead_peer_times_out_instead_of_hanging():
+    out = _torchrun(2, [os.path.join(ROOT, "tests", "mp_workers.py"), "dead_peer"], timeout=120)
+    assert "dead_peer ok" in out
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
 def test_cli_under_torchrun_trains_and_resumes(tmp_path):
     env = {"DDP_B200_SYNTHETIC_SIZE": "2048"}
     out = _torchrun(2, [os.path.join(ROOT, "train_ddp.py"), "--epochs", "1", "--batch_size", "64"],

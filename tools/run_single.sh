@@ -23,11 +23,3 @@ bench b64 --steps 1000 --warmup 50
 DDPB_TAIL_UPDATE=pull bench b64_pull --steps 1000 --warmup 50
 DDPB_TAIL_UPDATE=split bench b64_split --steps 1000 --warmup 50
 bench b4096 --batch_size 4096 --steps 50 --warmup 5
-# eager run first (must exit 0 without ncu), then the capture: skip the warm-up steps' launches
-timeout 300 python bench.py --batch_size 4096 --steps 2 --warmup 3 --no_graph > gpurun_out/plain_b4096.log 2>&1
-rc=$?; echo "plain eager rc=$rc"
-if [ $rc -eq 0 ]; then
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:ddpb --launch-skip 43 -c 28 -f \
-    -o gpurun_out/prof_b4096_v2 python bench.py --batch_size 4096 --steps 2 --warmup 3 --no_graph > gpurun_out/ncu_full_v2.log 2>&1
-  echo "ncu rc=$?"; tail -3 gpurun_out/ncu_full_v2.log | cut -c1-300
-fi
