@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 #include <unistd.h>
 #include <new>
@@ -129,6 +130,10 @@ __device__ __forceinline__ void st_f4(float* p, const float4& v) {
                : "memory");
 }
 
+// Grid-stride iterations whose peer loads are issued back to back (registers: U*WORLD float4).
+template <int WORLD>
+constexpr int kPeerUnroll = WORLD <= 2 ? 4 : (WORLD <= 4 ? 2 : 1);
+
 // ---------------------------------------------------------------- fused all-reduce + SGD
 // n4 = number of float4 elements in the bucket (buckets are 16-byte aligned slices).
 template <int WORLD>
@@ -142,23 +147,38 @@ allreduce_sgd_oneshot_kernel(const __grid_constant__ PeerPtrs pp, int rank, int 
   flag_round<WORLD>(pp, rank, slot, e, timeout_ns);
   const float scale = -(*lr) * (1.0f / WORLD);
   float* params = reinterpret_cast<float*>(pp.p[rank] + param_off);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
-       i += (long long)gridDim.x * blockDim.x) {
-    float4 v[WORLD];
+  // U grid-stride iterations per round: all U*WORLD peer loads are issued before any is used, so
+  // a thread pays one NVLink round trip per U elements instead of one per element
+  constexpr int U = kPeerUnroll<WORLD>;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += stride * U) {
+    float4 v[U][WORLD];
 #pragma unroll
-    for (int r = 0; r < WORLD; ++r)
-      v[r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
-    float4 s = v[0];
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < n4) {
 #pragma unroll
-    for (int r = 1; r < WORLD; ++r) {
-      s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+        for (int r = 0; r < WORLD; ++r)
+          v[u][r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
+      }
     }
-    float4 p = *reinterpret_cast<float4*>(params + i * 4);
-    p.x = fmaf(scale, s.x, p.x);
-    p.y = fmaf(scale, s.y, p.y);
-    p.z = fmaf(scale, s.z, p.z);
-    p.w = fmaf(scale, s.w, p.w);
-    *reinterpret_cast<float4*>(params + i * 4) = p;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < n4) {
+        float4 s = v[u][0];
+#pragma unroll
+        for (int r = 1; r < WORLD; ++r) {
+          s.x += v[u][r].x; s.y += v[u][r].y; s.z += v[u][r].z; s.w += v[u][r].w;
+        }
+        float4 p = *reinterpret_cast<float4*>(params + i * 4);
+        p.x = fmaf(scale, s.x, p.x);
+        p.y = fmaf(scale, s.y, p.y);
+        p.z = fmaf(scale, s.z, p.z);
+        p.w = fmaf(scale, s.w, p.w);
+        *reinterpret_cast<float4*>(params + i * 4) = p;
+      }
+    }
   }
   if (threadIdx.x == 0) *ep = e;
 }
@@ -177,25 +197,38 @@ allreduce_sgd_twoshot_kernel(const __grid_constant__ PeerPtrs pp, int rank, int 
   const long long lo = per * rank;
   const long long hi = lo + per < n4 ? lo + per : n4;
   const float* params = reinterpret_cast<const float*>(pp.p[rank] + param_off);
-  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
-       i += (long long)gridDim.x * blockDim.x) {
-    float4 v[WORLD];
+  constexpr int U = kPeerUnroll<WORLD>;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * U) {
+    float4 v[U][WORLD];
 #pragma unroll
-    for (int r = 0; r < WORLD; ++r)
-      v[r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
-    float4 s = v[0];
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi) {
 #pragma unroll
-    for (int r = 1; r < WORLD; ++r) {
-      s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+        for (int r = 0; r < WORLD; ++r)
+          v[u][r] = ld_f4(reinterpret_cast<const float*>(pp.p[r] + grad_off) + i * 4);
+      }
     }
-    float4 p = *reinterpret_cast<const float4*>(params + i * 4);
-    p.x = fmaf(scale, s.x, p.x);
-    p.y = fmaf(scale, s.y, p.y);
-    p.z = fmaf(scale, s.z, p.z);
-    p.w = fmaf(scale, s.w, p.w);
 #pragma unroll
-    for (int r = 0; r < WORLD; ++r)
-      st_f4(reinterpret_cast<float*>(pp.p[r] + param_off) + i * 4, p);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < hi) {
+        float4 s = v[u][0];
+#pragma unroll
+        for (int r = 1; r < WORLD; ++r) {
+          s.x += v[u][r].x; s.y += v[u][r].y; s.z += v[u][r].z; s.w += v[u][r].w;
+        }
+        float4 p = *reinterpret_cast<const float4*>(params + i * 4);
+        p.x = fmaf(scale, s.x, p.x);
+        p.y = fmaf(scale, s.y, p.y);
+        p.z = fmaf(scale, s.z, p.z);
+        p.w = fmaf(scale, s.w, p.w);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r)
+          st_f4(reinterpret_cast<float*>(pp.p[r] + param_off) + i * 4, p);
+      }
+    }
   }
   flag_round<WORLD>(pp, rank, slot, e + 1, timeout_ns);
   if (threadIdx.x == 0) *ep = e + 1;
@@ -497,14 +530,28 @@ allreduce_nvls_kernel(const __grid_constant__ PeerPtrs pp, uint8_t* mc, int rank
   if (threadIdx.x == 0) *ep = e + 1;
 }
 
-// Remote loads over NVLink cost ~4-5 us of latency per dependent round, so the grid is sized for
-// ONE grid-stride iteration per thread wherever the block cap allows (measured: 2 MB two-shot on
-// 8 GPUs took 43 us with 4 iterations per thread).
+// Every dependent round of peer loads costs a full NVLink round trip (~4.5 us), so a thread should
+// need as few rounds as possible — but these kernels also run beside the convolution backward on
+// other streams, so a small bucket must not flood the SMs with spinning blocks either.  Buckets of
+// up to 8 MB get at most kSmallMaxBlocks blocks (the fused kernels issue kPeerUnroll iterations of
+// loads per round); DDPB_COMM_MAXBLOCKS overrides the cap.
+constexpr int kSmallMaxBlocks = 48;
+static int small_block_cap() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("DDPB_COMM_MAXBLOCKS");
+    v = e ? atoi(e) : kSmallMaxBlocks;
+    if (v < 1) v = 1;
+    if (v > kMaxBlocks) v = kMaxBlocks;
+  }
+  return v;
+}
 static int blocks_for(long long nvec, int world, bool twoshot) {
   long long work = twoshot ? (nvec + world - 1) / world : nvec;
   long long b = (work + kCommThreads - 1) / kCommThreads;
   if (b < 1) b = 1;
-  if (b > kMaxBlocks) b = kMaxBlocks;
+  const long long cap = nvec * 16 <= (8ll << 20) ? small_block_cap() : kMaxBlocks;
+  if (b > cap) b = cap;
   return static_cast<int>(b);
 }
 

@@ -22,10 +22,15 @@
 
 namespace ddpb {
 
-constexpr int kC1Threads = 288;  // warps 0-3 producers, 4 MMA/TMEM, 5-8 epilogue
+constexpr int kC1Threads = 288;     // wgrad: warps 0-3 producers A, 4 MMA/TMEM, 5-8 producers B + epilogue
+constexpr int kC1FwdThreads = 416;  // fwd: warps 0-3 producers A, 4 MMA/TMEM, 5-8 epilogue, 9-12 producers B
 constexpr int kC1Stages = 3;
 
-constexpr int kXStages = 3;             // input-image staging ring (prefetch distance in tiles)
+// Input-image staging: each producer group owns a private ring of kXStagesG stages (so the threads
+// that wait on a stage barrier are the ones that consumed its previous phase — a ring shared by both
+// groups let a group that ran ahead mistake an old phase of the other group's tile for its own).
+constexpr int kXStagesG = 2;              // prefetch distance, in tiles of one group
+constexpr int kXStages = 2 * kXStagesG;   // stages (and barriers) in total
 constexpr uint32_t kXStageBytes = 8192;  // two images of up to 32x32 fp32
 
 // A 128-row tile touches at most two consecutive images.  One bulk async copy stages both
@@ -56,11 +61,9 @@ __device__ __forceinline__ void taps_from_stage(const float* xs, const Geom& g, 
       t[r * 3 + s] = (hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? xp[hh * g.W + ww] : 0.f;
     }
 }
-__device__ __forceinline__ void producer_sync() {  // the 128 producer threads only
-  asm volatile("bar.sync 1, 128;" ::: "memory");
-}
 __device__ __forceinline__ void producer_group_sync(int grp) {  // 128 threads of producer group grp
-  asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+  if (grp == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+  else asm volatile("bar.sync 2, 128;" ::: "memory");
 }
 
 // ------------------------------------------------------------------------------------- forward
@@ -76,7 +79,7 @@ struct C1FwdSmem {
   static constexpr uint32_t total = off_tmem + 16;
 };
 
-__global__ void __launch_bounds__(kC1Threads, 1)
+__global__ void __launch_bounds__(kC1FwdThreads, 2)
 conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
                     const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, Geom g) {
   using S = C1FwdSmem;
@@ -113,7 +116,7 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
   // nothing global may be read before it has completed.
   pdl_sync();
   // W1 [32][9] -> tf32 K-major canonical tile: word (k/4)*128 + n*4 + k%4 ; k >= 9 is zero padding
-  for (int i = tid; i < 32 * 16; i += kC1Threads) {
+  for (int i = tid; i < 32 * 16; i += kC1FwdThreads) {
     const int n = i >> 4, k = i & 15;
     reinterpret_cast<float*>(smem)[(k >> 2) * 128 + n * 4 + (k & 3)] = k < 9 ? w[n * 9 + k] : 0.f;
   }
@@ -124,35 +127,46 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
-  if (warp < 4) {
-    // ---- producers: one im2col row per thread; the tile's input images arrive by bulk copy
-    if (tid == 0) {
-      int pre = 0;
-      for (int t = blockIdx.x; t < g.ntiles && pre < kXStages; t += gridDim.x, ++pre)
-        x_stage_issue(x, g, t, s_base + S::off_x + pre * kXStageBytes, bar_x + pre * 8);
+  if (warp < 4 || warp >= 9) {
+    // ---- producers: one im2col row per thread; the tile's input images arrive by bulk copy.
+    // Two groups of 128 threads take alternate tiles, so two tiles are being built at any time.
+    const int grp = warp < 4 ? 0 : 1;
+    const int ptid = grp ? tid - 288 : tid;
+    if (ptid == 0) {  // this group's first tiles: it = grp, grp + 2, ...
+      for (int j = 0; j < kXStagesG; ++j) {
+        const long long t = (long long)blockIdx.x + (long long)(grp + 2 * j) * gridDim.x;
+        if (t < g.ntiles)
+          x_stage_issue(x, g, static_cast<int>(t),
+                        s_base + S::off_x + (grp * kXStagesG + j) * kXStageBytes,
+                        bar_x + (grp * kXStagesG + j) * 8);
+      }
     }
-    int it = 0;
-    for (int t = blockIdx.x; t < g.ntiles; t += gridDim.x, ++it) {
+    for (int it = grp;; it += 2) {
+      const long long tl = (long long)blockIdx.x + (long long)it * gridDim.x;
+      if (tl >= g.ntiles) break;
+      const int t = static_cast<int>(tl);
       const int stage = it % kC1Stages;
       const uint32_t phase = (it / kC1Stages) & 1;
-      const int xst = it % kXStages;
+      const int j = it >> 1;  // this group's tile counter
+      const int xst = grp * kXStagesG + j % kXStagesG;
       int img, h, wc;
-      const bool valid = decode_row(g, t * kTileM + tid, img, h, wc);
+      const bool valid = decode_row(g, t * kTileM + ptid, img, h, wc);
       float tp[9];
 #pragma unroll
       for (int i = 0; i < 9; ++i) tp[i] = 0.f;
-      mbar_wait(bar_x + xst * 8, (it / kXStages) & 1);
+      mbar_wait(bar_x + xst * 8, (j / kXStagesG) & 1);
       if (valid)
         taps_from_stage(reinterpret_cast<const float*>(smem + S::off_x + xst * kXStageBytes), g,
                         img - x_stage_first_image(g, t), h, wc, tp);
-      producer_sync();  // every producer has read this x stage: refill it for tile it + kXStages
-      if (tid == 0) {
-        const int tn = t + kXStages * gridDim.x;
+      producer_group_sync(grp);  // the whole group has read this x stage: refill it
+      if (ptid == 0) {
+        const long long tn = tl + 2ll * kXStagesG * gridDim.x;  // this group's tile j + kXStagesG
         if (tn < g.ntiles)
-          x_stage_issue(x, g, tn, s_base + S::off_x + xst * kXStageBytes, bar_x + xst * 8);
+          x_stage_issue(x, g, static_cast<int>(tn), s_base + S::off_x + xst * kXStageBytes,
+                        bar_x + xst * 8);
       }
       mbar_wait(bar_empty + stage * 8, phase ^ 1);
-      uint8_t* a = smem + S::off_a + stage * S::a_stage + tid * 16;
+      uint8_t* a = smem + S::off_a + stage * S::a_stage + ptid * 16;
       *reinterpret_cast<float4*>(a) = make_float4(tp[0], tp[1], tp[2], tp[3]);
       *reinterpret_cast<float4*>(a + S::a_plane) = make_float4(tp[4], tp[5], tp[6], tp[7]);
       *reinterpret_cast<float4*>(a + 2 * S::a_plane) = make_float4(tp[8], 0.f, 0.f, 0.f);
@@ -278,10 +292,14 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
     // tiles' im2col rows are being built at any time; group 1 also runs the epilogue at the end.
     const int grp = warp < 4 ? 0 : 1;
     const int ptid = grp ? tid - 160 : tid;
-    if (tid == 0) {
-      int pre = 0;
-      for (int t = blockIdx.x; t < g.ntiles && pre < kXStages; t += gridDim.x, ++pre)
-        x_stage_issue(x, g, t, s_base + S::off_x + pre * kXStageBytes, bar_x + pre * 8);
+    if (ptid == 0) {  // this group's first tiles: it = grp, grp + 2, ...
+      for (int j = 0; j < kXStagesG; ++j) {
+        const long long t = (long long)blockIdx.x + (long long)(grp + 2 * j) * gridDim.x;
+        if (t < g.ntiles)
+          x_stage_issue(x, g, static_cast<int>(t),
+                        s_base + S::off_x + (grp * kXStagesG + j) * kXStageBytes,
+                        bar_x + (grp * kXStagesG + j) * 8);
+      }
     }
     for (int it = grp;; it += 2) {
       const long long tl = (long long)blockIdx.x + (long long)it * gridDim.x;
@@ -289,19 +307,20 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       const int t = static_cast<int>(tl);
       const int stage = it % kC1Stages;
       const uint32_t phase = (it / kC1Stages) & 1;
-      const int xst = it % kXStages;
+      const int j = it >> 1;  // this group's tile counter
+      const int xst = grp * kXStagesG + j % kXStagesG;
       int img, h, wc;
       const bool valid = decode_row(g, t * kTileM + ptid, img, h, wc);
       float tp[9];
 #pragma unroll
       for (int i = 0; i < 9; ++i) tp[i] = 0.f;
-      mbar_wait(bar_x + xst * 8, (it / kXStages) & 1);
+      mbar_wait(bar_x + xst * 8, (j / kXStagesG) & 1);
       if (valid)
         taps_from_stage(reinterpret_cast<const float*>(smem + S::off_x + xst * kXStageBytes), g,
                         img - x_stage_first_image(g, t), h, wc, tp);
       producer_group_sync(grp);  // the whole group has read this x stage: refill it
       if (ptid == 0) {
-        const long long tn = tl + (long long)kXStages * gridDim.x;
+        const long long tn = tl + 2ll * kXStagesG * gridDim.x;  // this group's tile j + kXStagesG
         if (tn < g.ntiles)
           x_stage_issue(x, g, static_cast<int>(tn), s_base + S::off_x + xst * kXStageBytes,
                         bar_x + xst * 8);
@@ -425,7 +444,7 @@ int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out,
     configured[dev & 63] = true;
   }
   const int grid = c1_grid(g.ntiles);
-  return static_cast<int>(launch_k(conv1_fwd_tc_kernel, dim3(grid), dim3(kC1Threads), C1FwdSmem::total,
+  return static_cast<int>(launch_k(conv1_fwd_tc_kernel, dim3(grid), dim3(kC1FwdThreads), C1FwdSmem::total,
                                    static_cast<cudaStream_t>(stream), x, w, b,
                                    static_cast<__nv_bfloat16*>(out), g));
 }

@@ -294,12 +294,16 @@ constexpr uint32_t kLbDlBytes = 4 * kTileM * 16;          // 8,192
 constexpr uint32_t kLbStage = kLbActBytes + kLbDlBytes;
 constexpr uint32_t kLbWbBytes = 4 * kLbFB * 128;          // 8,192 per feature block (hi, hi, lo, lo)
 
-constexpr uint32_t kLbOutPitch = kLbFB * 16 + 16;  // staged dX row of one image: 256 B + 16 B bank skew
+// Eight epilogue warps: two per TMEM lane quadrant, each owning half of the 128 accumulator columns.
+// (With four, each scheduler had ONE epilogue warp running a ~550-instruction dependent chain per
+// tile — tcgen05.ld, mask, pack, stage, store — and the whole kernel waited on it.)
+constexpr int kLbThreads = 416;  // warps 0-3 gather, 4 MMA/TMEM, 5-12 epilogue
+constexpr uint32_t kLbOutPitch = (kLbFB / 2) * 16 + 16;  // staged half row of one image: 128 B + 16 B bank skew
 
 struct LinBwdSmem {
   static constexpr uint32_t off_wb = kLbStages * kLbStage;          // 2 buffers
-  static constexpr uint32_t off_out = off_wb + 2 * kLbWbBytes;      // per epilogue warp: 32 rows
-  static constexpr uint32_t off_bar = off_out + 4 * 32 * kLbOutPitch;
+  static constexpr uint32_t off_out = off_wb + 2 * kLbWbBytes;      // per epilogue warp: 32 half rows
+  static constexpr uint32_t off_bar = off_out + 8 * 32 * kLbOutPitch;
   // full[ST], empty[ST], wbfull[2], wbfree[2], d1full[2], d1free[2], dwfull, dwfree
   static constexpr uint32_t nbar = 2 * kLbStages + 12;
   static constexpr uint32_t off_tmem = off_bar + nbar * 8;
@@ -307,7 +311,7 @@ struct LinBwdSmem {
 };
 
 template <int NOUT>
-__global__ void __launch_bounds__(kLinThreads, 1)
+__global__ void __launch_bounds__(kLbThreads, 1)
 linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16* __restrict__ dlp,
                      const __nv_bfloat16* __restrict__ wb, __nv_bfloat16* __restrict__ dact,
                      float* __restrict__ dW, Geom g, int HW, int nkc, int nkc_pad, int C) {
@@ -330,13 +334,13 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
   if (tid == 0) {
     for (int i = 0; i < kLbStages; ++i) {
       mbar_init(bar_full + i * 8, 129);   // 128 cp.async completions + the dlogits-tile bulk copy
-      mbar_init(bar_empty + i * 8, 129);  // MMA commit + 128 epilogue threads (mask read)
+      mbar_init(bar_empty + i * 8, 257);  // MMA commit + 256 epilogue threads (mask read)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_wbfull + i * 8, 1);
       mbar_init(bar_wbfree + i * 8, 1);
       mbar_init(bar_d1full + i * 8, 1);
-      mbar_init(bar_d1free + i * 8, 128);
+      mbar_init(bar_d1free + i * 8, 256);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_dwfull + i * 8, 1);
@@ -451,7 +455,8 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
     }
   } else {
     // ---------------- epilogue
-    const int q = warp & 3;
+    const int q = warp & 3;          // TMEM lane quadrant this warp may read
+    const int half = (warp - 5) >> 2;  // which 64 of the 128 accumulator columns (8 of the 16 chunks)
     const int row = q * 32 + lane;  // image within the tile (dX) / feature within the block (dW)
     int it = 0, fbi = 0;
     for (int fb = blockIdx.x; fb < nfb; fb += gridDim.x, ++fbi) {
@@ -465,17 +470,19 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
           my_off = ((long long)chunk * g.plane_rows + kGuard + (long long)(h + 1) * g.PW + (w + 1)) * 8;
         }
       }
+      // this lane's chunk in the coalesced write-out below
+      const long long off = __shfl_sync(0xffffffffu, my_off, half * 8 + (lane & 7));
       for (int mt = 0; mt < mtiles; ++mt, ++it) {
         const int stage = it % kLbStages;
         const int acc = it & 1;
-        const int img = mt * kTileM + row;
         mbar_wait(bar_d1full + acc * 8, (it >> 1) & 1);
         tc_fence_after();
         const uint8_t* sact = smem + stage * kLbStage + (row >> 3) * 128 + (row & 7) * 16;
-        // masked dX row of this image -> this warp's staging rows (256 B per image)
+        // masked dX half row of this image -> this warp's staging rows (128 B per image)
         uint8_t* sout = smem + S::off_out + (warp - 5) * 32 * kLbOutPitch;
-#pragma unroll 1
-        for (int c0 = 0; c0 < 128; c0 += 32) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c0 = half * 64 + cc * 32;
           uint32_t v[32];
           tmem_ld32(tmem_dx + (static_cast<uint32_t>(q * 32) << 16) + acc * 128 + c0, v);
           tmem_ld_wait();
@@ -492,19 +499,18 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
               const float x1 = bf16_hi(mp[e]) > 0.f ? __uint_as_float(v[j * 8 + 2 * e + 1]) : 0.f;
               op[e] = pack_bf16x2(x0, x1);
             }
-            *reinterpret_cast<uint4*>(sout + lane * kLbOutPitch + kl * 16) = o;
+            *reinterpret_cast<uint4*>(sout + lane * kLbOutPitch + (cc * 4 + j) * 16) = o;
           }
         }
         __syncwarp();
-        // coalesced write-out: each instruction stores two images x 16 chunks = two 256 B runs
+        // coalesced write-out: each instruction stores four images x 8 chunks = four 128 B runs
         {
-          const int kl = lane & 15;
-          const long long off = __shfl_sync(0xffffffffu, my_off, kl);
+          const int kl8 = lane & 7;
 #pragma unroll 4
-          for (int r2 = 0; r2 < 16; ++r2) {
-            const int il = 2 * r2 + (lane >> 4);
+          for (int r4 = 0; r4 < 8; ++r4) {
+            const int il = 4 * r4 + (lane >> 3);
             const int im = mt * kTileM + q * 32 + il;
-            const uint4 o = *reinterpret_cast<const uint4*>(sout + il * kLbOutPitch + kl * 16);
+            const uint4 o = *reinterpret_cast<const uint4*>(sout + il * kLbOutPitch + kl8 * 16);
             if (off >= 0 && im < g.batch)
               *reinterpret_cast<uint4*>(dact + (long long)im * g.PHW * 8 + off) = o;
           }
@@ -514,6 +520,7 @@ linear_bwd_tc_kernel(const __nv_bfloat16* __restrict__ act, const __nv_bfloat16*
         mbar_arrive(bar_d1free + acc * 8);
         mbar_arrive(bar_empty + stage * 8);  // done reading the activation tile (mask)
       }
+      if (half != 0) continue;  // the dW read-out below is the first four warps' job
       // dW of this feature block: row = feature kl*8 + e
       const int wbuf = fbi & 1;
       mbar_wait(bar_dwfull + wbuf * 8, (fbi >> 1) & 1);
@@ -574,7 +581,7 @@ extern "C" int ddpb_linear_bwd_tc(const void* act, const void* dl_packed, const 
   const int nfb = (nkc + kLbFB - 1) / kLbFB;
   const int sms = ddpb_num_sms();
   const int grid = nfb < sms ? nfb : sms;
-  return static_cast<int>(launch_k(linear_bwd_tc_kernel<10>, dim3(grid), dim3(kLinThreads),
+  return static_cast<int>(launch_k(linear_bwd_tc_kernel<10>, dim3(grid), dim3(kLbThreads),
                                    LinBwdSmem::total, static_cast<cudaStream_t>(stream),
                                    static_cast<const __nv_bfloat16*>(act),
                                    static_cast<const __nv_bfloat16*>(dl_packed), wb,

@@ -93,6 +93,9 @@ class B200DataParallel(_EngineBase):
         self.algo = algo
         import os
         self.tail_update = tail_update or os.environ.get("DDPB_TAIL_UPDATE", "push")
+        # timing diagnostics only (the step is then WRONG): skip the update of the named buckets to see
+        # which stream is the critical path, e.g. DDPB_ABLATE=conv2 or DDPB_ABLATE=fl,pack
+        self._ablate = set(filter(None, os.environ.get("DDPB_ABLATE", "").split(",")))
         if self.tail_update not in ("push", "pull", "split"):
             raise ValueError(f"tail_update must be push, pull or split, got {self.tail_update!r}")
         # programmatic dependent launch pays off for latency-bound (small-batch) steps only
@@ -197,17 +200,23 @@ class B200DataParallel(_EngineBase):
         self.side.wait_event(self._ev_fork)
         self.side2.wait_event(self._ev_fork)
         with nvtx_range("bucket fl: all-reduce+sgd, re-pack"):
-            self._update(self.bucket_fl, parity, 0, self.side)
-            m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
+            if "fl" not in self._ablate:
+                self._update(self.bucket_fl, parity, 0, self.side)
+            if "pack" not in self._ablate:
+                m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
         with nvtx_range("bwd conv2 wgrad + bucket net.2"):
             m.backward_conv2_wgrad(b, self.side2, parity)
-            self._update(self.bucket_conv2, parity, 2, self.side2)
+            if "conv2" not in self._ablate:
+                self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
         with nvtx_range("bwd conv2 dgrad, conv1 wgrad + bucket net.0"):
             if self.tail_update == "split":
                 m.backward_dgrad_conv1(x, b, main, parity)
-                self._update(self.bucket_conv1, parity, 1, main)
+                if "conv1" not in self._ablate:
+                    self._update(self.bucket_conv1, parity, 1, main)
+            elif "conv1" in self._ablate:
+                m.backward_dgrad_conv1_partials(x, b, main)
             else:
                 from .comm import ALGO_ONESHOT, ALGO_PUSH
                 nparts = m.backward_dgrad_conv1_partials(x, b, main)

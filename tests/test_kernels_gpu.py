@@ -58,7 +58,8 @@ def test_conv1_fwd(nat, batch, cap):
     assert _lay().border_rows_are_zero(out, batch, H, W)
 
 
-@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (5, 16), (300, 300)])
+# 2500 images = 17.6K tiles = ~60 tiles per CTA: long enough for the two producer groups to drift apart
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (5, 16), (300, 300), (2500, 2500)])
 def test_conv1_fwd_tcgen05_tf32(nat, batch, cap):
     torch.manual_seed(10)
     x = torch.rand(batch, 1, H, W, device="cuda")
@@ -73,7 +74,7 @@ def test_conv1_fwd_tcgen05_tf32(nat, batch, cap):
     assert _lay().border_rows_are_zero(out, batch, H, W)
 
 
-@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (300, 300)])
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (300, 300), (2500, 2500)])
 def test_conv1_wgrad_tcgen05(nat, batch, cap):
     torch.manual_seed(11)
     x = torch.rand(batch, 1, H, W, device="cuda")
@@ -239,7 +240,7 @@ def test_linear_fwd_tcgen05(nat, batch, cap):
     _report("dbias", dbias, dz.sum(0), 1e-5, 1e-3)
 
 
-@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (130, 130), (300, 300)])
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (130, 130), (300, 300), (1100, 1100)])
 def test_linear_bwd_tcgen05(nat, batch, cap):
     torch.manual_seed(13)
     C = 64

@@ -1,5 +1,7 @@
 """Top stall locations of one kernel in an .ncu-rep (reads the source page; no GPU needed).
-    python tools/ncu_hot.py gpurun_out/prof.ncu-rep conv1_fwd_tc_kernel [top=25] [view=sass|cuda]
+    python tools/ncu_hot.py gpurun_out/prof.ncu-rep conv1_fwd_tc_kernel [top=25] [view=sass|cuda] [skip=0]
+(`skip` selects the (skip+1)-th captured launch with that base name, e.g. the dgrad instantiation of
+conv3x3_tc_kernel is launch 1 when the forward one is launch 0.)
 Prints the SASS (or CUDA source, needs -lineinfo + --import-source on) lines with the most warp
 stall samples, their share, and instruction counts, plus the stall-reason totals."""
 import csv
@@ -11,7 +13,9 @@ def main():
     rep, kernel = sys.argv[1], sys.argv[2]
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 25
     view = sys.argv[4] if len(sys.argv) > 4 else "sass"
-    cmd = ["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", kernel, "--launch-count", "1"]
+    skip = sys.argv[5] if len(sys.argv) > 5 else "0"
+    cmd = ["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", kernel, "--launch-skip", skip,
+           "--launch-count", "1"]
     if view == "cuda":
         cmd += ["--print-source", "cuda"]
     raw = subprocess.run(cmd, capture_output=True, text=True).stdout
