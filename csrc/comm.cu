@@ -45,9 +45,12 @@ constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * kMaxWorld;
 constexpr size_t kEpochWords = (size_t)kSlots * kMaxBlocks;
 // Flag-carrying ("LL") staging lines for the latency-bound tiny buckets: per slot, two epochs
 // (double buffer) x source rank x kLLMaxN 8-byte {epoch, fp32 payload} words.
-constexpr int kLLMaxN = 32 * kMaxBlocks;
+constexpr int kLLMaxN = 32 * 608;  // 19,456 values: covers the conv2 wgrad accumulator image (18,944)
 constexpr size_t kLLWordsPerSlot = 2ull * kMaxWorld * kLLMaxN;
+// after the status word: per slot {epoch, finished-block counter} of the flag-carrying kernels
+constexpr size_t kLLCtlWord = kFlagWords + kEpochWords + 16;
 constexpr size_t kLLOffset = ((kFlagWords + kEpochWords + 64) * 4 + 255) / 256 * 256;
+static_assert(kLLCtlWord + 2 * kSlots <= kFlagWords + kEpochWords + 64, "LL control words overflow");
 // header: flags | epochs | status word | LL lines, rounded up
 constexpr size_t kHeaderBytes = (kLLOffset + (size_t)kSlots * kLLWordsPerSlot * 8 + 4095) / 4096 * 4096;
 constexpr int kCommThreads = 512;
@@ -82,6 +85,9 @@ __device__ __forceinline__ uint32_t* epoch_word(uint8_t* base, int slot, int blo
 }
 __device__ __forceinline__ uint32_t* status_word(uint8_t* base) {
   return reinterpret_cast<uint32_t*>(base) + kFlagWords + kEpochWords;
+}
+__device__ __forceinline__ uint32_t* ll_ctl(uint8_t* base, int slot) {
+  return reinterpret_cast<uint32_t*>(base) + kLLCtlWord + 2 * slot;
 }
 __device__ __forceinline__ uint64_t* ll_line(uint8_t* base, int slot, uint32_t epoch, int src) {
   return reinterpret_cast<uint64_t*>(base + kLLOffset) +
@@ -302,17 +308,45 @@ reduce_allreduce_sgd_kernel(const __grid_constant__ PeerPtrs pp, int rank, int s
 // Staging lines are double-buffered by epoch parity; a rank can only be one call ahead of a peer
 // (call e+1 cannot finish without that peer's words of e+1, which the peer sends after it has
 // finished reading e), so a line is never overwritten while it is still being read.
-template <int WORLD>
+// The epoch is one word per slot (all blocks read it on entry; the last block to finish bumps
+// it), so the grid is not limited by the per-block flag words of the pull kernels.
+//
+// MAP selects where output idx of the partial vectors lives in the gradient / parameter slices:
+//   0  identity
+//   1  the conv3x3 <CI=32, CO=64> weight-gradient accumulator image (csrc/conv_tc.cu):
+//      per output channel [row0: 96 taps | 8 bias columns][row1: 96][row2: 96] ->
+//      net.2.weight[co][ci][r][s] followed by net.2.bias[co]; unused bias columns are dropped.
+template <int MAP>
+__device__ __forceinline__ int ll_dest(int idx) {
+  if (MAP == 0) return idx;
+  constexpr int CI = 32, CO = 64, n0 = 3 * CI + 8, n1 = 3 * CI, ncols = n0 + 2 * n1;
+  const int co = idx / ncols;
+  int col = idx - co * ncols, r = 0;
+  if (col < n0) {
+    if (col >= n1) return col == n1 ? CO * CI * 9 + co : -1;
+  } else if (col < n0 + n1) {
+    r = 1;
+    col -= n0;
+  } else {
+    r = 2;
+    col -= n0 + n1;
+  }
+  const int sx = col / CI, ci = col - sx * CI;
+  return (co * CI + ci) * 9 + r * 3 + sx;
+}
+
+template <int WORLD, int MAP>
 __global__ void __launch_bounds__(256)
-reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot, const float* __restrict__ partials,
-                               int nparts, int n, size_t grad_off, size_t param_off,
-                               const float* __restrict__ lr, unsigned long long timeout_ns) {
+reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot,
+                               const float* __restrict__ partials, int nparts, int n, size_t grad_off,
+                               size_t param_off, const float* __restrict__ lr,
+                               unsigned long long timeout_ns) {
   __shared__ float sm[8][32];
   pdl_sync();
   const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
   const int idx = blockIdx.x * 32 + lane;
-  uint32_t* ep = epoch_word(pp.p[rank], slot, blockIdx.x);
-  const uint32_t e = *ep + 1;
+  uint32_t* ctl = ll_ctl(pp.p[rank], slot);
+  const uint32_t e = ctl[0] + 1;
   float s = 0.f;
   if (idx < n) {
     int p = pg;
@@ -331,12 +365,13 @@ reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, in
   float tot = sm[0][lane];
 #pragma unroll
   for (int u = 1; u < 8; ++u) tot += sm[u][lane];
-  if (pg < WORLD && idx < n)
+  const int dest = idx < n ? ll_dest<MAP>(idx) : -1;
+  if (pg < WORLD && dest >= 0)
     st_relaxed_sys_u64(ll_line(pp.p[pg], slot, e, rank) + idx,
                        (static_cast<uint64_t>(e) << 32) | __float_as_uint(tot));
-  if (pg == 0 && idx < n) reinterpret_cast<float*>(pp.p[rank] + grad_off)[idx] = tot;
+  if (pg == 0 && dest >= 0) reinterpret_cast<float*>(pp.p[rank] + grad_off)[dest] = tot;
   __syncthreads();  // sm is reused below
-  if (pg < WORLD && idx < n) {
+  if (pg < WORLD && dest >= 0) {
     const uint64_t* src = ll_line(pp.p[rank], slot, e, pg) + idx;
     uint64_t v = ld_relaxed_sys_u64(src);
     if (static_cast<uint32_t>(v >> 32) != e) {
@@ -353,14 +388,21 @@ reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, in
     sm[pg][lane] = __uint_as_float(static_cast<uint32_t>(v));
   }
   __syncthreads();
-  if (pg == 0 && idx < n) {
+  if (pg == 0 && dest >= 0) {
     float acc = sm[0][lane];
 #pragma unroll
     for (int r = 1; r < WORLD; ++r) acc += sm[r][lane];
-    float* pr = reinterpret_cast<float*>(pp.p[rank] + param_off) + idx;
+    float* pr = reinterpret_cast<float*>(pp.p[rank] + param_off) + dest;
     *pr = fmaf(-(*lr) * (1.0f / WORLD), acc, *pr);
   }
-  if (threadIdx.x == 0) *ep = e;
+  // the last block to finish publishes the new epoch for the next launch on this slot
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(ctl + 1, 1u);
+    if (done == gridDim.x - 1) {
+      ctl[1] = 0;
+      ctl[0] = e;
+    }
+  }
 }
 
 // ---------------------------------------------------------------- plain all-reduce (sum)
@@ -1009,31 +1051,38 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
 }
 
 // grads[slice] = fixed-order sum of `nparts` partial vectors (each n floats, n % 4 == 0), then
-// params[slice] -= lr/world * sum_over_ranks(grads[slice]); one kernel.  n <= 32 * kMaxBlocks.
-// algo: 0 or 3 = push with flag-carrying words (lowest latency), 1 = flag round + pull.
+// params[slice] -= lr/world * sum_over_ranks(grads[slice]); one kernel.
+// algo: 0 or 3 = push with flag-carrying words (lowest latency; n <= 19,456), 1 = flag round + pull
+// (n <= 5,120).  layout: 0 = partial element i is slice element i; 1 = the partials are conv3x3
+// <32,64> weight-gradient accumulator images (n = 18,944) and the slice is net.2.weight followed by
+// net.2.bias (push only).
 int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
                               size_t grad_off, size_t param_off, const float* lr_dev, int algo,
-                              int slot, void* stream) {
+                              int layout, int slot, void* stream) {
   Comm* c = static_cast<Comm*>(comm);
   if (!c->connected) return DDPB_ERR_STATE;
   const long long blocks = (n + 31) / 32;
   if ((n & 3) || (grad_off & 15) || (param_off & 15) || slot < 0 || slot >= kSlots || nparts < 1 ||
-      !(algo == 0 || algo == 1 || algo == 3))
+      !(algo == 0 || algo == 1 || algo == 3) || !(layout == 0 || layout == 1))
     return DDPB_ERR_SHAPE;
-  if (blocks > kMaxBlocks) return DDPB_ERR_LIMIT;
+  if (layout == 1 && (algo == 1 || n != 64 * (9 * 32 + 8))) return DDPB_ERR_SHAPE;
+  if (algo == 1 ? blocks > kMaxBlocks : n > kLLMaxN) return DDPB_ERR_LIMIT;
   const PeerPtrs pp = peer_ptrs(c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const size_t go = grad_off + kHeaderBytes, po = param_off + kHeaderBytes;
+  const dim3 grid(static_cast<int>(blocks));
   DDPB_DISPATCH_WORLD(c->world, {
     if (algo == 1)
-      return static_cast<int>(launch_k(reduce_allreduce_sgd_kernel<WORLD>,
-                                       dim3(static_cast<int>(blocks)), dim3(256), 0, st, pp, c->rank,
-                                       slot, partials, nparts, static_cast<int>(n), go, po, lr_dev,
-                                       c->timeout_ns));
-    return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD>,
-                                     dim3(static_cast<int>(blocks)), dim3(256), 0, st, pp, c->rank,
-                                     slot, partials, nparts, static_cast<int>(n), go, po, lr_dev,
-                                     c->timeout_ns));
+      return static_cast<int>(launch_k(reduce_allreduce_sgd_kernel<WORLD>, grid, dim3(256), 0, st, pp,
+                                       c->rank, slot, partials, nparts, static_cast<int>(n), go, po,
+                                       lr_dev, c->timeout_ns));
+    if (layout == 1)
+      return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD, 1>, grid, dim3(256), 0, st,
+                                       pp, c->rank, slot, partials, nparts, static_cast<int>(n), go, po,
+                                       lr_dev, c->timeout_ns));
+    return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD, 0>, grid, dim3(256), 0, st, pp,
+                                     c->rank, slot, partials, nparts, static_cast<int>(n), go, po,
+                                     lr_dev, c->timeout_ns));
   });
   return static_cast<int>(cudaGetLastError());
 }

@@ -577,8 +577,8 @@ size_t ddpb_conv3x3_wgrad_scratch_bytes(int cin, int cout) {
   return static_cast<size_t>(ddpb_num_sms()) * cout * (9 * cin + 8) * sizeof(float);
 }
 
-int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, float* scratch,
-                       int cin, int cout, int batch, int batch_cap, int H, int W, void* stream) {
+static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch, int* nparts, int cin,
+                               int cout, int batch, int batch_cap, int H, int W, void* stream) {
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
@@ -598,9 +598,29 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
   DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
                         static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(in),
                         scratch, g, g_prof));
+  *nparts = grid;
+  return 0;
+}
+
+int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, float* scratch,
+                       int cin, int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  int grid = 0;
+  const int rc = conv3x3_wgrad_launch(dout, in, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
+  if (rc != 0) return rc;
+  constexpr int CI = 32, CO = 64;
   const int n = CO * (9 * CI + 8);
-  return static_cast<int>(launch_k(wgrad_reduce_kernel<CI, CO>, dim3((n + 31) / 32), dim3(256), 0, st,
-                                   static_cast<const float*>(scratch), grid, dw, db));
+  return static_cast<int>(launch_k(wgrad_reduce_kernel<CI, CO>, dim3((n + 31) / 32), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), static_cast<const float*>(scratch),
+                                   grid, dw, db));
+}
+
+// Partials only: scratch[nparts][cout * (9*cin + 8)] accumulator images (one per CTA) and their count
+// in *nparts_out (host).  Feed them to ddpb_reduce_allreduce_sgd with layout = 1 (fused split-K
+// reduce + all-reduce + SGD).
+int ddpb_conv3x3_wgrad_partials(const void* dout, const void* in, float* scratch, int* nparts_out,
+                                int cin, int cout, int batch, int batch_cap, int H, int W,
+                                void* stream) {
+  return conv3x3_wgrad_launch(dout, in, scratch, nparts_out, cin, cout, batch, batch_cap, H, W, stream);
 }
 
 }  // extern "C"

@@ -41,6 +41,12 @@ const char* ddpb_error_string(int code);
 void ddpb_set_pdl(int on);
 int ddpb_get_pdl(void);
 int ddpb_num_sms(void);
+/* Tuning hooks (tools/kprof.py, tools/mma_bench.py): SM-clock phase stamps of the conv kernels into
+ * buf[block*16 + slot] (NULL = off), and a tcgen05.mma issue-cost microbenchmark. */
+void ddpb_set_prof_buffer(void* buf);
+int ddpb_mma_microbench(int config, int a_shift16, int b_shift16, int outer, unsigned lbo_a,
+                        unsigned sbo_a, unsigned lbo_b, unsigned sbo_b,
+                        unsigned long long* out_dev, void* stream);
 
 /* ---- geometry of the activation layout */
 long long ddpb_plane_rows(int batch_cap, int H, int W);
@@ -102,6 +108,11 @@ size_t ddpb_conv3x3_wgrad_scratch_bytes(int cin, int cout);
 int ddpb_conv3x3_wgrad(const void* dout_planes, const void* in_planes, float* dw, float* db,
                        float* scratch, int cin, int cout, int batch, int batch_cap, int H, int W,
                        void* stream);
+/* Same tensor-core kernel, but the per-CTA accumulator images stay in scratch[nparts][cout*(9*cin+8)]
+ * and *nparts_out (host) receives their count: feed them to ddpb_reduce_allreduce_sgd, layout 1. */
+int ddpb_conv3x3_wgrad_partials(const void* dout_planes, const void* in_planes, float* scratch,
+                                int* nparts_out, int cin, int cout, int batch, int batch_cap, int H,
+                                int W, void* stream);
 
 /* ---- linear layer over the flattened activation (NCHW flatten order).  reference model.py:16,19.
  * fwd writes per-slice partial logits partial[S][batch][nout]; *S_out (host) receives S. */
@@ -146,10 +157,13 @@ int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int
  * ddpb_comm_create cudaMallocs this rank's buffer (header + payload, zero-filled);
  * ddpb_comm_get_handle / ddpb_comm_connect exchange CUDA IPC handles (host side, any transport).
  * Offsets are byte offsets into the payload, identical on all ranks, 16-byte aligned.
- * algo: 0 by size, 1 one-shot, 2 two-shot.  slot: independent flag channel in [0, 8).
+ * algo: 0 by size, 1 one-shot, 2 two-shot, 4 two-shot through the NVSwitch (multimem; needs the
+ * multicast communicator below).  slot: independent flag channel in [0, 8).
  * Replaces ProcessGroupNCCL + the DDP Reducer + torch.optim.SGD, reference train_ddp.py:34,199-200. */
 size_t ddpb_comm_header_bytes(void);
 int ddpb_comm_handle_bytes(void);
+int ddpb_comm_max_world(void);   /* 8 */
+int ddpb_comm_num_slots(void);   /* 8 */
 int ddpb_comm_create(int rank, int world, size_t payload_bytes, void** comm_out);
 int ddpb_comm_get_handle(void* comm, void* handle_out /* host */);
 int ddpb_comm_connect(void* comm, const void* all_handles /* host, world * handle_bytes */);
@@ -159,17 +173,38 @@ size_t ddpb_comm_payload_bytes(void* comm);
 void ddpb_comm_set_timeout_ms(void* comm, long long ms);
 int ddpb_comm_status(void* comm, unsigned int* status_out /* host */);
 int ddpb_comm_destroy(void* comm);
+/* VMM + multicast (NVLS) variant of the communicator: the buffer is a cuMemCreate allocation shared
+ * as POSIX file descriptors (the caller carries them between the rank processes, e.g. AF_UNIX +
+ * SCM_RIGHTS) and bound to one multicast object, so multimem.ld_reduce / multimem.st reduce and
+ * broadcast inside the switch.  Call order on every rank: create_vmm -> export_fd, import_peer_fd for
+ * every peer -> rank 0 mc_create (others mc_import with rank 0's descriptor) -> mc_add_device ->
+ * [all ranks agree it succeeded] -> mc_bind -> set_connected.  Every call returns 0 or an error code
+ * and never aborts, so the ranks can agree to fall back to ddpb_comm_create.
+ * ddpb_multicast_supported: 1 / 0, or < 0 when the driver API cannot be resolved. */
+int ddpb_multicast_supported(void);
+int ddpb_comm_create_vmm(int rank, int world, size_t payload_bytes, void** comm_out);
+int ddpb_comm_export_fd(void* comm, int* fd_out);
+int ddpb_comm_import_peer_fd(void* comm, int rank, int fd);
+int ddpb_comm_mc_create(void* comm, int* fd_out);
+int ddpb_comm_mc_import(void* comm, int fd);
+int ddpb_comm_mc_add_device(void* comm);
+int ddpb_comm_mc_bind(void* comm);
+int ddpb_comm_set_connected(void* comm);
+int ddpb_comm_has_multicast(void* comm);
+void* ddpb_comm_multicast_ptr(void* comm);
 /* params[slice] -= lr/world * sum_over_ranks(grads[slice]) in ONE kernel (in-kernel flags). */
 int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long n_floats,
                        const float* lr_dev, int algo, int slot, void* stream);
-/* Split-K reduce + all-reduce + SGD in ONE kernel for a latency-bound bucket (n <= 5120 floats,
- * n % 4 == 0): grads[slice] = fixed-order sum of nparts local partial vectors of n floats, then
+/* Split-K reduce + all-reduce + SGD in ONE kernel for a latency-bound bucket (n % 4 == 0):
+ * grads[slice] = fixed-order sum of nparts local partial vectors of n floats, then
  * params[slice] -= lr/world * sum_over_ranks(grads[slice]).  algo 0/3 = push exchange (8-byte
- * {epoch, value} words stored straight into the peers' staging lines, one one-way NVLink latency),
- * 1 = flag round followed by peer loads. */
+ * {epoch, value} words stored straight into the peers' staging lines, one one-way NVLink latency;
+ * n <= 19,456), 1 = flag round followed by peer loads (n <= 5,120).  layout 0: partial element i
+ * is slice element i; layout 1 (push only): the partials are the accumulator images written by
+ * ddpb_conv3x3_wgrad_partials (n = 18,944) and the slice is net.2.weight followed by net.2.bias. */
 int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
                               size_t grad_off, size_t param_off, const float* lr_dev, int algo,
-                              int slot, void* stream);
+                              int layout, int slot, void* stream);
 /* plain sum all-reduce, dtype 0 = fp32, 1 = bf16; out_off must not overlap in_off. */
 int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, int dtype, int algo,
                    int slot, void* stream);

@@ -218,6 +218,12 @@ class SimpleCNNB200(_ModelBase):
         self.nat.conv3x3_wgrad(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
                                self.batch_cap, IMG_H, IMG_W, stream)
 
+    def backward_conv2_wgrad_partials(self, batch: int, stream=None) -> int:
+        """Like backward_conv2_wgrad but leaves the gradient as per-CTA accumulator images in
+        ``self.scr_w2`` (returns their count) for the fused reduce + all-reduce + SGD kernel."""
+        return self.nat.conv3x3_wgrad_partials(self.dact2, self.act1, self.scr_w2, C1, C2, batch,
+                                               self.batch_cap, IMG_H, IMG_W, stream)
+
     def backward_dgrad_conv1(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 data gradient (with ReLU') followed by the conv1 weight + bias gradient."""
         nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W

@@ -41,6 +41,7 @@ _SIGNATURES = {
     "ddpb_conv3x3_dgrad": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_wgrad_scratch_bytes": (c_size_t, [I, I]),
     "ddpb_conv3x3_wgrad": (I, [P, P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_wgrad_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_linear_fwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_fwd": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_softmax_xent": (I, [P, I, P, P, P, P, P, P, I, I, P]),
@@ -198,6 +199,16 @@ def conv3x3_wgrad_scratch_bytes(cin, cout) -> int:
 def conv3x3_wgrad(dout, inp, dw, db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
     check(lib().ddpb_conv3x3_wgrad(ptr(dout), ptr(inp), ptr(dw), ptr(db), ptr(scr), cin, cout,
                                    batch, batch_cap, H, W, stream_ptr(stream)), "conv3x3_wgrad")
+
+
+def conv3x3_wgrad_partials(dout, inp, scr, cin, cout, batch, batch_cap, H, W, stream=None) -> int:
+    """Per-CTA accumulator images only (scr[nparts][cout*(9*cin+8)]); returns nparts.  Consumed by
+    SymmetricComm.reduce_allreduce_sgd(..., layout=LAYOUT_CONV3X3_WGRAD)."""
+    n = c_int(0)
+    check(lib().ddpb_conv3x3_wgrad_partials(ptr(dout), ptr(inp), ptr(scr), ctypes.byref(n), cin, cout,
+                                            batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv3x3_wgrad_partials")
+    return n.value
 
 
 def linear_fwd_scratch_bytes(nout, C, batch_cap, H, W) -> int:

@@ -61,7 +61,7 @@ for _name, _res, _args in (
     ("ddpb_comm_has_multicast", I, [P]),
     ("ddpb_comm_multicast_ptr", c_void_p, [P]),
     ("ddpb_allreduce_sgd", I, [P, SZ, SZ, LL, P, I, I, P]),
-    ("ddpb_reduce_allreduce_sgd", I, [P, P, I, LL, SZ, SZ, P, I, I, P]),
+    ("ddpb_reduce_allreduce_sgd", I, [P, P, I, LL, SZ, SZ, P, I, I, I, P]),
     ("ddpb_allreduce", I, [P, SZ, SZ, LL, I, I, I, P]),
     ("ddpb_broadcast", I, [P, SZ, LL, I, I, P]),
 ):
@@ -69,6 +69,29 @@ for _name, _res, _args in (
 
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH, ALGO_NVLS = 0, 1, 2, 3, 4
 DTYPE_CODES = {torch.float32: 0, torch.bfloat16: 1}
+# how partial element i maps into the gradient/parameter slice of reduce_allreduce_sgd
+LAYOUT_IDENTITY, LAYOUT_CONV3X3_WGRAD = 0, 1
+CONV3X3_WGRAD_IMAGE = 64 * (9 * 32 + 8)  # floats per partial for LAYOUT_CONV3X3_WGRAD
+
+
+def conv3x3_wgrad_image_dest() -> torch.Tensor:
+    """Destination index (into net.2.weight ++ net.2.bias, -1 = unused column) of every element of a
+    conv3x3 <32,64> weight-gradient accumulator image; the Python restatement of ll_dest<1> in
+    csrc/comm.cu, used by the tests."""
+    CI, CO = 32, 64
+    n0, n1 = 3 * CI + 8, 3 * CI
+    ncols = n0 + 2 * n1
+    idx = torch.arange(CO * ncols)
+    co, col = idx // ncols, idx % ncols
+    dest = torch.full_like(idx, -1)
+    r = torch.where(col < n0, 0, torch.where(col < n0 + n1, 1, 2))
+    c = torch.where(col < n0, col, torch.where(col < n0 + n1, col - n0, col - n0 - n1))
+    tap = (r > 0) | (col < n1)
+    sx, ci = c // CI, c % CI
+    dest[tap] = ((co * CI + ci) * 9 + r * 3 + sx)[tap]
+    bias = (r == 0) & (col == n1)
+    dest[bias] = (CO * CI * 9 + co)[bias]
+    return dest
 
 
 class _RawCudaBuffer:
@@ -281,14 +304,17 @@ class SymmetricComm:
 
     def reduce_allreduce_sgd(self, partials: torch.Tensor, nparts: int, n_floats: int, grad_off: int,
                              param_off: int, lr_dev: torch.Tensor, algo: int = ALGO_AUTO,
-                             slot: int = 0, stream=None) -> None:
+                             layout: int = LAYOUT_IDENTITY, slot: int = 0, stream=None) -> None:
         """One kernel: grads[slice] = sum of ``nparts`` local partial vectors (fixed order), then
         params[slice] -= lr * mean_over_ranks(grads[slice]).  ``algo``: ALGO_PUSH (default; every
         rank stores flag-carrying words straight into its peers' staging lines) or ALGO_ONESHOT
-        (flag round, then pull)."""
+        (flag round, then pull).  ``layout`` LAYOUT_CONV3X3_WGRAD: the partials are the conv2
+        weight-gradient accumulator images (``n_floats`` = CONV3X3_WGRAD_IMAGE) and the slice is
+        net.2.weight followed by net.2.bias."""
         nat.check(self.lib.ddpb_reduce_allreduce_sgd(self._h, nat.ptr(partials), nparts, n_floats,
-                                                     grad_off, param_off, nat.ptr(lr_dev), algo, slot,
-                                                     nat.stream_ptr(stream)), "reduce_allreduce_sgd")
+                                                     grad_off, param_off, nat.ptr(lr_dev), algo, layout,
+                                                     slot, nat.stream_ptr(stream)),
+                  "reduce_allreduce_sgd")
 
     def allreduce(self, in_off: int, out_off: int, nbytes: int, dtype=torch.float32,
                   algo: int = ALGO_AUTO, slot: int = 0, stream=None) -> None:

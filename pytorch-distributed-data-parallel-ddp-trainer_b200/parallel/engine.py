@@ -167,8 +167,11 @@ class B200DataParallel(_EngineBase):
 
     # ------------------------------------------------------------------ the step
     def launches_per_step(self, batch: int) -> int:
-        # three bucket updates + weight re-pack (+ the separate conv1 split-K reduce in "split" mode)
-        return self.model.launches_per_step(batch) + 4 + (1 if self.tail_update == "split" else 0)
+        # the model counts the conv2 split-K reduce as its own kernel and no conv1 reduce; on top of it:
+        # three bucket updates + the weight re-pack.  "push" folds the conv2 reduce into its update
+        # kernel as well (-1), "split" runs the conv1 reduce separately (+1).
+        extra = {"push": -1, "pull": 0, "split": 1}[self.tail_update]
+        return self.model.launches_per_step(batch) + 4 + extra
 
     def _update(self, bucket, parity: int, slot: int, stream) -> None:
         """Fused all-reduce + 1/W + SGD of one gradient bucket (plain SGD kernel when W == 1)."""
@@ -206,9 +209,19 @@ class B200DataParallel(_EngineBase):
                 m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
         with nvtx_range("bwd conv2 wgrad + bucket net.2"):
-            m.backward_conv2_wgrad(b, self.side2, parity)
-            if "conv2" not in self._ablate:
-                self._update(self.bucket_conv2, parity, 2, self.side2)
+            if self.tail_update == "push" and "conv2" not in self._ablate:
+                # same one-kernel split-K reduce + exchange + SGD as the tail bucket below
+                from .comm import ALGO_PUSH, CONV3X3_WGRAD_IMAGE, LAYOUT_CONV3X3_WGRAD
+                nparts2 = m.backward_conv2_wgrad_partials(b, self.side2)
+                s2, _n2 = self.bucket_conv2
+                self.comm.reduce_allreduce_sgd(
+                    m.scr_w2, nparts2, CONV3X3_WGRAD_IMAGE, self.grad_off[parity] + s2 * 4,
+                    self.param_off + s2 * 4, m.lr_dev, algo=ALGO_PUSH, layout=LAYOUT_CONV3X3_WGRAD,
+                    slot=2, stream=self.side2)
+            else:
+                m.backward_conv2_wgrad(b, self.side2, parity)
+                if "conv2" not in self._ablate:
+                    self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
         with nvtx_range("bwd conv2 dgrad, conv1 wgrad + bucket net.0"):
             if self.tail_update == "split":

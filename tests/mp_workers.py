@@ -133,6 +133,40 @@ def scenario_fused_sgd():
         dist.all_gather(gathered, p2.clone())
         assert all(torch.equal(t, gathered[0]) for t in gathered), "back-to-back calls diverged bitwise"
         dist.barrier()
+    # the conv2 bucket path: partials are weight-gradient accumulator images, the kernel permutes
+    from ddp_b200.parallel.comm import CONV3X3_WGRAD_IMAGE, LAYOUT_CONV3X3_WGRAD, conv3x3_wgrad_image_dest
+    n_src, n_dst, np3 = CONV3X3_WGRAD_IMAGE, 64 * 32 * 9 + 64, 5
+    dest = conv3x3_wgrad_image_dest().to(dev)
+    keep = dest >= 0
+    p3 = comm.tensor(0, n_dst)
+    g3 = comm.tensor(region, n_dst)
+
+    def image_of(seed, r):
+        return _rank_data(seed, r, np3 * n_src, torch.float32, dev).view(np3, n_src).contiguous()
+
+    p3.copy_(_rank_data(70, 0, n_dst, torch.float32, dev))
+    start = p3.clone()
+    reps = 6
+    imgs = [image_of(400 + k, rank) for k in range(reps)]
+    torch.cuda.synchronize()
+    dist.barrier()
+    for k in range(reps):  # back to back, no host sync
+        comm.reduce_allreduce_sgd(imgs[k], np3, n_src, region, 0, lr, algo=ALGO_PUSH,
+                                  layout=LAYOUT_CONV3X3_WGRAD, slot=6)
+    torch.cuda.synchronize()
+    tot = torch.zeros(n_dst, device=dev, dtype=torch.float64)
+    for k in range(reps):
+        for r in range(world):
+            tot[dest[keep]] += image_of(400 + k, r).sum(0).double()[keep]
+    want3 = start.double() - 0.01 * tot / world
+    assert torch.allclose(p3.double(), want3, rtol=1e-4, atol=1e-3), (p3 - want3).abs().max().item()
+    mine = torch.zeros(n_dst, device=dev)
+    mine[dest[keep]] = imgs[-1].sum(0)[keep]
+    assert torch.allclose(g3, mine, rtol=1e-5, atol=1e-4), "local conv2 gradient not published"
+    gathered = [torch.empty_like(p3) for _ in range(world)]
+    dist.all_gather(gathered, p3.clone())
+    assert all(torch.equal(t, gathered[0]) for t in gathered), "conv3x3-layout update diverged bitwise"
+    dist.barrier()
     comm.close()
     if rank == 0:
         print("fused_sgd ok", flush=True)

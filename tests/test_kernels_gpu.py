@@ -327,3 +327,43 @@ def test_reduce_allreduce_sgd_single_rank(nat, algo_name, nparts, n):
             assert torch.allclose(p, want, atol=1e-5, rtol=1e-5), (it, (p - want).abs().max().item())
     finally:
         comm.close()
+
+
+def test_reduce_allreduce_sgd_conv3x3_layout_single_rank(nat):
+    """layout = conv3x3 weight-gradient accumulator images: the fused kernel must apply the same
+    permutation as wgrad_reduce_kernel (checked against ddpb_conv3x3_wgrad on real data)."""
+    from ddp_b200.parallel.comm import (ALGO_PUSH, CONV3X3_WGRAD_IMAGE, LAYOUT_CONV3X3_WGRAD,
+                                        SymmetricComm, conv3x3_wgrad_image_dest)
+    lay = _lay()
+    torch.manual_seed(9)
+    batch = 37
+    a1 = lay.nchw_to_planes(torch.relu(torch.randn(batch, 32, H, W, device="cuda")), batch)
+    d2 = lay.nchw_to_planes(torch.randn(batch, 64, H, W, device="cuda") * 0.1, batch)
+    dw = torch.zeros(64, 32, 3, 3, device="cuda")
+    db = torch.zeros(64, device="cuda")
+    scr = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(32, 64))
+    nat.conv3x3_wgrad(d2, a1, dw, db, scr, 32, 64, batch, batch, H, W)
+    n_dst = 64 * 32 * 9 + 64
+    region = (n_dst * 4 + 255) // 256 * 256
+    comm = SymmetricComm(0, 1, 2 * region)
+    try:
+        p, g = comm.tensor(0, n_dst), comm.tensor(region, n_dst)
+        lr = torch.tensor([0.5], device="cuda")
+        for it in range(2):
+            p.copy_(torch.randn(n_dst, device="cuda"))
+            start = p.clone()
+            nparts = nat.conv3x3_wgrad_partials(d2, a1, scr, 32, 64, batch, batch, H, W)
+            comm.reduce_allreduce_sgd(scr, nparts, CONV3X3_WGRAD_IMAGE, region, 0, lr, algo=ALGO_PUSH,
+                                      layout=LAYOUT_CONV3X3_WGRAD, slot=5)
+            torch.cuda.synchronize()
+            want_g = torch.cat([dw.reshape(-1), db])
+            assert torch.allclose(g, want_g, atol=1e-5, rtol=1e-5), (g - want_g).abs().max().item()
+            assert torch.allclose(p, start - 0.5 * want_g, atol=1e-5, rtol=1e-5)
+        # the Python restatement of the index map agrees with the kernel
+        dest = conv3x3_wgrad_image_dest().cuda()
+        img = scr.view(torch.float32)[: nparts * CONV3X3_WGRAD_IMAGE].view(nparts, -1).sum(0)
+        ref = torch.zeros(n_dst, device="cuda")
+        ref[dest[dest >= 0]] = img[dest >= 0]
+        assert torch.allclose(ref, g, atol=1e-4, rtol=1e-4)
+    finally:
+        comm.close()

@@ -82,3 +82,21 @@ def test_state_dict_is_a_copy():
     sd = m.state_dict()
     sd["fl.bias"].add_(1.0)
     assert not torch.equal(sd["fl.bias"], m.arena.view("fl.bias").detach())
+
+
+def test_header_declares_every_exported_entry_point():
+    """include/ddp_b200.h is the C contract: every extern "C" ddpb_* function defined in csrc/ must
+    be declared there (checked on the sources, so it runs without a GPU or a built library)."""
+    import glob
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "ddp_b200.h")).read()
+    declared = set(re.findall(r"\b(ddpb_[a-z0-9_]+)\s*\(", header))
+    defined = set()
+    for path in glob.glob(os.path.join(root, "csrc", "*.cu")):
+        src = open(path).read()
+        defined |= set(re.findall(r"^(?:extern \"C\" )?(?:const )?[a-z_ ]+\*?\s*\*?(ddpb_[a-z0-9_]+)\s*\(", src, re.M))
+    assert len(defined) > 40, sorted(defined)
+    missing = sorted(d for d in defined if d not in declared)
+    assert not missing, f"not declared in include/ddp_b200.h: {missing}"
