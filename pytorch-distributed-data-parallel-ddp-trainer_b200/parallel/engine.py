@@ -38,6 +38,21 @@ class _EngineBase:
     def set_lr(self, lr: float) -> None:
         self.lr = float(lr)
 
+    def verify_replicas(self, rank: int, world_size: int, **settings) -> None:
+        """Every rank must hold the same parameter list and run the same kernel/collective sequence
+        (what DDP's constructor checks with _verify_param_shape_across_processes; here a
+        mismatch would not be an error message later but a dead-peer timeout).  One small object
+        all-gather at construction."""
+        if world_size <= 1:
+            return
+        mine = (tuple((s.name, tuple(s.shape)) for s in self.model.arena.specs), tuple(sorted(settings.items())))
+        everyone = [None] * world_size
+        dist.all_gather_object(everyone, mine)
+        for r, other in enumerate(everyone):
+            if other != mine:
+                what = "parameter names/shapes" if other[0] != mine[0] else f"engine settings {dict(other[1])} vs {dict(mine[1])}"
+                raise RuntimeError(f"rank {rank}: replica mismatch with rank {r}: {what}")
+
 
 class CpuDataParallel(_EngineBase):
     def __init__(self, rank: int, world_size: int, lr: float = 0.01, device="cpu"):
@@ -45,6 +60,7 @@ class CpuDataParallel(_EngineBase):
         self.device = torch.device(device)
         self.model = SimpleCNN(device=self.device)
         self.buckets = self.model.buckets()
+        self.verify_replicas(rank, world_size, engine="cpu")
         self.sync_params()
 
     @property
@@ -124,6 +140,9 @@ class B200DataParallel(_EngineBase):
         self.bucket_conv1 = self._slice(a, ("net.0.weight", "net.0.bias"))
         self.buckets = [self.bucket_fl, self.bucket_conv2, self.bucket_conv1]
         assert all(s % 4 == 0 and s + m <= n for s, m in self.buckets)
+        self.verify_replicas(rank, world_size, engine="b200", tail_update=self.tail_update, algo=self.algo,
+                             multicast=self.comm.multicast,
+                             ablate=",".join(sorted(self._ablate)))
 
         self.main = torch.cuda.Stream(self.device)
         self.side = torch.cuda.Stream(self.device)

@@ -82,3 +82,20 @@ def fd_exchange_worker(rank, world_size, out_path):
     with open(f"{out_path}.{rank}", "w") as f:
         f.write(repr(sorted((str(k), v) for k, v in seen.items())))
     cleanup()
+
+
+def verify_replicas_worker(rank, world_size, out_path):
+    """Matching settings pass; a rank configured differently is named in the error on every rank."""
+    from ddp_b200.parallel.engine import CpuDataParallel
+    from ddp_b200.parallel.process_group import cleanup, setup
+    setup(rank, world_size, backend="gloo")
+    eng = CpuDataParallel(rank, world_size)           # constructor runs the check with equal settings
+    eng.verify_replicas(rank, world_size, tail_update="push")
+    try:
+        eng.verify_replicas(rank, world_size, tail_update="push" if rank == 0 else "split")
+        msg = "no error"
+    except RuntimeError as e:
+        msg = str(e)
+    with open(f"{out_path}.{rank}", "w") as f:
+        f.write(msg)
+    cleanup()

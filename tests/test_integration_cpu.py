@@ -176,3 +176,16 @@ def test_fd_exchange_between_rank_processes(tmp_path):
             if src != rank:
                 assert seen[str(src)] == f"hello from {src}"
         assert (seen.get("mc") == "mc") == (rank != 0)
+
+
+def test_replica_mismatch_is_reported_at_construction(tmp_path):
+    """ranks that would run different collective sequences must fail fast."""
+    from torch.multiprocessing.spawn import spawn
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import cpu_workers
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(_free_port())
+    out = str(tmp_path / "verify")
+    spawn(cpu_workers.verify_replicas_worker, args=(2, out), nprocs=2)
+    m0, m1 = open(out + ".0").read(), open(out + ".1").read()
+    assert "replica mismatch with rank 1" in m0 and "tail_update" in m0
+    assert "replica mismatch with rank 0" in m1
