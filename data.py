@@ -1,5 +1,5 @@
 """Drop-in for the reference's ``data.py``: ``get_dataloader(batch_size, world_size, rank)``
-returns ``(dataloader, sampler)``.  Implementation: ddp_b200/utils/data.py."""
+returns ``(dataloader, sampler)`` (reference data.py:6-27).  Implementation: ddp_b200/utils/data.py."""
 import os
 import sys
 

@@ -1,4 +1,4 @@
-"""Drop-in for the reference's ``model.py``: ``from model import SimpleCNN`` keeps working.
+"""Drop-in for the reference's ``model.py`` (model.py:4-20): ``from model import SimpleCNN`` keeps working.
 The implementation lives in ddp_b200/models/simple_cnn.py (flat-arena CPU model + sm_100a model)."""
 import os
 import sys

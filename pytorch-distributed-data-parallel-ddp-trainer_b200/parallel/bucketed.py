@@ -11,6 +11,7 @@ parity, see csrc/comm.cu), buckets are contiguous slices in reverse registration
 from __future__ import annotations
 
 import torch
+import torch.distributed as dist
 
 from .comm import ALGO_AUTO, SymmetricComm
 
@@ -113,6 +114,9 @@ class BucketedDataParallel:
         self.step_count += 1
         return loss.detach()
 
-    def close(self) -> None:
+    def close(self, sync_peers: bool = True) -> None:
+        """See B200DataParallel.close: peers must be done reading this rank's buffer before it goes."""
         torch.cuda.synchronize(self.device)
+        if sync_peers and self.world_size > 1 and dist.is_available() and dist.is_initialized():
+            dist.barrier()
         self.comm.close()

@@ -86,7 +86,7 @@ class CpuDataParallel(_EngineBase):
     def read_loss(self, loss) -> float:
         return float(loss)
 
-    def close(self) -> None:
+    def close(self, sync_peers: bool = True) -> None:
         pass
 
 
@@ -331,8 +331,14 @@ class B200DataParallel(_EngineBase):
         self.side2.synchronize()
         self.copy.synchronize()
 
-    def close(self) -> None:
+    def close(self, sync_peers: bool = True) -> None:
+        """Release the graphs and the peer-mapped buffer.  Peers read this rank's buffer from inside
+        their kernels, so it must not be freed while any rank still has a step in flight: with
+        ``sync_peers`` (default) all ranks meet at a host barrier after draining their own streams.
+        Pass False only on an error path where the peers may never arrive."""
         self.synchronize()
+        if sync_peers and self.world_size > 1 and dist.is_available() and dist.is_initialized():
+            dist.barrier()
         self._graphs.clear()
         self.comm.close()
 

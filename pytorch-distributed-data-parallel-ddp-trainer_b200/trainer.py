@@ -9,6 +9,7 @@ works on every rank, and cleanup runs even when training raises.
 from __future__ import annotations
 
 import os
+import sys
 import time
 
 import torch
@@ -98,7 +99,8 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
     finally:
         if engine is not None:
             try:
-                engine.close()
+                # on an error path the peers may never reach their close(): do not wait for them
+                engine.close(sync_peers=sys.exc_info()[0] is None)
             except Exception as e:  # pragma: no cover - best effort on an already failing path
                 print(f"Rank {rank}: engine close failed: {e}", flush=True)
         trace.close()

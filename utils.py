@@ -1,5 +1,5 @@
 """Drop-in for the reference's ``utils.py``: ``setup(rank, world_size, backend=None)`` and
-``cleanup()``.  Implementation: ddp_b200/parallel/process_group.py."""
+``cleanup()`` (reference utils.py:5-19).  Implementation: ddp_b200/parallel/process_group.py."""
 import os
 import sys
 
