@@ -121,6 +121,26 @@ class SimpleCNN(_ModelBase):
             self.arena.params.grad = self.arena.grads
         return loss.detach()
 
+    def forward_backward_staged(self, x: torch.Tensor, y: torch.Tensor, on_bucket_ready) -> torch.Tensor:
+        """Same result as forward_backward, but the backward pass runs bucket by bucket in
+        gradient-ready order (BUCKET_GROUPS: the linear layer first) and ``on_bucket_ready(i)`` is
+        called as soon as bucket i's gradients are in the arena — the CPU counterpart of DDP's
+        autograd-hook launch (reference train_ddp.py:199): the engine starts that
+        bucket's all-reduce while the convolution backward is still running."""
+        a = self.arena
+        v = {s.name: a.view(s.name) for s in a.specs}
+        h = F.relu(F.conv2d(x, v["net.0.weight"], v["net.0.bias"], padding=1))
+        h = F.relu(F.conv2d(h, v["net.2.weight"], v["net.2.bias"], padding=1))
+        loss = F.cross_entropy(F.linear(h.flatten(1), v["fl.weight"], v["fl.bias"]), y)
+        for i, names in enumerate(BUCKET_GROUPS):
+            last = i == len(BUCKET_GROUPS) - 1
+            grads = torch.autograd.grad(loss, [v[n] for n in names], retain_graph=not last)
+            with torch.no_grad():
+                for n, g in zip(names, grads):
+                    a.grad_view(n).copy_(g)
+            on_bucket_ready(i)
+        return loss.detach()
+
     def sgd_step(self, lr: float) -> None:
         with torch.no_grad():
             self.arena.params.add_(self.arena.grads, alpha=-lr)

@@ -72,13 +72,21 @@ class CpuDataParallel(_EngineBase):
             dist.broadcast(self.model.arena.params.detach(), src=src)
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        loss = self.model.forward_backward(x, y)
         a = self.model.arena
         if self.world_size > 1:
-            works = [dist.all_reduce(a.grads[b.start:b.start + b.numel], async_op=True)
-                     for b in self.buckets]
+            # each bucket's all-reduce starts the moment its gradients exist and runs on gloo's
+            # threads under the rest of the backward pass
+            works = []
+
+            def launch(i: int) -> None:
+                b = self.buckets[i]
+                works.append(dist.all_reduce(a.grads[b.start:b.start + b.numel], async_op=True))
+
+            loss = self.model.forward_backward_staged(x, y, launch)
             for w in works:
                 w.wait()
+        else:
+            loss = self.model.forward_backward(x, y)
         with torch.no_grad():
             a.params.add_(a.grads, alpha=-self.lr / self.world_size)
         return loss

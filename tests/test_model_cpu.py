@@ -100,3 +100,30 @@ def test_header_declares_every_exported_entry_point():
     assert len(defined) > 40, sorted(defined)
     missing = sorted(d for d in defined if d not in declared)
     assert not missing, f"not declared in include/ddp_b200.h: {missing}"
+
+
+def test_staged_backward_equals_plain_backward():
+    """The bucket-by-bucket backward (used to overlap the gloo all-reduce with the convolution
+    backward) must give bit-identical gradients and report the buckets in gradient-ready order."""
+    from ddp_b200.models.simple_cnn import BUCKET_GROUPS, SimpleCNN
+    torch.manual_seed(4)
+    m = SimpleCNN()
+    x, y = torch.rand(6, 1, 28, 28), torch.randint(0, 10, (6,))
+    l0 = m.forward_backward(x, y)
+    g0 = m.arena.grads.clone()
+    m.arena.grads.fill_(123.0)
+    order = []
+    seen_at_call = []
+
+    def ready(i):
+        order.append(i)
+        b = m.buckets()[i]
+        seen_at_call.append(torch.equal(m.arena.grads[b.start:b.start + b.numel], g0[b.start:b.start + b.numel]))
+
+    l1 = m.forward_backward_staged(x, y, ready)
+    assert order == list(range(len(BUCKET_GROUPS))) and all(seen_at_call)
+    assert torch.equal(l0, l1)
+    covered = torch.zeros_like(g0, dtype=torch.bool)
+    for b in m.buckets():
+        covered[b.start:b.start + b.numel] = True
+    assert torch.equal(m.arena.grads[covered], g0[covered])
