@@ -68,6 +68,7 @@ for _name, _res, _args in (
     nat.declare(_name, _res, _args)
 
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH, ALGO_NVLS = 0, 1, 2, 3, 4
+SUPPORTED_WORLD_SIZES = (1, 2, 4, 8)  # the kernels are instantiated per world size (csrc/comm.cu)
 DTYPE_CODES = {torch.float32: 0, torch.bfloat16: 1}
 # how partial element i maps into the gradient/parameter slice of reduce_allreduce_sgd
 LAYOUT_IDENTITY, LAYOUT_CONV3X3_WGRAD = 0, 1
@@ -164,6 +165,9 @@ def _all_ok(ok: bool, world_size: int) -> bool:
 class SymmetricComm:
     def __init__(self, rank: int, world_size: int, payload_bytes: int, timeout_ms: int | None = None,
                  multicast: bool | None = None):
+        if world_size not in SUPPORTED_WORLD_SIZES or not 0 <= rank < world_size:
+            raise ValueError(f"the peer-memory communicator is built for world sizes {SUPPORTED_WORLD_SIZES} "
+                             f"(one NVSwitch node); got rank {rank} of {world_size}")
         lib = nat.lib()
         self.lib = lib
         self.rank, self.world_size = rank, world_size

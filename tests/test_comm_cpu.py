@@ -1,0 +1,28 @@
+"""Host-side behaviour of the communicator module that needs no GPU."""
+import pytest
+import torch
+
+
+def test_unsupported_world_size_is_a_clear_error():
+    from ddp_b200.parallel.comm import SUPPORTED_WORLD_SIZES, SymmetricComm
+    assert SUPPORTED_WORLD_SIZES == (1, 2, 4, 8)
+    for rank, world in ((0, 3), (0, 16), (2, 2), (-1, 2)):
+        with pytest.raises(ValueError, match="world sizes"):
+            SymmetricComm(rank, world, 1024)
+
+
+def test_conv3x3_wgrad_image_dest_is_a_bijection_onto_the_bucket():
+    """The index map of the fused conv2 update: every weight and bias element of net.2 is hit exactly
+    once, the 7 spare bias columns per output channel are dropped."""
+    from ddp_b200.parallel.comm import CONV3X3_WGRAD_IMAGE, conv3x3_wgrad_image_dest
+    dest = conv3x3_wgrad_image_dest()
+    assert dest.numel() == CONV3X3_WGRAD_IMAGE == 64 * (9 * 32 + 8)
+    kept = dest[dest >= 0]
+    assert kept.numel() == 64 * 32 * 9 + 64
+    assert torch.equal(torch.sort(kept).values, torch.arange(64 * 32 * 9 + 64))
+    assert int((dest < 0).sum()) == 64 * 7
+    # spot checks against the accumulator layout: channel co, row r, tap sx, input channel ci
+    co, r, sx, ci = 5, 2, 1, 17
+    col = (3 * 32 + 8) + 3 * 32 + sx * 32 + ci          # row 2 block starts after row 0 (104) and row 1 (96)
+    assert int(dest[co * 296 + col]) == (co * 32 + ci) * 9 + r * 3 + sx
+    assert int(dest[co * 296 + 96]) == 64 * 32 * 9 + co  # first bias column
