@@ -33,11 +33,15 @@ def free_port() -> int:
         return s.getsockname()[1]
 
 
-def launch(worker: Callable, world_size: int | None, args: Sequence = ()) -> None:
+def launch(worker: Callable, world_size: int | None, args: Sequence = (), max_restarts: int = 0) -> None:
     """Run ``worker(rank, world_size, *args)`` on every rank.
 
-    torchrun: this process IS one rank.  Otherwise spawn ``world_size`` local processes
-    (spawn start method, like the reference) with MASTER_ADDR/PORT set to a free local port.
+    torchrun: this process IS one rank (its own ``--max-restarts`` applies).  Otherwise spawn
+    ``world_size`` local processes (spawn start method, like the reference) with MASTER_ADDR/PORT set
+    to a free local port.  ``max_restarts`` > 0 turns the reference's recovery story — "rerun the same
+    command" (README.md:74), which resumes from the newest checkpoint — into something the launcher
+    does itself: when any rank dies, the whole group is torn down (spawn does that) and started again
+    on a fresh port, up to ``max_restarts`` times.
     """
     if under_torchrun():
         rank = int(os.environ["RANK"])
@@ -48,10 +52,24 @@ def launch(worker: Callable, world_size: int | None, args: Sequence = ()) -> Non
         return
     ws = world_size if world_size is not None else default_world_size()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    if "MASTER_PORT" not in os.environ:
-        os.environ["MASTER_PORT"] = str(free_port())
-    if ws == 1:
-        worker(0, 1, *args)
-        return
-    from torch.multiprocessing.spawn import spawn
-    spawn(worker, args=(ws, *args), nprocs=ws)
+    user_port = "MASTER_PORT" in os.environ
+    attempt = 0
+    while True:
+        if not user_port:
+            os.environ["MASTER_PORT"] = str(free_port())
+        try:
+            if ws == 1:
+                worker(0, 1, *args)
+            else:
+                from torch.multiprocessing.spawn import spawn
+                spawn(worker, args=(ws, *args), nprocs=ws)
+            return
+        except KeyboardInterrupt:
+            raise
+        except Exception as e:
+            if attempt >= max_restarts:
+                raise
+            attempt += 1
+            first = str(e).strip().splitlines()[-1] if str(e).strip() else type(e).__name__
+            print(f"launcher: worker group failed ({first}); restart {attempt}/{max_restarts} "
+                  f"(training resumes from the newest checkpoint)", flush=True)

@@ -25,6 +25,19 @@ LEARNING_RATE = 0.01   # reference train_ddp.py:41
 LOG_INTERVAL = 100     # reference train_ddp.py:201
 
 
+def _maybe_inject_failure(rank: int, epoch: int) -> None:
+    """Fault injection for the recovery tests: ``DDP_B200_FAIL_ONCE="<rank>:<epoch>:<marker file>"``
+    makes that rank raise at the start of that epoch, once (the marker file records that it happened)."""
+    spec = os.environ.get("DDP_B200_FAIL_ONCE")
+    if not spec:
+        return
+    r, e, marker = spec.split(":", 2)
+    if int(r) == rank and int(e) == epoch and not os.path.exists(marker):
+        with open(marker, "w") as f:
+            f.write(f"rank {rank} epoch {epoch}\n")
+        raise RuntimeError(f"injected failure on rank {rank} at epoch {epoch}")
+
+
 def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_root: str = "./data",
               ckpt_dir: str = ckpt.CHECKPOINT_DIR, lr: float = LEARNING_RATE,
               log_interval: int = LOG_INTERVAL, dataset=None, backend: str | None = None,
@@ -58,6 +71,7 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
         timer = StepTimer(device)
         step_stream = getattr(engine, "main", None)
         for epoch in range(start_epoch, epochs):
+            _maybe_inject_failure(rank, epoch)
             sampler.set_epoch(epoch)
             print(f"Rank {rank}: Starting epoch {epoch}", flush=True)
             t0 = time.perf_counter()

@@ -189,3 +189,27 @@ def test_replica_mismatch_is_reported_at_construction(tmp_path):
     m0, m1 = open(out + ".0").read(), open(out + ".1").read()
     assert "replica mismatch with rank 1" in m0 and "tail_update" in m0
     assert "replica mismatch with rank 0" in m1
+
+
+def test_launcher_restarts_after_a_rank_dies_and_resumes(tmp_path):
+    """the reference's only recovery is "rerun the command"; with --max_restarts the
+    launcher does it.  Rank 1 is made to die once at the start of epoch 1: the group is restarted,
+    resumes from epoch_0.pt and finishes both epochs; without restarts the same failure is fatal."""
+    cmd = [sys.executable, os.path.join(ROOT, "train_ddp.py"), "--batch_size", "64", "--world_size", "2",
+           "--epochs", "2"]
+    env = _env()
+    marker = tmp_path / "failed_once"
+    env["DDP_B200_FAIL_ONCE"] = f"1:1:{marker}"
+    out = _run(cmd + ["--max_restarts", "1"], str(tmp_path), env)
+    assert marker.exists()
+    # (which rank's exception the parent sees first is a race: the injected one or its peer's broken pipe)
+    assert "restart 1/1" in out
+    assert out.count("Starting epoch 0") == 2            # first attempt only
+    assert out.count("Resumed from checkpoint, next epoch 1") == 2
+    assert (tmp_path / "checkpoints" / "epoch_1.pt").exists()
+    # the same kind of failure with no restarts allowed is fatal
+    fresh = tmp_path / "fresh"
+    fresh.mkdir()
+    env["DDP_B200_FAIL_ONCE"] = f"0:0:{fresh / 'failed_once'}"
+    res = subprocess.run(cmd, cwd=str(fresh), env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode != 0 and "injected failure" in (res.stdout + res.stderr)

@@ -23,8 +23,12 @@ def main(argv=None):
     parser.add_argument("--batch_size", type=int, default=32, help="Batch size for training (per rank)")
     parser.add_argument("--world_size", type=int, default=None,
                         help="Processes to spawn (default: torchrun's WORLD_SIZE, else GPU count, else 2)")
+    parser.add_argument("--max_restarts", type=int, default=0,
+                        help="Self-spawn mode: restart the worker group this many times if a rank dies "
+                             "(each restart resumes from the newest checkpoint); under torchrun use its "
+                             "own --max-restarts")
     args = parser.parse_args(argv)
-    launch(ddp_train, args.world_size, args=(args.epochs, args.batch_size))
+    launch(ddp_train, args.world_size, args=(args.epochs, args.batch_size), max_restarts=args.max_restarts)
 
 
 if __name__ == "__main__":
