@@ -245,6 +245,7 @@ def run_ours(args):
              "allreduce": "fused (split-K reduce +) all-reduce + SGD kernels over peer memory, in-kernel flags",
              "communicator": "vmm+multicast" if getattr(getattr(eng, "comm", None), "multicast", False) else "cuda-ipc",
              "tail_update": getattr(eng, "tail_update", None),
+             "net2_order": getattr(eng, "net2_order", None),
              "final_loss": round(loss_e2e, 4), "loss_after_device_region": round(loss_dev, 4),
              "native_lib": os.path.relpath(native.LIB_PATH, ROOT)}
     _emit(args, rank, world, "ours", dev_ms, e2e_s, clocks, launches, "bf16", extra)

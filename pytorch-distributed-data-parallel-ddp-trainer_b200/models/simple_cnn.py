@@ -244,19 +244,33 @@ class SimpleCNNB200(_ModelBase):
         return self.nat.conv3x3_wgrad_partials(self.dact2, self.act1, self.scr_w2, C1, C2, batch,
                                                self.batch_cap, IMG_H, IMG_W, stream)
 
+    def backward_dgrad(self, batch: int, stream=None) -> None:
+        """conv2 data gradient (with ReLU'): dact1 from dact2.  The LAST reader of net.2.weight in a
+        step — the engine must not let the net.2 bucket update start before this has finished."""
+        self.nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, self.batch_cap,
+                               IMG_H, IMG_W, stream)
+
+    def backward_conv1_wgrad(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0) -> None:
+        """conv1 weight + bias gradient into the gradient arena (tensor-core kernel + split-K reduce)."""
+        gs = self.grad_sets[parity]
+        self.nat.conv1_wgrad_tc(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, self.batch_cap,
+                                IMG_H, IMG_W, stream)
+
+    def backward_conv1_wgrad_partials(self, x: torch.Tensor, batch: int, stream=None) -> int:
+        """conv1 gradient left as per-CTA partials in ``self.scr_w1`` (returns their count) for the
+        fused reduce + all-reduce + SGD kernel."""
+        return self.nat.conv1_wgrad_tc_partials(self.dact1, x, self.scr_w1, 1, C1, batch, self.batch_cap,
+                                                IMG_H, IMG_W, stream)
+
     def backward_dgrad_conv1(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 data gradient (with ReLU') followed by the conv1 weight + bias gradient."""
-        nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
-        gs = self.grad_sets[parity]
-        nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
-        nat.conv1_wgrad_tc(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, cap, H, W, stream)
+        self.backward_dgrad(batch, stream)
+        self.backward_conv1_wgrad(x, batch, stream, parity)
 
     def backward_dgrad_conv1_partials(self, x: torch.Tensor, batch: int, stream=None) -> int:
-        """Like backward_dgrad_conv1 but leaves the conv1 gradient as per-CTA partials in
-        ``self.scr_w1`` (returns their count) for the fused reduce + all-reduce + SGD kernel."""
-        nat, cap, H, W = self.nat, self.batch_cap, IMG_H, IMG_W
-        nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, cap, H, W, stream)
-        return nat.conv1_wgrad_tc_partials(self.dact1, x, self.scr_w1, 1, C1, batch, cap, H, W, stream)
+        """Like backward_dgrad_conv1 but leaves the conv1 gradient as per-CTA partials."""
+        self.backward_dgrad(batch, stream)
+        return self.backward_conv1_wgrad_partials(x, batch, stream)
 
     def backward_body(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 wgrad + dgrad, conv1 wgrad: completes bucket 1."""

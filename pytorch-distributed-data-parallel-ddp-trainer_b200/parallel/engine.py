@@ -13,6 +13,8 @@ SURVEY.md X13) so all ranks start identical without any seed being set.
 """
 from __future__ import annotations
 
+import contextlib
+
 import torch
 import torch.distributed as dist
 
@@ -120,6 +122,14 @@ class B200DataParallel(_EngineBase):
         # timing diagnostics only (the step is then WRONG): skip the update of the named buckets to see
         # which stream is the critical path, e.g. DDPB_ABLATE=conv2 or DDPB_ABLATE=fl,pack
         self._ablate = set(filter(None, os.environ.get("DDPB_ABLATE", "").split(",")))
+        # "event" (default): the net.2 bucket update waits for the conv2 data gradient, the last reader of
+        # net.2.weight in the step.  "legacy": the ordering every number in BASELINE.md was measured with,
+        # where the update only follows the weight gradient and can overtake the data gradient's weight
+        # staging (a real, timing-dependent race).  The event ordering was written after the round's GPU
+        # time ran out and has NOT run on hardware yet; "legacy" is the fallback if it misbehaves.
+        self.net2_order = os.environ.get("DDPB_NET2_ORDER", "event")
+        if self.net2_order not in ("event", "legacy"):
+            raise ValueError(f"DDPB_NET2_ORDER must be event or legacy, got {self.net2_order!r}")
         if self.tail_update not in ("push", "pull", "split"):
             raise ValueError(f"tail_update must be push, pull or split, got {self.tail_update!r}")
         # programmatic dependent launch pays off for latency-bound (small-batch) steps only
@@ -149,7 +159,7 @@ class B200DataParallel(_EngineBase):
         self.buckets = [self.bucket_fl, self.bucket_conv2, self.bucket_conv1]
         assert all(s % 4 == 0 and s + m <= n for s, m in self.buckets)
         self.verify_replicas(rank, world_size, engine="b200", tail_update=self.tail_update, algo=self.algo,
-                             multicast=self.comm.multicast,
+                             multicast=self.comm.multicast, net2_order=self.net2_order,
                              ablate=",".join(sorted(self._ablate)))
 
         self.main = torch.cuda.Stream(self.device)
@@ -159,6 +169,7 @@ class B200DataParallel(_EngineBase):
         self._ev_fork = torch.cuda.Event()
         self._ev_join = torch.cuda.Event()
         self._ev_join2 = torch.cuda.Event()
+        self._ev_dgrad = torch.cuda.Event()
         self._ev_ready = [torch.cuda.Event(), torch.cuda.Event()]
         self._ev_free = [torch.cuda.Event(), torch.cuda.Event()]
         self.x_in = [torch.zeros(batch_cap, 1, IMG_H, IMG_W, device=self.device) for _ in range(2)]
@@ -200,6 +211,18 @@ class B200DataParallel(_EngineBase):
         extra = {"push": -1, "pull": 0, "split": 1}[self.tail_update]
         return self.model.launches_per_step(batch) + 4 + extra
 
+    @contextlib.contextmanager
+    def _plain_launch(self):
+        """Kernels launched inside are ordinary stream-ordered launches (no programmatic dependent
+        launch attribute), whatever the engine-wide setting is."""
+        lib = self.model.nat.lib()
+        prev = lib.ddpb_get_pdl()
+        lib.ddpb_set_pdl(0)
+        try:
+            yield
+        finally:
+            lib.ddpb_set_pdl(prev)
+
     def _update(self, bucket, parity: int, slot: int, stream) -> None:
         """Fused all-reduce + 1/W + SGD of one gradient bucket (plain SGD kernel when W == 1)."""
         m = self.model
@@ -218,7 +241,11 @@ class B200DataParallel(_EngineBase):
 
             main : fwd+loss, linear bwd | conv2 dgrad -> conv1 wgrad -> reduce+update {net.0.*} (one kernel)
             side : (after linear bwd)    update {fl.*} -> re-pack fl.weight tiles
-            side2: (after linear bwd)    conv2 wgrad -> update {net.2.*}
+            side2: (after linear bwd)    conv2 wgrad -> [waits for dgrad] -> reduce+update {net.2.*}
+
+        A bucket's update rewrites its parameters in place, so it must come after the last kernel of the
+        step that reads them: fl.* is last read by the linear backward (before the fork), net.0.* by the
+        conv1 forward, net.2.weight by the conv2 data gradient on the main stream — hence the event.
         """
         m, main = self.model, self.main
         x, y = self.x_in[parity][:b], self.y_in[parity][:b]
@@ -235,31 +262,46 @@ class B200DataParallel(_EngineBase):
             if "pack" not in self._ablate:
                 m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
-        with nvtx_range("bwd conv2 wgrad + bucket net.2"):
-            if self.tail_update == "push" and "conv2" not in self._ablate:
+        # side2: conv2 weight gradient (shares the SMs with the data gradient below: 112 KB + 112 KB of
+        # shared memory, 384 + 64 TMEM columns)
+        fused2 = self.tail_update == "push" and "conv2" not in self._ablate
+        with nvtx_range("bwd conv2 wgrad"):
+            if fused2:
+                nparts2 = m.backward_conv2_wgrad_partials(b, self.side2)
+            else:
+                m.backward_conv2_wgrad(b, self.side2, parity)
+        # main: conv2 data gradient, the last reader of net.2.weight in this step
+        with nvtx_range("bwd conv2 dgrad"):
+            m.backward_dgrad(b, main)
+        # side2: net.2.* may only be rewritten once the data gradient is done with it.  The update is
+        # then the one kernel of the step with two predecessors (wgrad in stream order, dgrad through
+        # the event), so it is launched with ordinary full dependencies, not as a programmatic dependent.
+        ordered = self.net2_order == "event"
+        if ordered:
+            self._ev_dgrad.record(main)
+            self.side2.wait_event(self._ev_dgrad)
+        with nvtx_range("bucket net.2"), (self._plain_launch() if ordered else contextlib.nullcontext()):
+            if fused2:
                 # same one-kernel split-K reduce + exchange + SGD as the tail bucket below
                 from .comm import ALGO_PUSH, CONV3X3_WGRAD_IMAGE, LAYOUT_CONV3X3_WGRAD
-                nparts2 = m.backward_conv2_wgrad_partials(b, self.side2)
                 s2, _n2 = self.bucket_conv2
                 self.comm.reduce_allreduce_sgd(
                     m.scr_w2, nparts2, CONV3X3_WGRAD_IMAGE, self.grad_off[parity] + s2 * 4,
                     self.param_off + s2 * 4, m.lr_dev, algo=ALGO_PUSH, layout=LAYOUT_CONV3X3_WGRAD,
                     slot=2, stream=self.side2)
-            else:
-                m.backward_conv2_wgrad(b, self.side2, parity)
-                if "conv2" not in self._ablate:
-                    self._update(self.bucket_conv2, parity, 2, self.side2)
+            elif "conv2" not in self._ablate:
+                self._update(self.bucket_conv2, parity, 2, self.side2)
         self._ev_join2.record(self.side2)
-        with nvtx_range("bwd conv2 dgrad, conv1 wgrad + bucket net.0"):
+        with nvtx_range("bwd conv1 wgrad + bucket net.0"):
             if self.tail_update == "split":
-                m.backward_dgrad_conv1(x, b, main, parity)
+                m.backward_conv1_wgrad(x, b, main, parity)
                 if "conv1" not in self._ablate:
                     self._update(self.bucket_conv1, parity, 1, main)
             elif "conv1" in self._ablate:
-                m.backward_dgrad_conv1_partials(x, b, main)
+                m.backward_conv1_wgrad_partials(x, b, main)
             else:
                 from .comm import ALGO_ONESHOT, ALGO_PUSH
-                nparts = m.backward_dgrad_conv1_partials(x, b, main)
+                nparts = m.backward_conv1_wgrad_partials(x, b, main)
                 s1, n1 = self.bucket_conv1
                 # split-K reduce of the conv1 partials + all-reduce + 1/W + SGD in ONE kernel: this
                 # bucket is the tail of the step's critical path

@@ -115,7 +115,9 @@ def main():
              "the fused conv2-bucket update; ours 4096 x 8 GPUs predates the conv1 / linear-backward kernel changes "
              "(its own N=1 was 1.2408 ms then, i.e. 0.95 efficiency, not the 0.77 the last column derives from the "
              "newer N=1).  The reference rows are unaffected by our changes.  The driver's end-of-round scaling "
-             "run is the authoritative set.")
+             "run is the authoritative set.  ALL rows of ours were measured with the net.2 bucket update ordered only "
+             "after the weight gradient (now `DDPB_NET2_ORDER=legacy`); the default since then also waits for the "
+             "data gradient (DESIGN.md §5) and has not been measured.")
     block = ("<!-- RESULTS:BEGIN -->\n### 3.1 SimpleCNN training throughput (configs 2 and 3)\n\n" + table + notes +
              "\n\n### 3.2 All-reduce sweep, 8 GPUs (config 5)\n\n" + sweep +
              "\n\n### 3.3 Widened CNN, 8 GPUs (config 4)\n\n" + wide +
