@@ -33,6 +33,7 @@
 #include <new>
 
 #include "ptx.cuh"
+#include "layout.cuh"
 #include "api_internal.cuh"
 #include "launch.cuh"
 
@@ -340,7 +341,8 @@ __global__ void __launch_bounds__(256)
 reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, int slot,
                                const float* __restrict__ partials, int nparts, int n, size_t grad_off,
                                size_t param_off, const float* __restrict__ lr,
-                               unsigned long long timeout_ns) {
+                               __nv_bfloat16* __restrict__ pack, const float* __restrict__ bias_part,
+                               int bp_nsplit, int bp_nbx, int bp_hw, unsigned long long timeout_ns) {
   __shared__ float sm[8][32];
   pdl_sync();
   const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
@@ -366,6 +368,10 @@ reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, in
 #pragma unroll
   for (int u = 1; u < 8; ++u) tot += sm[u][lane];
   const int dest = idx < n ? ll_dest<MAP>(idx) : -1;
+  // conv2 bias gradient: the exact-fp32 sums of the linear backward (layout.cuh) replace the
+  // tensor-core ones-column, whose operands carry 16 bits (every warp computes the same value)
+  if (MAP == 1 && bias_part != nullptr && dest >= 64 * 32 * 9)
+    tot = sum_bias_parts(bias_part, bp_nsplit, bp_nbx, bp_hw, dest - 64 * 32 * 9);
   if (pg < WORLD && dest >= 0)
     st_relaxed_sys_u64(ll_line(pp.p[pg], slot, e, rank) + idx,
                        (static_cast<uint64_t>(e) << 32) | __float_as_uint(tot));
@@ -393,7 +399,23 @@ reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, in
 #pragma unroll
     for (int r = 1; r < WORLD; ++r) acc += sm[r][lane];
     float* pr = reinterpret_cast<float*>(pp.p[rank] + param_off) + dest;
-    *pr = fmaf(-(*lr) * (1.0f / WORLD), acc, *pr);
+    const float nv = fmaf(-(*lr) * (1.0f / WORLD), acc, *pr);
+    *pr = nv;
+    if (MAP == 1 && pack != nullptr && dest < 64 * 32 * 9) {
+      // keep the split (hi + lo bf16) tensor-core tile images of net.2.weight (csrc/conv_tc.cu:
+      // [fwd hi | fwd lo | dgrad hi | dgrad lo]) in step with the master weights: the next forward /
+      // data gradient bulk-copy them without any conversion
+      constexpr int n = 9 * 32 * 64;
+      const int co = dest / (32 * 9), rem = dest - co * 32 * 9, ci = rem / 9, tap = rem - ci * 9;
+      float hi, lo;
+      split_bf16(nv, hi, lo);
+      const int f = conv3x3_fwd_tile_index<32, 64, 8>(co, ci, tap);
+      const int d = conv3x3_dgrad_tile_index<32, 64, 8>(co, ci, tap);
+      pack[f] = __float2bfloat16_rn(hi);
+      pack[n + f] = __float2bfloat16_rn(lo);
+      pack[2 * n + d] = __float2bfloat16_rn(hi);
+      pack[3 * n + d] = __float2bfloat16_rn(lo);
+    }
   }
   // the last block to finish publishes the new epoch for the next launch on this slot
   if (threadIdx.x == 0) {
@@ -718,7 +740,11 @@ static void vmm_unmap(const DrvApi* d, uint8_t* p, size_t bytes) {
   switch (W) {                                        \
     case 1: { constexpr int WORLD = 1; __VA_ARGS__; } break; \
     case 2: { constexpr int WORLD = 2; __VA_ARGS__; } break; \
+    case 3: { constexpr int WORLD = 3; __VA_ARGS__; } break; \
     case 4: { constexpr int WORLD = 4; __VA_ARGS__; } break; \
+    case 5: { constexpr int WORLD = 5; __VA_ARGS__; } break; \
+    case 6: { constexpr int WORLD = 6; __VA_ARGS__; } break; \
+    case 7: { constexpr int WORLD = 7; __VA_ARGS__; } break; \
     case 8: { constexpr int WORLD = 8; __VA_ARGS__; } break; \
     default: return DDPB_ERR_SHAPE;                   \
   }
@@ -735,10 +761,9 @@ int ddpb_comm_max_world() { return kMaxWorld; }
 int ddpb_comm_num_slots() { return kSlots; }
 
 // Allocates this rank's symmetric buffer (header + payload_bytes, zero-filled) on the current
-// device.  world must be 1, 2, 4 or 8.
+// device.  world: 1 .. 8 (any size; the kernels are instantiated per world size).
 int ddpb_comm_create(int rank, int world, size_t payload_bytes, void** out) {
-  if (!(world == 1 || world == 2 || world == 4 || world == 8) || rank < 0 || rank >= world)
-    return DDPB_ERR_SHAPE;
+  if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world) return DDPB_ERR_SHAPE;
   Comm* c = new (std::nothrow) Comm();
   if (!c) return static_cast<int>(cudaErrorMemoryAllocation);
   c->rank = rank;
@@ -784,8 +809,7 @@ int ddpb_multicast_supported() {
 }
 
 int ddpb_comm_create_vmm(int rank, int world, size_t payload_bytes, void** out) {
-  if (!(world == 1 || world == 2 || world == 4 || world == 8) || rank < 0 || rank >= world)
-    return DDPB_ERR_SHAPE;
+  if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world) return DDPB_ERR_SHAPE;
   const DrvApi* d = drv();
   if (!d) return DDPB_ERR_UNSUPPORTED;
   Comm* c = new (std::nothrow) Comm();
@@ -1056,9 +1080,36 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
 // (n <= 5,120).  layout: 0 = partial element i is slice element i; 1 = the partials are conv3x3
 // <32,64> weight-gradient accumulator images (n = 18,944) and the slice is net.2.weight followed by
 // net.2.bias (push only).
+// ddpb_reduce_allreduce_sgd_pack: same, and with layout 1 also rewrites `pack` (the split bf16 tile
+// images of net.2.weight, ddpb_conv3x3_pack_split_bytes(32, 64) bytes) from the updated weights.
+static int reduce_allreduce_sgd_impl(void* comm, const float* partials, int nparts, long long n,
+                                     size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                                     int layout, int slot, __nv_bfloat16* pack, const float* bias_part,
+                                     int bp_nsplit, int bp_nbx, int bp_hw, void* stream);
+
 int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
                               size_t grad_off, size_t param_off, const float* lr_dev, int algo,
                               int layout, int slot, void* stream) {
+  return reduce_allreduce_sgd_impl(comm, partials, nparts, n, grad_off, param_off, lr_dev, algo, layout,
+                                   slot, nullptr, nullptr, 0, 0, 0, stream);
+}
+// bias_part (optional, layout 1): exact-fp32 bias-gradient parts written by ddpb_linear_bwd_f32
+// (extents bp_nsplit x bp_nbx, bp_hw = H*W); their fixed-order sum replaces the bias column of the
+// accumulator images.
+int ddpb_reduce_allreduce_sgd_pack(void* comm, const float* partials, int nparts, long long n,
+                                   size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                                   int layout, int slot, void* pack, const float* bias_part,
+                                   int bp_nsplit, int bp_nbx, int bp_hw, void* stream) {
+  if ((pack != nullptr || bias_part != nullptr) && layout != 1) return DDPB_ERR_SHAPE;
+  return reduce_allreduce_sgd_impl(comm, partials, nparts, n, grad_off, param_off, lr_dev, algo, layout,
+                                   slot, static_cast<__nv_bfloat16*>(pack), bias_part, bp_nsplit, bp_nbx,
+                                   bp_hw, stream);
+}
+
+static int reduce_allreduce_sgd_impl(void* comm, const float* partials, int nparts, long long n,
+                                     size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                                     int layout, int slot, __nv_bfloat16* pack, const float* bias_part,
+                                     int bp_nsplit, int bp_nbx, int bp_hw, void* stream) {
   Comm* c = static_cast<Comm*>(comm);
   if (!c->connected) return DDPB_ERR_STATE;
   const long long blocks = (n + 31) / 32;
@@ -1079,10 +1130,11 @@ int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, lon
     if (layout == 1)
       return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD, 1>, grid, dim3(256), 0, st,
                                        pp, c->rank, slot, partials, nparts, static_cast<int>(n), go, po,
-                                       lr_dev, c->timeout_ns));
+                                       lr_dev, pack, bias_part, bp_nsplit, bp_nbx, bp_hw, c->timeout_ns));
     return static_cast<int>(launch_k(reduce_allreduce_sgd_ll_kernel<WORLD, 0>, grid, dim3(256), 0, st, pp,
                                      c->rank, slot, partials, nparts, static_cast<int>(n), go, po,
-                                     lr_dev, c->timeout_ns));
+                                     lr_dev, static_cast<__nv_bfloat16*>(nullptr),
+                                     static_cast<const float*>(nullptr), 0, 0, 0, c->timeout_ns));
   });
   return static_cast<int>(cudaGetLastError());
 }

@@ -67,10 +67,20 @@ __device__ __forceinline__ void producer_group_sync(int grp) {  // 128 threads o
 }
 
 // ------------------------------------------------------------------------------------- forward
+// X3 = false: one TF32 GEMM, K = 16 (9 taps + padding), two K=8 MMAs per tile.
+// X3 = true : "3xTF32" — x = hi + lo and w = hi + lo with all four terms tf32 (22-bit significands):
+//             A row = [x_hi taps 0-8 | x_lo taps 0-8 | 6 zeros] (K = 24), B1 = [w_hi | w_hi | 0],
+//             B2 = [w_lo | 0]; three MMAs against B1 (x_hi.w_hi + x_lo.w_hi) and two against B2
+//             (x_hi.w_lo; columns 9-15 of B2 are zero).  fp32-level accuracy: cuDNN runs this Cin = 1
+//             layer in plain fp32 for some batch sizes (profiles/precision.md), so TF32 alone would be
+//             below the reference there.
+template <bool X3>
 struct C1FwdSmem {
-  static constexpr uint32_t b_bytes = 4 * 32 * 16;        // W1 as tf32 [4 kchunks][32 n][4]
+  static constexpr uint32_t NKA = X3 ? 6 : 4;             // 4-wide k-chunks of an A row
+  static constexpr uint32_t b1_bytes = NKA * 32 * 16;     // W1 as tf32 [kchunks][32 n][4]
+  static constexpr uint32_t b_bytes = b1_bytes + (X3 ? 4 * 32 * 16 : 0);
   static constexpr uint32_t a_plane = kTileM * 16;        // one k-chunk of all 128 rows
-  static constexpr uint32_t a_stage = 4 * a_plane;        // 8 KB
+  static constexpr uint32_t a_stage = NKA * a_plane;      // 8 / 12 KB
   static constexpr uint32_t off_a = b_bytes;
   static constexpr uint32_t off_x = off_a + kC1Stages * a_stage;
   static constexpr uint32_t off_bias = off_x + kXStages * kXStageBytes;
@@ -79,10 +89,14 @@ struct C1FwdSmem {
   static constexpr uint32_t total = off_tmem + 16;
 };
 
+// P selects the output planes: bf16, split (hi + lo bf16 planes, the reference-precision mode) or
+// fp32 rounded to tf32 (for tf32 GEMM consumers: the rounding cuDNN applies to its input).
+template <class P>
 __global__ void __launch_bounds__(kC1FwdThreads, 2)
 conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                    const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, Geom g) {
-  using S = C1FwdSmem;
+                    const float* __restrict__ bias, uint4* __restrict__ out, Geom g) {
+  constexpr bool X3 = P::kSets == 2;  // the reference-precision mode
+  using S = C1FwdSmem<X3>;
   constexpr int CO = 32;
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -115,10 +129,28 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
   // The stream predecessor is the previous step's parameter update, which writes w and bias:
   // nothing global may be read before it has completed.
   pdl_sync();
-  // W1 [32][9] -> tf32 K-major canonical tile: word (k/4)*128 + n*4 + k%4 ; k >= 9 is zero padding
-  for (int i = tid; i < 32 * 16; i += kC1FwdThreads) {
-    const int n = i >> 4, k = i & 15;
-    reinterpret_cast<float*>(smem)[(k >> 2) * 128 + n * 4 + (k & 3)] = k < 9 ? w[n * 9 + k] : 0.f;
+  // W1 [32][9] -> tf32 K-major canonical tile(s): word (k/4)*128 + n*4 + k%4 ; zero padding elsewhere
+  if constexpr (X3) {
+    float* b1 = reinterpret_cast<float*>(smem);
+    float* b2 = reinterpret_cast<float*>(smem + S::b1_bytes);
+    for (int i = tid; i < 32 * 24; i += kC1FwdThreads) {
+      const int n = i / 24, k = i - n * 24;
+      const int tap = k < 9 ? k : k - 9;
+      float hi = 0.f, lo = 0.f;
+      if (k < 18) {
+        const float wv = w[n * 9 + tap];
+        hi = round_tf32(wv);
+        lo = round_tf32(wv - hi);
+      }
+      b1[(k >> 2) * 128 + n * 4 + (k & 3)] = hi;
+      if (k < 16) b2[(k >> 2) * 128 + n * 4 + (k & 3)] = k < 9 ? lo : 0.f;
+    }
+  } else {
+    for (int i = tid; i < 32 * 16; i += kC1FwdThreads) {
+      const int n = i >> 4, k = i & 15;
+      reinterpret_cast<float*>(smem)[(k >> 2) * 128 + n * 4 + (k & 3)] =
+          k < 9 ? round_tf32(w[n * 9 + k]) : 0.f;
+    }
   }
   if (tid < CO) s_bias[tid] = bias[tid];
   fence_proxy_async_smem();
@@ -167,10 +199,24 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
       }
       mbar_wait(bar_empty + stage * 8, phase ^ 1);
       uint8_t* a = smem + S::off_a + stage * S::a_stage + ptid * 16;
+      float lo[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        const float hi = round_tf32(tp[i]);  // nearest, not the MMA's truncation
+        lo[i] = round_tf32(tp[i] - hi);
+        tp[i] = hi;
+      }
       *reinterpret_cast<float4*>(a) = make_float4(tp[0], tp[1], tp[2], tp[3]);
       *reinterpret_cast<float4*>(a + S::a_plane) = make_float4(tp[4], tp[5], tp[6], tp[7]);
-      *reinterpret_cast<float4*>(a + 2 * S::a_plane) = make_float4(tp[8], 0.f, 0.f, 0.f);
-      *reinterpret_cast<float4*>(a + 3 * S::a_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if constexpr (X3) {
+        *reinterpret_cast<float4*>(a + 2 * S::a_plane) = make_float4(tp[8], lo[0], lo[1], lo[2]);
+        *reinterpret_cast<float4*>(a + 3 * S::a_plane) = make_float4(lo[3], lo[4], lo[5], lo[6]);
+        *reinterpret_cast<float4*>(a + 4 * S::a_plane) = make_float4(lo[7], lo[8], 0.f, 0.f);
+        *reinterpret_cast<float4*>(a + 5 * S::a_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        *reinterpret_cast<float4*>(a + 2 * S::a_plane) = make_float4(tp[8], 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(a + 3 * S::a_plane) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       fence_proxy_async_smem();
       mbar_arrive(bar_full + stage * 8);
     }
@@ -187,10 +233,18 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
       tc_fence_after();
       const uint32_t a_stage = s_a + stage * S::a_stage;
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk) {
+      for (int kk = 0; kk < (int)S::NKA / 2; ++kk) {
         const uint64_t adesc = umma_smem_desc(a_stage + kk * 2 * S::a_plane, S::a_plane, 128);
         const uint64_t bdesc = umma_smem_desc(s_base + kk * 2 * 512, 512, 128);
         if (elect_one()) umma_tf32(tmem_base + acc * CO, adesc, bdesc, idesc, kk != 0);
+      }
+      if constexpr (X3) {  // x_hi . w_lo
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          const uint64_t adesc = umma_smem_desc(a_stage + kk * 2 * S::a_plane, S::a_plane, 128);
+          const uint64_t bdesc = umma_smem_desc(s_base + S::b1_bytes + kk * 2 * 512, 512, 128);
+          if (elect_one()) umma_tf32(tmem_base + acc * CO, adesc, bdesc, idesc, 1);
+        }
       }
       if (elect_one()) {
         umma_commit(bar_empty + stage * 8);
@@ -214,19 +268,38 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_tempty + acc * 8);
+      float xo[32];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint4 o;
-        uint32_t* op = reinterpret_cast<uint32_t*>(&o);
+      for (int c = 0; c < 32; ++c) {
+        const float t = __uint_as_float(v[c]) + s_bias[c];
+        xo[c] = valid ? fmaxf(t, 0.f) : 0.f;
+      }
+      const long long row = (long long)kGuard + rel;
+      if constexpr (P::kTf32) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float x0 = __uint_as_float(v[j * 8 + 2 * e]) + s_bias[j * 8 + 2 * e];
-          float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + s_bias[j * 8 + 2 * e + 1];
-          x0 = valid ? fmaxf(x0, 0.f) : 0.f;
-          x1 = valid ? fmaxf(x1, 0.f) : 0.f;
-          op[e] = pack_bf16x2(x0, x1);
+        for (int j = 0; j < 8; ++j)
+          out[(long long)j * g.plane_rows + row] =
+              make_uint4(__float_as_uint(round_tf32(xo[4 * j])), __float_as_uint(round_tf32(xo[4 * j + 1])),
+                         __float_as_uint(round_tf32(xo[4 * j + 2])), __float_as_uint(round_tf32(xo[4 * j + 3])));
+      } else if constexpr (P::kSets == 2) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float hi[8], lo[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) split_bf16(xo[8 * j + e], hi[e], lo[e]);
+          out[(long long)j * g.plane_rows + row] =
+              make_uint4(pack_bf16x2(hi[0], hi[1]), pack_bf16x2(hi[2], hi[3]), pack_bf16x2(hi[4], hi[5]),
+                         pack_bf16x2(hi[6], hi[7]));
+          out[(long long)(4 + j) * g.plane_rows + row] =
+              make_uint4(pack_bf16x2(lo[0], lo[1]), pack_bf16x2(lo[2], lo[3]), pack_bf16x2(lo[4], lo[5]),
+                         pack_bf16x2(lo[6], lo[7]));
         }
-        *reinterpret_cast<uint4*>(out + ((long long)j * g.plane_rows + kGuard + rel) * 8) = o;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          out[(long long)j * g.plane_rows + row] =
+              make_uint4(pack_bf16x2(xo[8 * j], xo[8 * j + 1]), pack_bf16x2(xo[8 * j + 2], xo[8 * j + 3]),
+                         pack_bf16x2(xo[8 * j + 4], xo[8 * j + 5]), pack_bf16x2(xo[8 * j + 6], xo[8 * j + 7]));
       }
     }
   }
@@ -239,10 +312,19 @@ conv1_fwd_tc_kernel(const float* __restrict__ x, const float* __restrict__ w,
 // Accumulator [64 rows (32 real channels)][32 columns]:
 //   columns 0..8 : sum dact * bf16_hi(x tap)     9 : sum dact (bias gradient)
 //   columns 16..24: sum dact * bf16_lo(x tap)    others: zero
+//
+// Split planes: dact = hi + lo.  The four lo planes sit where the bf16 layout has its four zero planes
+// (rows 32..63 of the M = 64 operand): the MMA loop runs twice per tile, once with the A descriptor on
+// the hi planes and once on the lo planes, accumulating into rows 0..31 both times.  Rows 32..63 then
+// see whatever follows in shared memory — accumulator rows are independent and those are never read.
+template <class P>
 struct C1WgradSmem {
+  static_assert(!P::kTf32, "no MN-major tf32 operand in the no-swizzle layout");
   static constexpr uint32_t a_plane = kTileM * 16;   // 2048
-  static constexpr uint32_t a_bytes = 8 * a_plane;   // planes 4..7 stay zero (M = 64 needs 8 groups)
-  static constexpr uint32_t b_bytes = 4 * a_plane;   // N = 32 -> 4 groups of 8 columns
+  static constexpr uint32_t a_real = 4;              // planes that hold the 32 real channels
+  static constexpr uint32_t a_bytes = 8 * a_plane;   // bf16: planes 4..7 stay zero; split: the lo planes
+  static constexpr uint32_t b_planes = 4;            // N = 32 columns
+  static constexpr uint32_t b_bytes = b_planes * a_plane;
   static constexpr uint32_t stage = a_bytes + b_bytes;
   static constexpr uint32_t off_x = kC1Stages * stage;
   static constexpr uint32_t off_bar = off_x + kXStages * kXStageBytes;
@@ -250,10 +332,11 @@ struct C1WgradSmem {
   static constexpr uint32_t total = off_tmem + 16;
 };
 
+template <class P>
 __global__ void __launch_bounds__(kC1Threads, 1)
-conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restrict__ x,
+conv1_wgrad_tc_kernel(const uint4* __restrict__ dact, const float* __restrict__ x,
                       float* __restrict__ partial, Geom g) {
-  using S = C1WgradSmem;
+  using S = C1WgradSmem<P>;
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t s_base = smem_u32(smem);
@@ -325,29 +408,27 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
           x_stage_issue(x, g, static_cast<int>(tn), s_base + S::off_x + xst * kXStageBytes,
                         bar_x + xst * 8);
       }
-      // x = hi + lo with both terms bf16
+      // x = hi + lo with both terms bf16; column 9 of the hi block = ones -> bias gradient
       uint32_t hi[5], lo[5];
       float hf[9], lf[9];
 #pragma unroll
-      for (int i = 0; i < 9; ++i) {
-        hf[i] = __bfloat162float(__float2bfloat16(tp[i]));
-        lf[i] = tp[i] - hf[i];
-      }
+      for (int i = 0; i < 9; ++i) split_bf16(tp[i], hf[i], lf[i]);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         hi[i] = pack_bf16x2(hf[2 * i], hf[2 * i + 1]);
         lo[i] = pack_bf16x2(lf[2 * i], lf[2 * i + 1]);
       }
-      hi[4] = pack_bf16x2(hf[8], 1.0f);  // column 9 = ones -> bias gradient
+      hi[4] = pack_bf16x2(hf[8], 1.0f);
       lo[4] = pack_bf16x2(lf[8], 0.f);
       mbar_wait(bar_empty + stage * 8, phase ^ 1);
       if (ptid == 0) {
-        mbar_arrive_expect_tx(bar_fa + stage * 8, 4 * S::a_plane);
+        constexpr int NP = P::kSets * 4;  // hi planes (and, split, the lo planes right after them)
+        mbar_arrive_expect_tx(bar_fa + stage * 8, NP * S::a_plane);
         const long long rowa = (long long)kGuard + (long long)t * kTileM;
 #pragma unroll
-        for (int p = 0; p < 4; ++p)
+        for (int p = 0; p < NP; ++p)
           bulk_g2s(s_base + stage * S::stage + p * S::a_plane,
-                   dact + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane, bar_fa + stage * 8);
+                   dact + ((long long)p * g.plane_rows + rowa), S::a_plane, bar_fa + stage * 8);
       }
       uint8_t* b = smem + stage * S::stage + S::a_bytes + ptid * 16;
       *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -387,10 +468,13 @@ conv1_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dact, const float* __res
       const uint32_t sa = s_base + stage * S::stage;
       const uint32_t sb = sa + S::a_bytes;
 #pragma unroll
-      for (int ks = 0; ks < kTileM / 16; ++ks) {
-        const uint64_t adesc = umma_smem_desc(sa + ks * 256, 128, S::a_plane);
-        const uint64_t bdesc = umma_smem_desc(sb + ks * 256, 128, S::a_plane);
-        if (elect_one()) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks) != 0);
+      for (int set = 0; set < P::kSets; ++set) {  // dact hi, then (split) dact lo
+#pragma unroll
+        for (int ks = 0; ks < kTileM / 16; ++ks) {
+          const uint64_t adesc = umma_smem_desc(sa + set * 4 * S::a_plane + ks * 256, 128, S::a_plane);
+          const uint64_t bdesc = umma_smem_desc(sb + ks * 256, 128, S::a_plane);
+          if (elect_one()) umma_bf16(tmem_base, adesc, bdesc, idesc, (it | ks | set) != 0);
+        }
       }
       if (elect_one()) umma_commit(bar_empty + stage * 8);
       __syncwarp();
@@ -421,17 +505,16 @@ static int c1_ctas_per_sm() {
 }
 // Two CTAs per SM only when every CTA still gets a few tiles (measured: B=4096 step 1.243 ->
 // 1.122 ms, but at B=64 = 450 tiles the extra start-up cost makes the step slightly slower).
-static int c1_grid(int ntiles) {
+static int c1_grid(int ntiles, bool allow_two) {
   const int sms = ddpb_num_sms();
-  const int per_sm = ntiles >= 4 * kC1MaxCtasPerSm * sms ? c1_ctas_per_sm() : 1;
+  const int per_sm = (allow_two && ntiles >= 4 * kC1MaxCtasPerSm * sms) ? c1_ctas_per_sm() : 1;
   const int slots = sms * per_sm;
   return ntiles < slots ? ntiles : slots;
 }
 
-extern "C" {
-
-int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out, int cin, int cout,
-                      int batch, int batch_cap, int H, int W, void* stream) {
+template <class P>
+static int conv1_fwd_tc_launch(const float* x, const float* w, const float* b, void* out, int cin,
+                               int cout, int batch, int batch_cap, int H, int W, void* stream) {
   if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
   if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
@@ -439,61 +522,92 @@ int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out,
   int dev = 0;
   DDPB_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      C1FwdSmem::total));
+    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_fwd_tc_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      C1FwdSmem<P::kSets == 2>::total));
     configured[dev & 63] = true;
   }
-  const int grid = c1_grid(g.ntiles);
-  return static_cast<int>(launch_k(conv1_fwd_tc_kernel, dim3(grid), dim3(kC1FwdThreads), C1FwdSmem::total,
-                                   static_cast<cudaStream_t>(stream), x, w, b,
-                                   static_cast<__nv_bfloat16*>(out), g));
+  const int grid = c1_grid(g.ntiles, true);
+  return static_cast<int>(launch_k(conv1_fwd_tc_kernel<P>, dim3(grid), dim3(kC1FwdThreads),
+                                   C1FwdSmem<P::kSets == 2>::total, static_cast<cudaStream_t>(stream), x, w, b,
+                                   static_cast<uint4*>(out), g));
+}
+
+template <class P>
+static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratch, int* nparts, int cin,
+                                 int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  using S = C1WgradSmem<P>;
+  static bool configured[64] = {};
+  int dev = 0;
+  DDPB_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_tc_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      S::total));
+    configured[dev & 63] = true;
+  }
+  const int grid = c1_grid(g.ntiles, 2 * S::total <= 220 * 1024);
+  DDPB_CUDA_OK(launch_k(conv1_wgrad_tc_kernel<P>, dim3(grid), dim3(kC1Threads), S::total,
+                        static_cast<cudaStream_t>(stream), static_cast<const uint4*>(dact), x, scratch, g));
+  *nparts = grid;
+  return 0;
+}
+
+extern "C" {
+
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
+
+int ddpb_conv1_fwd_tc(const float* x, const float* w, const float* b, void* out, int cin, int cout,
+                      int batch, int batch_cap, int H, int W, void* stream) {
+  return conv1_fwd_tc_launch<Bf16Planes>(x, w, b, out, cin, cout, batch, batch_cap, H, W, stream);
+}
+// Same with split output planes (hi + lo bf16: the reference-precision mode).
+int ddpb_conv1_fwd_tc_split(const float* x, const float* w, const float* b, void* out, int cin, int cout,
+                            int batch, int batch_cap, int H, int W, void* stream) {
+  return conv1_fwd_tc_launch<SplitPlanes>(x, w, b, out, cin, cout, batch, batch_cap, H, W, stream);
+}
+// Same, fp32 output planes (values rounded to tf32).
+int ddpb_conv1_fwd_tc_f32(const float* x, const float* w, const float* b, void* out, int cin, int cout,
+                          int batch, int batch_cap, int H, int W, void* stream) {
+  return conv1_fwd_tc_launch<F32Planes>(x, w, b, out, cin, cout, batch, batch_cap, H, W, stream);
 }
 
 size_t ddpb_conv1_wgrad_tc_scratch_bytes(int cin, int cout) {
   return static_cast<size_t>(ddpb_num_sms()) * kC1MaxCtasPerSm * (cout * cin * 9 + cout) * sizeof(float);
 }
 
-int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
-
-static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratch, int* nparts, int cin,
-                                 int cout, int batch, int batch_cap, int H, int W, void* stream);
-
 // Partials only: scratch[nparts][cout*cin*9 + cout]; *nparts_out (host) receives the partial count.
 // Feed them to ddpb_reduce_allreduce_sgd (fused split-K reduce + all-reduce + SGD).
 int ddpb_conv1_wgrad_tc_partials(const void* dact, const float* x, float* scratch, int* nparts_out,
                                  int cin, int cout, int batch, int batch_cap, int H, int W,
                                  void* stream) {
-  return conv1_wgrad_tc_launch(dact, x, scratch, nparts_out, cin, cout, batch, batch_cap, H, W, stream);
+  return conv1_wgrad_tc_launch<Bf16Planes>(dact, x, scratch, nparts_out, cin, cout, batch, batch_cap, H,
+                                           W, stream);
+}
+int ddpb_conv1_wgrad_tc_split_partials(const void* dact, const float* x, float* scratch, int* nparts_out,
+                                     int cin, int cout, int batch, int batch_cap, int H, int W,
+                                     void* stream) {
+  return conv1_wgrad_tc_launch<SplitPlanes>(dact, x, scratch, nparts_out, cin, cout, batch, batch_cap, H,
+                                          W, stream);
 }
 
 // dw_db: cout*cin*9 weight gradients immediately followed by cout bias gradients.
 int ddpb_conv1_wgrad_tc(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
                         int cout, int batch, int batch_cap, int H, int W, void* stream) {
   int grid = 0;
-  const int rc = conv1_wgrad_tc_launch(dact, x, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
+  const int rc = conv1_wgrad_tc_launch<Bf16Planes>(dact, x, scratch, &grid, cin, cout, batch, batch_cap,
+                                                   H, W, stream);
+  if (rc != 0) return rc;
+  return ddpb_reduce_partials(scratch, grid, (long long)cout * cin * 9 + cout, dw_db, stream);
+}
+int ddpb_conv1_wgrad_tc_split(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
+                            int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  int grid = 0;
+  const int rc = conv1_wgrad_tc_launch<SplitPlanes>(dact, x, scratch, &grid, cin, cout, batch, batch_cap,
+                                                  H, W, stream);
   if (rc != 0) return rc;
   return ddpb_reduce_partials(scratch, grid, (long long)cout * cin * 9 + cout, dw_db, stream);
 }
 
 }  // extern "C"
-
-static int conv1_wgrad_tc_launch(const void* dact, const float* x, float* scratch, int* nparts, int cin,
-                                 int cout, int batch, int batch_cap, int H, int W, void* stream) {
-  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
-  if (H * W * 4 * 2 > (int)kXStageBytes || (H * W * 4) % 16 != 0) return DDPB_ERR_SHAPE;
-  const Geom g = make_geom(batch, batch_cap, H, W);
-  static bool configured[64] = {};
-  int dev = 0;
-  DDPB_CUDA_OK(cudaGetDevice(&dev));
-  if (!configured[dev & 63]) {
-    DDPB_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      C1WgradSmem::total));
-    configured[dev & 63] = true;
-  }
-  const int grid = c1_grid(g.ntiles);
-  DDPB_CUDA_OK(launch_k(conv1_wgrad_tc_kernel, dim3(grid), dim3(kC1Threads), C1WgradSmem::total,
-                        static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(dact), x,
-                        scratch, g));
-  *nparts = grid;
-  return 0;
-}

@@ -9,9 +9,13 @@
 // Warp roles (192 threads, one CTA per SM, persistent over tiles):
 //   warp 0    bulk-copy producer (one lane)
 //   warp 1    TMEM allocator + MMA issuer (one lane issues tcgen05.mma)
-//   warps 2-9 epilogue: tcgen05.ld the accumulator tile, fuse bias/ReLU/mask, store bf16 planes
+//   warps 2-9 epilogue: tcgen05.ld the accumulator tile, fuse bias/ReLU/mask, store the planes
 //             (two warps per TMEM lane quadrant, each takes half of the columns: the epilogue,
 //             not the MMA, was the per-tile bottleneck with four warps — profiles/)
+//
+// Every kernel is a template over the plane formats of layout.cuh.  The reference-precision mode
+// runs them on split planes (x = hi + lo, three MMAs per K step, "bf16x3"): at least the operand
+// precision of the TF32 convolutions cuDNN runs for the reference, fp32 accumulation.
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
@@ -24,19 +28,24 @@ constexpr int kWgradThreads = 192;  // wgrad: 1 producer + 1 MMA + 4 epilogue wa
 constexpr uint32_t kRowBytes = 16;
 constexpr uint32_t kStagePlaneBytes = kStageRows * kRowBytes;  // 3072
 
-template <int CI, int CO, int STAGES>
+template <class P, int CI, int CO, int STAGES>
 struct ConvSmem {
-  static constexpr uint32_t KP = CI / 8;
-  // B tile of one tap: [KP k-chunks][CO rows][16 B]; the k-chunk stride (UMMA LBO) is skewed by
-  // 16 B so that the fp32->bf16 conversion below writes shared memory without bank conflicts.
-  static constexpr uint32_t w_lbo = CO * 16 + 16;
+  static constexpr uint32_t KP = CI / P::kCh;      // planes per set
+  static constexpr uint32_t NPL = P::kSets * KP;   // planes staged per tile (hi set, then lo set)
+  static constexpr bool kPrepacked = P::kTf32 || P::kSets == 2;
+  // B tile of one tap: [KP k-chunks][CO rows][16 B].  Plain bf16: built per CTA from the fp32 master
+  // weights; the k-chunk stride (UMMA LBO) is skewed by 16 B so that the conversion writes shared
+  // memory without bank conflicts.  Split / tf32: the tile images (one per set) are pre-packed in
+  // global memory (pack kernels below / the fused bucket update) and arrive with one bulk copy.
+  static constexpr uint32_t w_lbo = CO * 16 + (kPrepacked ? 0 : 16);
   static constexpr uint32_t w_tap_bytes = KP * w_lbo;
-  static constexpr uint32_t w_bytes = (9 * w_tap_bytes + 127) / 128 * 128;
-  static constexpr uint32_t a_stage_bytes = KP * kStagePlaneBytes;
+  static constexpr uint32_t w_set_bytes = 9 * w_tap_bytes;
+  static constexpr uint32_t w_bytes = (P::kSets * w_set_bytes + 127) / 128 * 128;
+  static constexpr uint32_t a_stage_bytes = NPL * kStagePlaneBytes;
   static constexpr uint32_t off_a = w_bytes;
-  // fp32 master weights are bulk-copied (TMA, one copy) into a staging area and converted from
-  // there.  It aliases the A-stage ring when that is large enough (the ring is idle during setup).
-  static constexpr uint32_t wstage_bytes = 9 * CI * CO * 4;
+  // plain bf16: fp32 master weights are bulk-copied (TMA, one copy) into a staging area and converted
+  // from there.  It aliases the A-stage ring when that is large enough (the ring is idle during setup).
+  static constexpr uint32_t wstage_bytes = kPrepacked ? 0 : 9 * CI * CO * 4;
   static constexpr uint32_t ring_bytes = STAGES * a_stage_bytes;
   static constexpr bool stage_aliases_ring = ring_bytes >= wstage_bytes;
   static constexpr uint32_t off_wstage = stage_aliases_ring ? off_a : off_a + ring_bytes;
@@ -44,7 +53,56 @@ struct ConvSmem {
   static constexpr uint32_t off_bar = off_bias + CO * 4;
   static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 5) * 8;
   static constexpr uint32_t total = off_tmem + 16;
+  static_assert(total <= 232448, "conv CTA exceeds the 227 KB shared-memory limit");
 };
+
+// One MMA of the format's kind (bf16 / split: kind::f16, K = 16; fp32 planes: kind::tf32, K = 8).
+template <class P>
+__device__ __forceinline__ void umma_p(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                       uint32_t accumulate) {
+  if constexpr (P::kTf32) umma_tf32(d_tmem, adesc, bdesc, idesc, accumulate);
+  else umma_bf16(d_tmem, adesc, bdesc, idesc, accumulate);
+}
+template <class P>
+__host__ __device__ constexpr uint32_t umma_idesc_p(int M, int N, int a_mn, int b_mn) {
+  return P::kTf32 ? umma_idesc_tf32(M, N, a_mn, b_mn) : umma_idesc_bf16(M, N, a_mn, b_mn);
+}
+
+// Store CH*NV consecutive channels (starting at channel c0, a multiple of 8) of one pixel row in
+// the output format PO.  `nch` = channels of the whole tensor (locates the lo plane set).
+template <class PO, int N>
+__device__ __forceinline__ void store_channels(uint4* __restrict__ out, long long plane_rows, long long row,
+                                               int c0, int nch, const float (&x)[N], int round_out) {
+  if constexpr (PO::kTf32) {
+#pragma unroll
+    for (int j = 0; j < N / 4; ++j) {
+      float v[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) v[e] = round_out ? round_tf32(x[4 * j + e]) : x[4 * j + e];
+      out[(long long)(c0 / 4 + j) * plane_rows + row] =
+          make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+    }
+  } else if constexpr (PO::kSets == 2) {
+#pragma unroll
+    for (int j = 0; j < N / 8; ++j) {
+      float hi[8], lo[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) split_bf16(x[8 * j + e], hi[e], lo[e]);
+      out[(long long)(c0 / 8 + j) * plane_rows + row] =
+          make_uint4(pack_bf16x2(hi[0], hi[1]), pack_bf16x2(hi[2], hi[3]), pack_bf16x2(hi[4], hi[5]),
+                     pack_bf16x2(hi[6], hi[7]));
+      out[(long long)(nch / 8 + c0 / 8 + j) * plane_rows + row] =
+          make_uint4(pack_bf16x2(lo[0], lo[1]), pack_bf16x2(lo[2], lo[3]), pack_bf16x2(lo[4], lo[5]),
+                     pack_bf16x2(lo[6], lo[7]));
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < N / 8; ++j)
+      out[(long long)(c0 / 8 + j) * plane_rows + row] =
+          make_uint4(pack_bf16x2(x[8 * j], x[8 * j + 1]), pack_bf16x2(x[8 * j + 2], x[8 * j + 3]),
+                     pack_bf16x2(x[8 * j + 4], x[8 * j + 5]), pack_bf16x2(x[8 * j + 6], x[8 * j + 7]));
+  }
+}
 
 // Optional in-kernel phase timestamps (SM clock) for bring-up/tuning: prof[block*16 + slot].
 __device__ __forceinline__ void prof_stamp(unsigned long long* prof, int slot) {
@@ -58,13 +116,17 @@ constexpr uint32_t pow2_cols(uint32_t c) {
 // MODE 0: out = relu(conv(in, w) + bias)                 (GEMM K = CI input channels, N = CO)
 // MODE 1: out = relu'(mask) * conv_transpose(in, w)      (in = grad wrt conv output with CI
 //         channels, w = the layer's weight [CI][CO][3][3], out = grad wrt conv input, CO chans)
-template <int CI, int CO, int MODE, int STAGES>
+// Planes are addressed as 16-byte rows (uint4) whatever the format.  P = format of `in` (and of the
+// tensor-core operands), PO = format of `out`, PM = format of `mask` (MODE 1).  For split / fp32
+// input planes `w` is the pre-packed tile image of this MODE (ddpb_conv3x3_pack_split / _tf32);
+// `round_out` != 0 rounds an fp32 result to tf32 (for when the next consumer is a tf32 GEMM).
+template <class P, class PO, class PM, int CI, int CO, int MODE, int STAGES>
 __global__ void __launch_bounds__(kConvThreads, 1)
-conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w,
-                  const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask,
-                  __nv_bfloat16* __restrict__ out, Geom g, unsigned long long* prof) {
-  using S = ConvSmem<CI, CO, STAGES>;
-  constexpr uint32_t KP = CI / 8;
+conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
+                  const float* __restrict__ bias, const uint4* __restrict__ mask,
+                  uint4* __restrict__ out, Geom g, int round_out, unsigned long long* prof) {
+  using S = ConvSmem<P, CI, CO, STAGES>;
+  constexpr uint32_t KP = CI / P::kCh;
   constexpr uint32_t TMEM_COLS = pow2_cols(2 * CO);
   extern __shared__ __align__(128) uint8_t smem[];
 
@@ -94,9 +156,15 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
     }
     mbar_init(bar_w, 1);
     fence_mbar_init();
-    // fp32 master weights: one bulk async copy into the staging area
-    mbar_arrive_expect_tx(bar_w, S::wstage_bytes);
-    bulk_g2s(s_base + S::off_wstage, w, S::wstage_bytes, bar_w);
+    if constexpr (S::kPrepacked) {
+      // pre-packed tile images (all sets): one bulk async copy straight into the B-tile area
+      mbar_arrive_expect_tx(bar_w, P::kSets * S::w_set_bytes);
+      bulk_g2s(s_w, w, P::kSets * S::w_set_bytes, bar_w);
+    } else {
+      // fp32 master weights: one bulk async copy into the staging area
+      mbar_arrive_expect_tx(bar_w, S::wstage_bytes);
+      bulk_g2s(s_base + S::off_wstage, w, S::wstage_bytes, bar_w);
+    }
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(s_tmem), TMEM_COLS);
@@ -112,7 +180,7 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
   //   t*w_tap + (k/8)*w_lbo + n*16 + (k%8)*2          => LBO = w_lbo, SBO = 128
   // Thread->element maps are chosen so that both the staged reads and the tile writes of a warp
   // fall into 32 different banks.
-  {
+  if constexpr (!S::kPrepacked) {
     const float* ws = reinterpret_cast<const float*>(smem + S::off_wstage);
     if (MODE == 0) {
       // source w[n][k][tap] (tap fastest, then k): a warp covers 16 k-pairs x 2 taps of one n
@@ -171,16 +239,16 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
         mbar_arrive_expect_tx(bar_full + stage * 8, S::a_stage_bytes);
         const long long row0 = (long long)kGuard + (long long)t * kTileM - kHalo;
 #pragma unroll
-        for (uint32_t p = 0; p < KP; ++p)
+        for (uint32_t p = 0; p < S::NPL; ++p)  // hi planes, then (split) lo planes
           bulk_g2s(s_a + stage * S::a_stage_bytes + p * kStagePlaneBytes,
-                   in + ((long long)p * g.plane_rows + row0) * 8, kStagePlaneBytes,
+                   in + ((long long)p * g.plane_rows + row0), kStagePlaneBytes,
                    bar_full + stage * 8);
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // MMA issuer: the whole warp stays converged, one elected lane issues (see elect_one()).
-    constexpr uint32_t idesc = umma_idesc_bf16(kTileM, CO, 0, 0);
+    constexpr uint32_t idesc = umma_idesc_p<P>(kTileM, CO, 0, 0);
     uint32_t tap_off[9];
 #pragma unroll
     for (int tap = 0; tap < 9; ++tap)
@@ -200,12 +268,26 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
 #pragma unroll
-        for (int kk = 0; kk < CI / 16; ++kk) {
+        for (int kk = 0; kk < CI / P::kMmaK; ++kk) {
           const uint64_t adesc = umma_smem_desc(a_stage + tap_off[tap] + kk * 2 * kStagePlaneBytes,
                                                 kStagePlaneBytes, 128);
           const uint64_t bdesc =
               umma_smem_desc(s_w + tap * S::w_tap_bytes + kk * 2 * S::w_lbo, S::w_lbo, 128);
-          if (elect_one()) umma_bf16(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
+          if constexpr (P::kSets == 2) {
+            // split operands: hi.hi + lo.hi + hi.lo (lo planes / lo tile image follow the hi ones)
+            const uint64_t adesc_lo =
+                umma_smem_desc(a_stage + KP * kStagePlaneBytes + tap_off[tap] + kk * 2 * kStagePlaneBytes,
+                               kStagePlaneBytes, 128);
+            const uint64_t bdesc_lo = umma_smem_desc(
+                s_w + S::w_set_bytes + tap * S::w_tap_bytes + kk * 2 * S::w_lbo, S::w_lbo, 128);
+            if (elect_one()) {
+              umma_p<P>(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
+              umma_p<P>(d_tmem, adesc_lo, bdesc, idesc, 1);
+              umma_p<P>(d_tmem, adesc, bdesc_lo, idesc, 1);
+            }
+          } else {
+            if (elect_one()) umma_p<P>(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
+          }
         }
       }
       if (elect_one()) {
@@ -228,12 +310,12 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
       int img, h, wc;
       const bool valid = decode_row(g, rel, img, h, wc);
       const long long row = (long long)kGuard + rel;
-      uint4 mk[COLS / 8];
+      constexpr int MCH = PM::kCh;        // mask: channels per 16-byte row (hi planes when split)
+      constexpr int NMV = COLS / MCH;
+      uint4 mk[NMV];
       if (MODE == 1) {  // issue the ReLU-mask loads before blocking on the accumulator
 #pragma unroll
-        for (int j = 0; j < COLS / 8; ++j)
-          mk[j] = *reinterpret_cast<const uint4*>(
-              mask + ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8);
+        for (int j = 0; j < NMV; ++j) mk[j] = mask[(long long)(c0 / MCH + j) * g.plane_rows + row];
       }
       mbar_wait(bar_tfull + acc * 8, aphase);
       tc_fence_after();
@@ -245,36 +327,24 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_tempty + acc * 8);  // accumulator is in registers: release it early
+      float x[COLS];
+      if (MODE == 0) {
 #pragma unroll
-      for (int j = 0; j < COLS / 8; ++j) {
-        const long long off = ((long long)(c0 / 8 + j) * g.plane_rows + row) * 8;
-        uint4 o;
-        uint32_t* op = reinterpret_cast<uint32_t*>(&o);
-        if (MODE == 0) {
-          const float4 b0 = *reinterpret_cast<const float4*>(s_bias + c0 + j * 8);
-          const float4 b1 = *reinterpret_cast<const float4*>(s_bias + c0 + j * 8 + 4);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x0 = __uint_as_float(v[j * 8 + 2 * e]) + bb[2 * e];
-            float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]) + bb[2 * e + 1];
-            x0 = valid ? fmaxf(x0, 0.f) : 0.f;
-            x1 = valid ? fmaxf(x1, 0.f) : 0.f;
-            op[e] = pack_bf16x2(x0, x1);
-          }
-        } else {
-          const uint32_t* mp = reinterpret_cast<const uint32_t*>(&mk[j]);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x0 = __uint_as_float(v[j * 8 + 2 * e]);
-            float x1 = __uint_as_float(v[j * 8 + 2 * e + 1]);
-            x0 = (valid && bf16_lo(mp[e]) > 0.f) ? x0 : 0.f;
-            x1 = (valid && bf16_hi(mp[e]) > 0.f) ? x1 : 0.f;
-            op[e] = pack_bf16x2(x0, x1);
-          }
+        for (int c = 0; c < COLS; ++c) {
+          const float t = __uint_as_float(v[c]) + s_bias[c0 + c];
+          x[c] = valid ? fmaxf(t, 0.f) : 0.f;
         }
-        *reinterpret_cast<uint4*>(out + off) = o;
+      } else {
+        const uint32_t* mp = reinterpret_cast<const uint32_t*>(mk);
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) {
+          float m;  // sign of the forward activation (for split planes its hi term decides)
+          if constexpr (PM::kTf32) m = __uint_as_float(mp[c]);
+          else m = (c & 1) ? bf16_hi(mp[c >> 1]) : bf16_lo(mp[c >> 1]);
+          x[c] = (valid && m > 0.f) ? __uint_as_float(v[c]) : 0.f;
+        }
       }
+      store_channels<PO, COLS>(out, g.plane_rows, row, c0, CO, x, round_out);
     }
     if (tid == 64) prof_stamp(prof, 7);
   }
@@ -297,28 +367,37 @@ conv3x3_tc_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict_
 // first MMA (N = 3*CI + 8).  Accumulator columns: [row0: 3*CI taps | 8 bias][row1: 3*CI][row2: 3*CI].
 // Each CTA accumulates its share of pixel tiles in TMEM and writes one partial; wgrad_reduce_kernel
 // sums the partials in a fixed order (deterministic).
-template <int CI, int CO, int STAGES>
+// Split planes: the tile's hi and lo sets are both staged and every K step issues three MMAs per
+// filter row, (dout_hi, in_hi) + (dout_lo, in_hi) + (dout_hi, in_lo); the ones plane belongs to the
+// hi set only, so the bias gradient is sum(dout_hi) + sum(dout_lo).
+// (There is no fp32-plane instantiation: tcgen05 defines an MN-major tf32 operand only for the
+// 128B_BASE32B swizzled layout, not for the no-swizzle layout of the planes — tools/umma_probe.cu.)
+template <class P, int CI, int CO, int STAGES>
 struct WgradSmem {
-  static constexpr uint32_t AP = CO / 8, BP = CI / 8;
-  static constexpr uint32_t NBP = 3 * BP + 1;              // B planes per stage incl. the ones plane
+  static_assert(!P::kTf32, "no MN-major tf32 operand in the no-swizzle layout");
+  static constexpr uint32_t AP = CO / P::kCh, BP = CI / P::kCh;
   static constexpr uint32_t a_plane = kTileM * kRowBytes;  // 2048
-  static constexpr uint32_t a_bytes = AP * a_plane;
-  static constexpr uint32_t b_bytes = NBP * kStagePlaneBytes;
+  static constexpr uint32_t a_set = AP * a_plane;
+  static constexpr uint32_t a_bytes = P::kSets * a_set;
+  static constexpr uint32_t b_set = (3 * BP + 1) * kStagePlaneBytes;  // 3 shifted copies + ones plane
+  static constexpr uint32_t b_lo_set = 3 * BP * kStagePlaneBytes;     // the lo set has no ones plane
+  static constexpr uint32_t b_bytes = b_set + (P::kSets == 2 ? b_lo_set : 0);
   static constexpr uint32_t stage_bytes = a_bytes + b_bytes;
-  static constexpr uint32_t tx_bytes = a_bytes + 3 * BP * kStagePlaneBytes;
+  static constexpr uint32_t tx_bytes = a_bytes + P::kSets * 3 * BP * kStagePlaneBytes;
   static constexpr uint32_t off_bar = STAGES * stage_bytes;
   static constexpr uint32_t off_tmem = off_bar + (2 * STAGES + 1) * 8;
   static constexpr uint32_t total = off_tmem + 16;
   static constexpr uint32_t n0 = 3 * CI + 8;  // first filter row + bias block
   static constexpr uint32_t n1 = 3 * CI;
   static constexpr uint32_t ncols = n0 + 2 * n1;  // 9*CI + 8
+  static_assert(total <= 232448, "wgrad CTA exceeds the 227 KB shared-memory limit");
 };
 
-template <int CI, int CO, int STAGES>
+template <class P, int CI, int CO, int STAGES>
 __global__ void __launch_bounds__(kWgradThreads, 1)
-conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ in,
+conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ in,
                         float* __restrict__ partial, Geom g, unsigned long long* prof) {
-  using S = WgradSmem<CI, CO, STAGES>;
+  using S = WgradSmem<P, CI, CO, STAGES>;
   static_assert(CO == 64 || CO == 128, "UMMA M must be 64 or 128");
   static_assert(S::n0 <= 128, "one filter row must fit a 128-column TMEM allocation");
   // Three separate 128-column allocations (one per filter row) instead of one 512-column block:
@@ -374,16 +453,18 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         const uint32_t sb = sa + S::a_bytes;
         const long long rowa = (long long)kGuard + (long long)t * kTileM;
 #pragma unroll
-        for (uint32_t p = 0; p < S::AP; ++p)
-          bulk_g2s(sa + p * S::a_plane, dout + ((long long)p * g.plane_rows + rowa) * 8, S::a_plane,
+        for (uint32_t p = 0; p < P::kSets * S::AP; ++p)  // hi planes, then (split) lo planes
+          bulk_g2s(sa + p * S::a_plane, dout + ((long long)p * g.plane_rows + rowa), S::a_plane,
                    bar_full + stage * 8);
 #pragma unroll
-        for (int sh = 0; sh < 3; ++sh)  // horizontal tap s: rows shifted by s-1
+        for (int set = 0; set < P::kSets; ++set)
 #pragma unroll
-          for (uint32_t p = 0; p < S::BP; ++p)
-            bulk_g2s(sb + (sh * S::BP + p) * kStagePlaneBytes,
-                     in + ((long long)p * g.plane_rows + rowa - kHalo + (sh - 1)) * 8,
-                     kStagePlaneBytes, bar_full + stage * 8);
+          for (int sh = 0; sh < 3; ++sh)  // horizontal tap s: rows shifted by s-1
+#pragma unroll
+            for (uint32_t p = 0; p < S::BP; ++p)
+              bulk_g2s(sb + set * S::b_set + (sh * S::BP + p) * kStagePlaneBytes,
+                       in + ((long long)(set * S::BP + p) * g.plane_rows + rowa - kHalo + (sh - 1)),
+                       kStagePlaneBytes, bar_full + stage * 8);
       }
     }
     __syncwarp();
@@ -410,7 +491,18 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
         for (int r = 0; r < 3; ++r) {  // vertical tap r: start row shifted by (r-1)*PW
           const uint64_t bdesc =
               umma_smem_desc(sb + row_off[r] + ks * 16 * kRowBytes, 128, kStagePlaneBytes);
-          if (elect_one()) umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
+          if constexpr (P::kSets == 2) {
+            const uint64_t adesc_lo = umma_smem_desc(sa + S::a_set + ks * 16 * kRowBytes, 128, S::a_plane);
+            const uint64_t bdesc_lo =
+                umma_smem_desc(sb + S::b_set + row_off[r] + ks * 16 * kRowBytes, 128, kStagePlaneBytes);
+            if (elect_one()) {
+              umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
+              umma_bf16(tmem_row[r], adesc_lo, bdesc, r == 0 ? idesc0 : idesc1, 1);
+              umma_bf16(tmem_row[r], adesc, bdesc_lo, idesc1, 1);  // lo set: taps only, no ones plane
+            }
+          } else {
+            if (elect_one()) umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
+          }
         }
       }
       if (elect_one()) umma_commit(bar_empty + stage * 8);
@@ -469,7 +561,8 @@ conv3x3_wgrad_tc_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloa
 template <int CI, int CO>
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __restrict__ dw,
-                    float* __restrict__ db) {
+                    float* __restrict__ db, const float* __restrict__ bias_part, int nsplit, int nbx,
+                    int HW) {
   // 256 threads = 32 consecutive outputs x 8 partial groups; group pg sums parts pg, pg+8, ...
   constexpr int n0 = 3 * CI + 8, n1 = 3 * CI;
   constexpr int ncols = n0 + 2 * n1;
@@ -501,7 +594,8 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __rest
   if (col < n0) {
     r = 0;
     if (col >= n1) {  // bias block: only its first column is used
-      if (col == n1) db[co] = s;
+      // bias_part: the exact-fp32 sums of the linear backward replace the tensor-core column
+      if (col == n1) db[co] = bias_part ? sum_bias_parts(bias_part, nsplit, nbx, HW, co) : s;
       return;
     }
   } else if (col < n0 + n1) {
@@ -517,28 +611,111 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __rest
 }
 
 // ------------------------------------------------------------------------------------------
+// fp32 master weights w[CO_L][CI_L][3][3] -> the pre-packed B-tile images the split / fp32-plane
+// kernels bulk-copy into shared memory (index maps: layout.cuh):
+//   split : [fwd hi | fwd lo | dgrad hi | dgrad lo], each 9*CI_L*CO_L bf16   (w = hi + lo)
+//   tf32  : [fwd | dgrad], each 9*CI_L*CO_L floats rounded to nearest tf32
+// The fused bucket update (comm.cu, MAP 1) rewrites the split images in place after every step; these
+// kernels are for initialisation, checkpoint load and the non-fused update modes.
+template <int CI_L, int CO_L>
+__global__ void __launch_bounds__(256)
+pack_conv3x3_split_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ packed) {
+  pdl_sync();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int n = CO_L * CI_L * 9;
+  if (idx >= n) return;
+  const int t = idx % 9;
+  const int ci = (idx / 9) % CI_L;
+  const int co = idx / (9 * CI_L);
+  float hi, lo;
+  split_bf16(w[idx], hi, lo);
+  const int f = conv3x3_fwd_tile_index<CI_L, CO_L, 8>(co, ci, t);
+  const int d = conv3x3_dgrad_tile_index<CI_L, CO_L, 8>(co, ci, t);
+  packed[f] = __float2bfloat16_rn(hi);
+  packed[n + f] = __float2bfloat16_rn(lo);
+  packed[2 * n + d] = __float2bfloat16_rn(hi);
+  packed[3 * n + d] = __float2bfloat16_rn(lo);
+}
+
+template <int CI_L, int CO_L>
+__global__ void __launch_bounds__(256)
+pack_conv3x3_tf32_kernel(const float* __restrict__ w, float* __restrict__ fwd, float* __restrict__ dgr) {
+  pdl_sync();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= CO_L * CI_L * 9) return;
+  const int t = idx % 9;
+  const int ci = (idx / 9) % CI_L;
+  const int co = idx / (9 * CI_L);
+  const float v = round_tf32(w[idx]);
+  fwd[conv3x3_fwd_tile_index<CI_L, CO_L, 4>(co, ci, t)] = v;
+  dgr[conv3x3_dgrad_tile_index<CI_L, CO_L, 4>(co, ci, t)] = v;
+}
+
 static unsigned long long* g_prof = nullptr;  // set by ddpb_set_prof_buffer (tuning only)
 
-template <int CI, int CO, int MODE>
-static int launch_conv(const void* in, const float* w, const float* bias, const void* mask,
-                       void* out, const Geom& g, int num_sms, cudaStream_t st) {
-  // dgrad: 3 stages (its ring then exactly holds the fp32 weight staging area) keeps the CTA at
-  // ~111 KB so it can share an SM with a weight-gradient CTA running on another stream.
-  constexpr int STAGES = MODE == 0 ? 4 : 3;
-  using S = ConvSmem<CI, CO, STAGES>;
-  auto kern = conv3x3_tc_kernel<CI, CO, MODE, STAGES>;
-  static bool configured[64] = {};
+template <class KernT>
+static int configure_smem(KernT kern, uint32_t bytes, bool (&configured)[64]) {
   int dev = 0;
   DDPB_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::total));
+    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     configured[dev & 63] = true;
   }
+  return 0;
+}
+
+template <class P, class PO, class PM, int CI, int CO, int MODE>
+static int launch_conv(const void* in, const void* w, const float* bias, const void* mask,
+                       void* out, const Geom& g, int round_out, int num_sms, cudaStream_t st) {
+  // dgrad: 3 stages (bf16: its ring then exactly holds the fp32 weight staging area) keeps the bf16
+  // CTA at ~111 KB so it can share an SM with a weight-gradient CTA running on another stream.
+  constexpr int STAGES = MODE == 0 ? 4 : 3;
+  using S = ConvSmem<P, CI, CO, STAGES>;
+  auto kern = conv3x3_tc_kernel<P, PO, PM, CI, CO, MODE, STAGES>;
+  static bool configured[64] = {};
+  const int rc = configure_smem(kern, S::total, configured);
+  if (rc != 0) return rc;
   const int grid = g.ntiles < num_sms ? g.ntiles : num_sms;
   return static_cast<int>(launch_k(kern, dim3(grid), dim3(kConvThreads), S::total, st,
-                                   static_cast<const __nv_bfloat16*>(in), w, bias,
-                                   static_cast<const __nv_bfloat16*>(mask),
-                                   static_cast<__nv_bfloat16*>(out), g, g_prof));
+                                   static_cast<const uint4*>(in), static_cast<const float*>(w), bias,
+                                   static_cast<const uint4*>(mask), static_cast<uint4*>(out), g,
+                                   round_out, g_prof));
+}
+
+template <class P>
+static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch, int* nparts, int cin,
+                                int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  constexpr int CI = 32, CO = 64, STAGES = 2;
+  using S = WgradSmem<P, CI, CO, STAGES>;
+  auto kern = conv3x3_wgrad_tc_kernel<P, CI, CO, STAGES>;
+  static bool configured[64] = {};
+  const int rc = configure_smem(kern, S::total, configured);
+  if (rc != 0) return rc;
+  const int sms = ddpb_num_sms();
+  const int grid = g.ntiles < sms ? g.ntiles : sms;
+  DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
+                        static_cast<const uint4*>(dout), static_cast<const uint4*>(in), scratch, g,
+                        g_prof));
+  *nparts = grid;
+  return 0;
+}
+
+template <class P>
+static int conv3x3_wgrad_full(const void* dout, const void* in, float* dw, float* db, float* scratch,
+                              int cin, int cout, int batch, int batch_cap, int H, int W, void* stream,
+                              const float* bias_part = nullptr, int nsplit = 0, int nbx = 0) {
+  int grid = 0;
+  const int rc = conv3x3_wgrad_launch<P>(dout, in, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
+  if (rc != 0) return rc;
+  constexpr int CI = 32, CO = 64;
+  const int n = CO * (9 * CI + 8);
+  return static_cast<int>(launch_k(wgrad_reduce_kernel<CI, CO>, dim3((n + 31) / 32), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), static_cast<const float*>(scratch),
+                                   grid, dw, db, bias_part, nsplit, nbx, H * W));
 }
 
 }  // namespace ddpb
@@ -551,13 +728,15 @@ extern "C" {
 // buf[block*16 + slot] (needs >= gridDim*16 entries).  NULL (default) disables it.
 void ddpb_set_prof_buffer(void* buf) { g_prof = static_cast<unsigned long long*>(buf); }
 
+// ---- bf16 planes (fast mode): fp32 master weights, converted per CTA
 int ddpb_conv3x3_fwd(const void* in, const float* w, const float* bias, void* out, int cin,
                      int cout, int batch, int batch_cap, int H, int W, void* stream) {
   const Geom g = make_geom(batch, batch_cap, H, W);
   const int sms = ddpb_num_sms();
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
-  if (cin == 32 && cout == 64) return launch_conv<32, 64, 0>(in, w, bias, nullptr, out, g, sms, st);
+  if (cin == 32 && cout == 64)
+    return launch_conv<Bf16Planes, Bf16Planes, Bf16Planes, 32, 64, 0>(in, w, bias, nullptr, out, g, 0, sms, st);
   return DDPB_ERR_SHAPE;
 }
 
@@ -569,7 +748,8 @@ int ddpb_conv3x3_dgrad(const void* dout, const float* w, const void* mask, void*
   const int sms = ddpb_num_sms();
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
-  if (cin == 32 && cout == 64) return launch_conv<64, 32, 1>(dout, w, nullptr, mask, din, g, sms, st);
+  if (cin == 32 && cout == 64)
+    return launch_conv<Bf16Planes, Bf16Planes, Bf16Planes, 64, 32, 1>(dout, w, nullptr, mask, din, g, 0, sms, st);
   return DDPB_ERR_SHAPE;
 }
 
@@ -577,41 +757,10 @@ size_t ddpb_conv3x3_wgrad_scratch_bytes(int cin, int cout) {
   return static_cast<size_t>(ddpb_num_sms()) * cout * (9 * cin + 8) * sizeof(float);
 }
 
-static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch, int* nparts, int cin,
-                               int cout, int batch, int batch_cap, int H, int W, void* stream) {
-  const Geom g = make_geom(batch, batch_cap, H, W);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
-  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
-  constexpr int CI = 32, CO = 64, STAGES = 2;
-  using S = WgradSmem<CI, CO, STAGES>;
-  auto kern = conv3x3_wgrad_tc_kernel<CI, CO, STAGES>;
-  static bool configured[64] = {};
-  int dev = 0;
-  DDPB_CUDA_OK(cudaGetDevice(&dev));
-  if (!configured[dev & 63]) {
-    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::total));
-    configured[dev & 63] = true;
-  }
-  const int sms = ddpb_num_sms();
-  const int grid = g.ntiles < sms ? g.ntiles : sms;
-  DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
-                        static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(in),
-                        scratch, g, g_prof));
-  *nparts = grid;
-  return 0;
-}
-
 int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, float* scratch,
                        int cin, int cout, int batch, int batch_cap, int H, int W, void* stream) {
-  int grid = 0;
-  const int rc = conv3x3_wgrad_launch(dout, in, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
-  if (rc != 0) return rc;
-  constexpr int CI = 32, CO = 64;
-  const int n = CO * (9 * CI + 8);
-  return static_cast<int>(launch_k(wgrad_reduce_kernel<CI, CO>, dim3((n + 31) / 32), dim3(256), 0,
-                                   static_cast<cudaStream_t>(stream), static_cast<const float*>(scratch),
-                                   grid, dw, db));
+  return conv3x3_wgrad_full<Bf16Planes>(dout, in, dw, db, scratch, cin, cout, batch, batch_cap, H, W,
+                                        stream);
 }
 
 // Partials only: scratch[nparts][cout * (9*cin + 8)] accumulator images (one per CTA) and their count
@@ -620,7 +769,99 @@ int ddpb_conv3x3_wgrad(const void* dout, const void* in, float* dw, float* db, f
 int ddpb_conv3x3_wgrad_partials(const void* dout, const void* in, float* scratch, int* nparts_out,
                                 int cin, int cout, int batch, int batch_cap, int H, int W,
                                 void* stream) {
-  return conv3x3_wgrad_launch(dout, in, scratch, nparts_out, cin, cout, batch, batch_cap, H, W, stream);
+  return conv3x3_wgrad_launch<Bf16Planes>(dout, in, scratch, nparts_out, cin, cout, batch, batch_cap, H,
+                                          W, stream);
+}
+
+// ---- split planes (x = hi + lo, bf16x3): the reference-precision mode.
+// packed: [fwd hi | fwd lo | dgrad hi | dgrad lo] bf16 tile images, ddpb_conv3x3_pack_split_bytes bytes.
+size_t ddpb_conv3x3_pack_split_bytes(int cin, int cout) {
+  return static_cast<size_t>(4) * 9 * cin * cout * sizeof(__nv_bfloat16);
+}
+int ddpb_conv3x3_pack_split(const float* w, void* packed, int cin, int cout, void* stream) {
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  const int n = 9 * cin * cout;
+  return static_cast<int>(launch_k(pack_conv3x3_split_kernel<32, 64>, dim3((n + 255) / 256), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), w,
+                                   static_cast<__nv_bfloat16*>(packed)));
+}
+// in: split planes (cin channels); out: fp32 planes when out_f32 != 0 (the consumer is the fp32
+// linear layer), else split planes.
+int ddpb_conv3x3_fwd_split(const void* in, const void* packed, const float* bias, void* out, int cin,
+                           int cout, int batch, int batch_cap, int H, int W, int out_f32, void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  const int sms = ddpb_num_sms();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (out_f32)
+    return launch_conv<SplitPlanes, F32Planes, SplitPlanes, 32, 64, 0>(in, packed, bias, nullptr, out, g, 0, sms, st);
+  return launch_conv<SplitPlanes, SplitPlanes, SplitPlanes, 32, 64, 0>(in, packed, bias, nullptr, out, g, 0, sms, st);
+}
+// dout and mask (the forward activation that fed the conv) are split planes; din = unrounded fp32
+// planes when out_f32 != 0 (its consumer is the exact-fp32 conv1 weight gradient), else split planes.
+int ddpb_conv3x3_dgrad_split(const void* dout, const void* packed, const void* mask, void* din, int cin,
+                             int cout, int batch, int batch_cap, int H, int W, int out_f32,
+                             void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  const __nv_bfloat16* dg = static_cast<const __nv_bfloat16*>(packed) + 2 * 9 * cin * cout;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (out_f32)
+    return launch_conv<SplitPlanes, F32Planes, SplitPlanes, 64, 32, 1>(dout, dg, nullptr, mask, din, g, 0,
+                                                                      ddpb_num_sms(), st);
+  return launch_conv<SplitPlanes, SplitPlanes, SplitPlanes, 64, 32, 1>(dout, dg, nullptr, mask, din, g, 0,
+                                                                      ddpb_num_sms(), st);
+}
+// bias_part (optional): exact-fp32 bias-gradient parts from ddpb_linear_bwd_f32 with their extents;
+// when given, db is their fixed-order sum instead of the tensor-core ones-column (16-bit operands).
+int ddpb_conv3x3_wgrad_split(const void* dout, const void* in, float* dw, float* db, float* scratch,
+                             const float* bias_part, int nsplit, int nbx, int cin, int cout, int batch,
+                             int batch_cap, int H, int W, void* stream) {
+  return conv3x3_wgrad_full<SplitPlanes>(dout, in, dw, db, scratch, cin, cout, batch, batch_cap, H, W,
+                                         stream, bias_part, nsplit, nbx);
+}
+int ddpb_conv3x3_wgrad_split_partials(const void* dout, const void* in, float* scratch, int* nparts_out,
+                                      int cin, int cout, int batch, int batch_cap, int H, int W,
+                                      void* stream) {
+  return conv3x3_wgrad_launch<SplitPlanes>(dout, in, scratch, nparts_out, cin, cout, batch, batch_cap, H,
+                                           W, stream);
+}
+
+// ---- fp32 planes, tf32 tensor-core operands: forward and data gradient only (K-major operands).
+size_t ddpb_conv3x3_pack_tf32_bytes(int cin, int cout) {
+  return static_cast<size_t>(2) * 9 * cin * cout * sizeof(float);
+}
+// packed: [fwd image | dgrad image], each 9*cin*cout floats (see pack_conv3x3_tf32_kernel).
+int ddpb_conv3x3_pack_tf32(const float* w, void* packed, int cin, int cout, void* stream) {
+  if (!(cin == 32 && cout == 64)) return DDPB_ERR_SHAPE;
+  float* fwd = static_cast<float*>(packed);
+  float* dgr = fwd + 9 * cin * cout;
+  const int n = 9 * cin * cout;
+  return static_cast<int>(launch_k(pack_conv3x3_tf32_kernel<32, 64>, dim3((n + 255) / 256), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), w, fwd, dgr));
+}
+int ddpb_conv3x3_fwd_tf32(const void* in, const void* packed, const float* bias, void* out, int cin,
+                          int cout, int batch, int batch_cap, int H, int W, int round_out,
+                          void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (cin == 32 && cout == 64)
+    return launch_conv<F32Planes, F32Planes, F32Planes, 32, 64, 0>(
+        in, packed, bias, nullptr, out, g, round_out, ddpb_num_sms(), static_cast<cudaStream_t>(stream));
+  return DDPB_ERR_SHAPE;
+}
+int ddpb_conv3x3_dgrad_tf32(const void* dout, const void* packed, const void* mask, void* din, int cin,
+                            int cout, int batch, int batch_cap, int H, int W, int round_out,
+                            void* stream) {
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
+  if (cin == 32 && cout == 64)
+    return launch_conv<F32Planes, F32Planes, F32Planes, 64, 32, 1>(
+        dout, static_cast<const float*>(packed) + 9 * cin * cout, nullptr, mask, din, g, round_out,
+        ddpb_num_sms(), static_cast<cudaStream_t>(stream));
+  return DDPB_ERR_SHAPE;
 }
 
 }  // extern "C"

@@ -19,6 +19,41 @@
 
 namespace ddpb {
 
+// Three storage formats share the layout; a plane row is 16 bytes in all of them:
+//   Bf16Planes  : 8 bf16 channels per row; kind::f16 MMAs (K = 16 = two planes).        Fast mode.
+//   SplitPlanes : every value as TWO bf16 terms, x = hi + lo (hi = nearest bf16, lo = the
+//                 remainder rounded to bf16: a 16-bit significand, 4 bytes per value like fp32):
+//                 C/8 "hi" planes followed by C/8 "lo" planes.  A GEMM over split operands issues
+//                 three kind::f16 MMAs per K step (hi.hi + lo.hi + hi.lo, fp32 accumulation; the
+//                 dropped lo.lo term is < 2^-16 relative) — "bf16x3".  This is how the
+//                 reference-precision mode feeds the tensor cores: it carries more operand bits than
+//                 the TF32 (11-bit) convolutions cuDNN runs for the reference (model.py:8-16), and,
+//                 unlike tf32, both operand majors exist for it in the no-swizzle layout this file
+//                 relies on (a tf32 MN-major operand — the weight gradient's view of a plane — is
+//                 only defined for the 128B_BASE32B swizzled layout: tools/umma_probe.cu,
+//                 profiles/umma_probe_tf32_mn.txt).
+//   F32Planes   : 4 fp32 channels per row; kind::tf32 MMAs (K = 8 = two planes), K-major operands
+//                 only.  Used for tensors the fp32 linear layer reads (act2) and by the tf32
+//                 forward / data-gradient building blocks.
+struct Bf16Planes {
+  static constexpr int kCh = 8;    // channels per 16-byte row
+  static constexpr int kMmaK = 16;
+  static constexpr int kSets = 1;  // plane sets per tensor (2 = hi + lo)
+  static constexpr bool kTf32 = false;
+};
+struct SplitPlanes {
+  static constexpr int kCh = 8;
+  static constexpr int kMmaK = 16;
+  static constexpr int kSets = 2;
+  static constexpr bool kTf32 = false;
+};
+struct F32Planes {
+  static constexpr int kCh = 4;
+  static constexpr int kMmaK = 8;
+  static constexpr int kSets = 1;
+  static constexpr bool kTf32 = true;
+};
+
 constexpr int kTileM = 128;  // pixels (rows) per GEMM tile
 constexpr int kHalo = 32;    // rows fetched before/after a tile; >= (W+2)+1, i.e. W <= 29
 constexpr int kGuard = 64;   // zero rows before the first / after the last tile
@@ -77,6 +112,41 @@ __device__ __forceinline__ bool decode_row(const Geom& g, int rel, int& img, int
   h = hp - 1;
   w = wp - 1;
   return img < g.batch && hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W;
+}
+
+// Exact-fp32 bias gradient of the convolution that precedes the linear layer.  The fp32 linear backward
+// (simt_ops.cu) sums, per block of kBiasBlock feature vectors (4 channels of one pixel each) and per
+// image split, the masked dX values it produces while they are still fp32 registers:
+//   bias_part[(split * nbx + bx) * 8 + slot * 4 + e],  slot = (4-channel group of the vector) -
+//   (group of the block's first vector) in {0, 1},  e = channel within the group.
+// This sums the parts of channel ch in a fixed order.
+constexpr int kBiasBlock = 256;
+__device__ __forceinline__ float sum_bias_parts(const float* __restrict__ bp, int nsplit, int nbx, int HW,
+                                                int ch) {
+  const int c4 = ch >> 2, e = ch & 3;
+  const int b_lo = (c4 * HW) / kBiasBlock;
+  int b_hi = ((c4 + 1) * HW - 1) / kBiasBlock;
+  if (b_hi >= nbx) b_hi = nbx - 1;
+  float s = 0.f;
+  for (int sp = 0; sp < nsplit; ++sp)
+    for (int bx = b_lo; bx <= b_hi; ++bx) {
+      const int slot = c4 - (bx * kBiasBlock) / HW;
+      if (slot == 0 || slot == 1) s += bp[((long long)sp * nbx + bx) * 8 + slot * 4 + e];
+    }
+  return s;
+}
+
+// Element index of layer weight w[co][ci][tap] inside the pre-packed B-tile images of a 3x3
+// convolution with CI_L input / CO_L output channels; E = elements per 16-byte row (4 tf32 / 8 bf16):
+//   forward image   [tap][ci/E][co][ci%E]
+//   data-grad image [8-tap][co/E][ci][co%E]   (GEMM K = layer output channels, taps mirrored)
+template <int CI_L, int CO_L, int E>
+__host__ __device__ constexpr int conv3x3_fwd_tile_index(int co, int ci, int tap) {
+  return ((tap * (CI_L / E) + ci / E) * CO_L + co) * E + ci % E;
+}
+template <int CI_L, int CO_L, int E>
+__host__ __device__ constexpr int conv3x3_dgrad_tile_index(int co, int ci, int tap) {
+  return (((8 - tap) * (CO_L / E) + co / E) * CI_L + ci) * E + co % E;
 }
 
 }  // namespace ddpb

@@ -215,9 +215,13 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
          (static_cast<uint32_t>(M >> 4) << 24);
 }
 
-// kind::tf32: a_format = b_format = 2 (TF32), fp32 D, both operands K-major.
-__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
-  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(N >> 3) << 17) |
+// kind::tf32: a_format = b_format = 2 (TF32), fp32 D.  Same major bits as above; an MN-major tf32
+// core matrix is 8 K-rows x 16 B (4 values along M/N) and one MMA (K = 8) spans exactly one of them
+// along K, so LBO is unused there.
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N, int a_mn_major = 0,
+                                                       int b_mn_major = 0) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
+         (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(N >> 3) << 17) |
          (static_cast<uint32_t>(M >> 4) << 24);
 }
 
@@ -225,6 +229,20 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+// fp32 -> nearest tf32 (10 mantissa bits, ties away from zero), returned as the fp32 bit pattern
+// with the low 13 bits clear.  The tensor cores ignore those bits (they truncate), so operands that
+// were rounded here enter kind::tf32 MMAs exactly — what cuDNN does with the reference's fp32
+// convolution inputs.
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+// x = hi + lo with both terms bf16 (round to nearest): a 16-bit significand.
+__device__ __forceinline__ void split_bf16(float x, float& hi, float& lo) {
+  hi = __bfloat162float(__float2bfloat16_rn(x));
+  lo = x - hi;  // exact in fp32; rounded to bf16 when packed
 }
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

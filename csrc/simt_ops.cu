@@ -170,9 +170,13 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
 // gridDim.y = C1/8 (channel chunk); block (bx, chunk) accumulates a contiguous range of images and
 // writes one partial per blockIdx.x: partial[bx][C1*CIN0*9 + C1] (weights then biases, canonical
 // order); reduce_partials_kernel sums them in a fixed order.
-template <int CIN0, int C1>
+// F32IN: dact is fp32 planes (4 channels per row; the chunk's 8 channels are planes 2*chunk and
+// 2*chunk+1) and the whole computation is exact fp32 FMA — the reference-precision mode uses this
+// for the Cin = 1 layer, which cuDNN also runs in plain fp32 (profiles/precision.md); otherwise bf16
+// planes.
+template <int CIN0, int C1, bool F32IN>
 __global__ void __launch_bounds__(256)
-conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restrict__ x,
+conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
                    float* __restrict__ partial, Geom g) {
   constexpr int NW = CIN0 * 9;
   constexpr int NV = 8 * NW + 8;
@@ -187,7 +191,9 @@ conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restri
   const int ipb = (g.batch + gridDim.x - 1) / gridDim.x;
   const int lo = blockIdx.x * ipb;
   const int hi = min(g.batch, lo + ipb);
-  const __nv_bfloat16* plane = dact + ((long long)chunk * g.plane_rows + kGuard) * 8;
+  // 16-byte rows: bf16 -> plane `chunk`; fp32 -> planes 2*chunk (channels 0-3) and 2*chunk+1 (4-7)
+  const uint4* plane = static_cast<const uint4*>(dact_v) +
+                       (long long)(F32IN ? 2 * chunk : chunk) * g.plane_rows + kGuard;
   for (int img0 = lo; img0 < hi; img0 += kConv1Group) {
     const int ng = min(kConv1Group, hi - img0);
     const int nidx = ng * g.PHW;
@@ -197,12 +203,13 @@ conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restri
     // border rows of dact are zero, so every row of the group can be accumulated unconditionally;
     // the window read stays inside the image's padded tile for interior rows only -> test those.
     for (int base = threadIdx.x; base < nidx; base += PF * blockDim.x) {
-      uint4 dv[PF];
+      uint4 dv[PF], dv2[PF];
 #pragma unroll
       for (int u = 0; u < PF; ++u) {
         const int idx = base + u * blockDim.x;
-        dv[u] = idx < nidx ? *reinterpret_cast<const uint4*>(plane + ((long long)img0 * g.PHW + idx) * 8)
-                           : make_uint4(0, 0, 0, 0);
+        dv[u] = idx < nidx ? plane[(long long)img0 * g.PHW + idx] : make_uint4(0, 0, 0, 0);
+        if (F32IN)
+          dv2[u] = idx < nidx ? plane[g.plane_rows + (long long)img0 * g.PHW + idx] : make_uint4(0, 0, 0, 0);
       }
 #pragma unroll
       for (int u = 0; u < PF; ++u) {
@@ -213,7 +220,14 @@ conv1_wgrad_kernel(const __nv_bfloat16* __restrict__ dact, const float* __restri
         const int hp = pos / g.PW, wp = pos - hp * g.PW;
         if (!(hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W)) continue;
         float d[8];
-        unpack8(dv[u], d);
+        if (F32IN) {
+          d[0] = __uint_as_float(dv[u].x); d[1] = __uint_as_float(dv[u].y);
+          d[2] = __uint_as_float(dv[u].z); d[3] = __uint_as_float(dv[u].w);
+          d[4] = __uint_as_float(dv2[u].x); d[5] = __uint_as_float(dv2[u].y);
+          d[6] = __uint_as_float(dv2[u].z); d[7] = __uint_as_float(dv2[u].w);
+        } else {
+          unpack8(dv[u], d);
+        }
         const float* xi = xs + li * CIN0 * g.PHW;
         float in[NW];
 #pragma unroll
@@ -606,7 +620,7 @@ linear_bwd_kernel(const __nv_bfloat16* __restrict__ act, const float* __restrict
 // Zero the rows of every plane between the end of the batch and the end of its last tile, so
 // the weight-gradient GEMM (which reduces over whole tiles) never sees stale rows after a
 // short tail batch (reference data.py:21-25 uses drop_last=False).
-__global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int nplanes, Geom g) {
+__global__ void zero_tail_rows_kernel(uint4* __restrict__ planes, int nplanes, Geom g) {
   pdl_sync();
   const int first = g.batch * g.PHW;
   const int nrows = g.ntiles * kTileM - first;
@@ -615,8 +629,185 @@ __global__ void zero_tail_rows_kernel(__nv_bfloat16* __restrict__ planes, int np
        idx += (long long)gridDim.x * blockDim.x) {
     const int p = static_cast<int>(idx / nrows);
     const int r = static_cast<int>(idx - (long long)p * nrows);
-    *reinterpret_cast<uint4*>(planes + ((long long)p * g.plane_rows + kGuard + first + r) * 8) =
-        make_uint4(0, 0, 0, 0);
+    planes[(long long)p * g.plane_rows + kGuard + first + r] = make_uint4(0, 0, 0, 0);
+  }
+}
+
+// ------------------------------------------------------------------ linear layer, fp32 planes
+// The reference's linear layer is plain fp32 (cuBLAS addmm/mm with TF32 off, reference
+// model.py:16,19): in the precision-parity mode it therefore runs as fp32 FMAs on the CUDA cores,
+// reading the fp32 planes (4 channels per 16-byte row) the tf32 convolutions write.  N = 10 makes it
+// a GEMV-shaped, bandwidth-bound op; the products are exact fp32 and every sum has a fixed order.
+//
+// forward: same decomposition as linear_fwd_kernel (a thread owns one 4-channel vector of a pixel
+// for 8 images), partial[s][img][j].
+template <int NOUT, int IMG>
+__global__ void __launch_bounds__(256, 1)
+linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ W,
+                      float* __restrict__ partial, Geom g, int C, int vec_per_slice) {
+  pdl_sync();
+  __shared__ float red[8][IMG * NOUT];
+  const int HW = g.H * g.W;
+  const int nvec = (C / 4) * HW;
+  const long long K = (long long)C * HW;
+  const int img0 = blockIdx.y * IMG;
+  const int v_begin = blockIdx.x * vec_per_slice;
+  const int v_end = min(nvec, v_begin + vec_per_slice);
+  static_assert(IMG * NOUT == 80, "warp_reduce80 expects 80 accumulators");
+  float acc[IMG * NOUT];
+#pragma unroll
+  for (int i = 0; i < IMG * NOUT; ++i) acc[i] = 0.f;
+
+  for (int v = v_begin + threadIdx.x; v < v_end; v += blockDim.x) {
+    const int chunk = v / HW;
+    const int pix = v - chunk * HW;
+    const int h = pix / g.W, wc = pix - h * g.W;
+    const long long rowi = (long long)chunk * g.plane_rows + kGuard + (long long)(h + 1) * g.PW + (wc + 1);
+    float4 av[IMG];
+#pragma unroll
+    for (int i = 0; i < IMG; ++i) {
+      const int img = img0 + i;
+      av[i] = img < g.batch ? act[rowi + (long long)img * g.PHW] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float wv[NOUT][4];
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) wv[j][c] = W[j * K + (long long)(chunk * 4 + c) * HW + pix];
+#pragma unroll
+    for (int i = 0; i < IMG; ++i) {
+      const float a[4] = {av[i].x, av[i].y, av[i].z, av[i].w};
+#pragma unroll
+      for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[i * NOUT + j] = fmaf(wv[j][c], a[c], acc[i * NOUT + j]);
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  warp_reduce80(acc, lane);
+  if ((lane & 1) == 0) {
+    const int base = warp_reduce80_base(lane);
+#pragma unroll
+    for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < IMG * NOUT; t += blockDim.x) {
+    const int i = t / NOUT, j = t - i * NOUT;
+    const int img = img0 + i;
+    if (img >= g.batch) continue;
+    float s = 0.f;
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][t];
+    partial[((long long)blockIdx.x * g.batch + img) * NOUT + j] = s;
+  }
+}
+
+// backward: dact[img][k] = relu'(act[img][k]) * sum_j dlogits[img][j] W[j][k]; dW[j][k] =
+// sum_img dlogits[img][j] act[img][k] through per-image-split partials.  A thread owns one 4-channel
+// vector of one pixel.  dact is what the conv2 gradient GEMMs consume: SPLIT_OUT writes it as split
+// planes (hi + lo bf16, half a 16-byte row per thread and set), otherwise as fp32 planes rounded to
+// tf32.
+template <int NOUT, bool SPLIT_OUT>
+__global__ void __launch_bounds__(256, 2)
+linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ dlogits,
+                      const float* __restrict__ W, float4* __restrict__ dact,
+                      float* __restrict__ dw_partial, float* __restrict__ bias_part, Geom g, int C,
+                      int imgs_per_split) {
+  pdl_sync();
+  extern __shared__ float sdl[];  // [imgs_per_split][NOUT]
+  __shared__ float bred[8][8];
+  static_assert(kBiasBlock == 256, "one bias block per thread block");
+  constexpr int PF = 8;           // image vectors kept in flight per thread
+  const int HW = g.H * g.W;
+  const int nvec = (C / 4) * HW;
+  const long long K = (long long)C * HW;
+  const int img_begin = blockIdx.y * imgs_per_split;
+  const int img_end = min(g.batch, img_begin + imgs_per_split);
+  for (int t = threadIdx.x; t < (img_end - img_begin) * NOUT; t += blockDim.x)
+    sdl[t] = dlogits[(long long)img_begin * NOUT + t];
+  __syncthreads();
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = v < nvec;
+  const int vv = active ? v : nvec - 1;
+  const int chunk = vv / HW;
+  const int pix = vv - chunk * HW;
+  const int h = pix / g.W, wc = pix - h * g.W;
+  float wv[NOUT][4], dwv[NOUT][4];
+#pragma unroll
+  for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      wv[j][c] = W[j * K + (long long)(chunk * 4 + c) * HW + pix];
+      dwv[j][c] = 0.f;
+    }
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};  // sum over this split's images of the masked dX (exact fp32)
+  const long long base = (long long)chunk * g.plane_rows + kGuard + (long long)(h + 1) * g.PW + (wc + 1);
+  if (active) {
+    for (int i0 = img_begin; i0 < img_end; i0 += PF) {
+      float4 av[PF];
+#pragma unroll
+      for (int u = 0; u < PF; ++u)
+        av[u] = (i0 + u < img_end) ? act[base + (long long)(i0 + u) * g.PHW] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < PF; ++u) {
+        if (i0 + u >= img_end) break;
+        const float a[4] = {av[u].x, av[u].y, av[u].z, av[u].w};
+        float gr[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* dl = sdl + (i0 + u - img_begin) * NOUT;
+#pragma unroll
+        for (int j = 0; j < NOUT; ++j) {
+          const float d = dl[j];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            gr[c] = fmaf(d, wv[j][c], gr[c]);
+            dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          gr[c] = a[c] > 0.f ? gr[c] : 0.f;
+          bsum[c] += gr[c];
+        }
+        if constexpr (SPLIT_OUT) {
+          float hi[4], lo[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) split_bf16(gr[c], hi[c], lo[c]);
+          // bf16 plane chunk/2, row = the same pixel row, 8-byte half (chunk & 1); lo set C/8 planes on
+          uint2* d2 = reinterpret_cast<uint2*>(dact);
+          const long long r16 = (long long)(chunk >> 1) * g.plane_rows + kGuard +
+                                (long long)(i0 + u) * g.PHW + (long long)(h + 1) * g.PW + (wc + 1);
+          d2[r16 * 2 + (chunk & 1)] = make_uint2(pack_bf16x2(hi[0], hi[1]), pack_bf16x2(hi[2], hi[3]));
+          d2[(r16 + (long long)(C / 8) * g.plane_rows) * 2 + (chunk & 1)] =
+              make_uint2(pack_bf16x2(lo[0], lo[1]), pack_bf16x2(lo[2], lo[3]));
+        } else {
+          dact[base + (long long)(i0 + u) * g.PHW] =
+              make_float4(round_tf32(gr[0]), round_tf32(gr[1]), round_tf32(gr[2]), round_tf32(gr[3]));
+        }
+      }
+    }
+    float* dst = dw_partial + (long long)blockIdx.y * NOUT * K;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) dst[j * K + (long long)(chunk * 4 + c) * HW + pix] = dwv[j][c];
+  }
+  if (bias_part == nullptr) return;
+  // fixed-shape reduction of the block's bias sums: a block spans at most two 4-channel groups
+  const int slot = chunk - (blockIdx.x * kBiasBlock) / HW;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int sl = 0; sl < 2; ++sl)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const float t = warp_sum((active && slot == sl) ? bsum[c] : 0.f);
+      if (lane == 0) bred[warp][sl * 4 + c] = t;
+    }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    float t = 0.f;
+#pragma unroll
+    for (int wdx = 0; wdx < 8; ++wdx) t += bred[wdx][threadIdx.x];
+    bias_part[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 8 + threadIdx.x] = t;
   }
 }
 
@@ -707,13 +898,49 @@ int ddpb_conv1_wgrad(const void* dact, const float* x, float* dw_db, float* scra
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int bx = conv1_wgrad_blocks(batch, H, W);
-  conv1_wgrad_kernel<1, 32><<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
-      static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
+  conv1_wgrad_kernel<1, 32, false><<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
+      dact, x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = (long long)cout * cin * 9 + cout;
   reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, bx, n,
                                                                                     dw_db);
   return static_cast<int>(cudaGetLastError());
+}
+
+int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
+
+// ---- exact-fp32 conv1 weight gradient from fp32 planes (reference-precision mode).
+// Partials: scratch[nparts][cout*cin*9 + cout] (same layout as the tensor-core version, so the fused
+// reduce + all-reduce + SGD kernel consumes them unchanged); scratch size:
+// ddpb_conv1_wgrad_f32_scratch_bytes.
+static int conv1_wgrad_f32_blocks(int batch) {
+  // one block per image up to two per SM-quarter: each block ends in an 80-value reduction whose
+  // partial is re-read by the reduce, so more blocks than ~2 waves only add reduction work
+  int bx = batch < 74 ? batch : 74;
+  return bx < 1 ? 1 : bx;
+}
+size_t ddpb_conv1_wgrad_f32_scratch_bytes(int cin, int cout) {
+  return static_cast<size_t>(74) * (cout * cin * 9 + cout) * sizeof(float);
+}
+int ddpb_conv1_wgrad_f32_partials(const void* dact, const float* x, float* scratch, int* nparts_out,
+                                  int cin, int cout, int batch, int batch_cap, int H, int W,
+                                  void* stream) {
+  if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int bx = conv1_wgrad_f32_blocks(batch);
+  DDPB_CUDA_OK(launch_k(conv1_wgrad_kernel<1, 32, true>, dim3(bx, cout / 8), dim3(256),
+                        (size_t)kConv1Group * cin * g.PHW * sizeof(float),
+                        static_cast<cudaStream_t>(stream), dact, x, scratch, g));
+  *nparts_out = bx;
+  return 0;
+}
+int ddpb_conv1_wgrad_f32(const void* dact, const float* x, float* dw_db, float* scratch, int cin,
+                         int cout, int batch, int batch_cap, int H, int W, void* stream) {
+  int bx = 0;
+  const int rc = ddpb_conv1_wgrad_f32_partials(dact, x, scratch, &bx, cin, cout, batch, batch_cap, H, W,
+                                               stream);
+  if (rc != 0) return rc;
+  return ddpb_reduce_partials(scratch, bx, (long long)cout * cin * 9 + cout, dw_db, stream);
 }
 
 // ---- linear layer launch geometry (shared by scratch-size queries and launches)
@@ -808,11 +1035,82 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
   const int splits = (batch + ips - 1) / ips;
   if (g.ntiles * kTileM > batch * g.PHW) {
     DDPB_CUDA_OK(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0, st,
-                          static_cast<__nv_bfloat16*>(dact), C / 8, g));
+                          static_cast<uint4*>(dact), C / 8, g));
   }
   DDPB_CUDA_OK(launch_k(linear_bwd_kernel<10>, dim3((nvec + 255) / 256, splits), dim3(256),
                         ips * 10 * sizeof(float), st, static_cast<const __nv_bfloat16*>(act), dlogits,
                         Wt, static_cast<__nv_bfloat16*>(dact), scratch, g, C, ips));
+  return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
+}
+
+// ---- fp32-plane (precision-parity) linear layer.  Scratch sizes: ddpb_linear_fwd_f32_scratch_bytes /
+// ddpb_linear_bwd_scratch_bytes (the partial layout of the backward is the same as the bf16 one).
+static void linear_fwd_f32_geom(int batch, int nvec, int& S, int& per, int& groups) {
+  constexpr int IMG = 8;
+  groups = (batch + IMG - 1) / IMG;
+  const int want = ddpb_num_sms() / groups;  // one CTA per SM (~200 registers), one wave
+  const int maxS = (nvec + 255) / 256;
+  S = want < 1 ? 1 : (want > maxS ? maxS : want);
+  per = ((nvec + S - 1) / S + 255) / 256 * 256;
+  S = (nvec + per - 1) / per;
+}
+size_t ddpb_linear_fwd_f32_scratch_bytes(int nout, int C, int batch_cap, int H, int W) {
+  const int nvec = (C / 4) * H * W;
+  const int maxS = (nvec + 255) / 256;
+  return static_cast<size_t>(maxS) * batch_cap * nout * sizeof(float);
+}
+int ddpb_linear_fwd_f32(const void* act, const float* Wt, float* partial, int* S_out, int nout, int C,
+                        int batch, int batch_cap, int H, int W, void* stream) {
+  if (nout != 10 || (C % 4) != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int nvec = (C / 4) * H * W;
+  int S, per, groups;
+  linear_fwd_f32_geom(batch, nvec, S, per, groups);
+  if (S_out) *S_out = S;
+  return static_cast<int>(launch_k(linear_fwd_f32_kernel<10, 8>, dim3(S, groups), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), static_cast<const float4*>(act),
+                                   Wt, partial, g, C, per));
+}
+// act: fp32 planes.  dact: split planes (split_out != 0: 2*C/8 bf16 planes) or fp32 planes rounded
+// to tf32 (C/4 planes).  bias_part (optional, ddpb_linear_bwd_f32_bias_part_bytes bytes): receives the
+// exact-fp32 partial sums of dact per channel (layout.cuh: sum_bias_parts) — the bias gradient of the
+// convolution that produced act; *nsplit_out / *nbx_out (host) receive its two extents.
+size_t ddpb_linear_bwd_f32_bias_part_bytes(int C, int batch_cap, int H, int W) {
+  const int nvec = (C / 4) * H * W;
+  size_t worst = 0;
+  const int cands[3] = {64 < batch_cap ? 64 : batch_cap, 512 < batch_cap ? 512 : batch_cap, batch_cap};
+  for (int i = 0; i < 3; ++i) {
+    const int ips = linear_bwd_imgs_per_split(cands[i]);
+    const size_t splits = (cands[i] + ips - 1) / ips;
+    if (splits > worst) worst = splits;
+  }
+  return worst * ((nvec + kBiasBlock - 1) / kBiasBlock) * 8 * sizeof(float);
+}
+int ddpb_linear_bwd_f32(const void* act, const float* dlogits, const float* Wt, void* dact, float* dW,
+                        float* scratch, int nout, int C, int batch, int batch_cap, int H, int W,
+                        int split_out, float* bias_part, int* nsplit_out, int* nbx_out, void* stream) {
+  if (nout != 10 || (C % 8) != 0) return DDPB_ERR_SHAPE;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nvec = (C / 4) * H * W;
+  const int ips = linear_bwd_imgs_per_split(batch);
+  const int splits = (batch + ips - 1) / ips;
+  const int nbx = (nvec + kBiasBlock - 1) / kBiasBlock;
+  if (nsplit_out) *nsplit_out = splits;
+  if (nbx_out) *nbx_out = nbx;
+  if (g.ntiles * kTileM > batch * g.PHW) {
+    DDPB_CUDA_OK(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0, st, static_cast<uint4*>(dact),
+                          C / 4, g));  // C/4 planes in either format (split: hi + lo sets of C/8)
+  }
+  if (split_out) {
+    DDPB_CUDA_OK(launch_k(linear_bwd_f32_kernel<10, true>, dim3(nbx, splits), dim3(256),
+                          ips * 10 * sizeof(float), st, static_cast<const float4*>(act), dlogits, Wt,
+                          static_cast<float4*>(dact), scratch, bias_part, g, C, ips));
+  } else {
+    DDPB_CUDA_OK(launch_k(linear_bwd_f32_kernel<10, false>, dim3(nbx, splits), dim3(256),
+                          ips * 10 * sizeof(float), st, static_cast<const float4*>(act), dlogits, Wt,
+                          static_cast<float4*>(dact), scratch, bias_part, g, C, ips));
+  }
   return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
 }
 
@@ -823,7 +1121,7 @@ int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int
   if (g.ntiles * kTileM <= batch * g.PHW) return 0;
   return static_cast<int>(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0,
                                    static_cast<cudaStream_t>(stream),
-                                   static_cast<__nv_bfloat16*>(planes), nplanes, g));
+                                   static_cast<uint4*>(planes), nplanes, g));
 }
 
 // out[i] = sum_p part[p*n + i] in a fixed order (shared by the split-K style kernels).
@@ -925,9 +1223,9 @@ extern "C" int ddpb_conv1_wgrad_noalloc(const void* dact, const float* x, float*
 
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout>
+  conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout, false>
       <<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
-          static_cast<const __nv_bfloat16*>(dact), x, scratch, g);
+          dact, x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = kNoAllocFloatsPerBlock;
   reduce_partials_kernel<<<static_cast<int>((n / 4 + 255) / 256 + 1), 256, 0, st>>>(scratch, bx, n,

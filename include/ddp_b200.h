@@ -82,8 +82,9 @@ int ddpb_conv1_wgrad_tc_partials(const void* dact_planes, const float* x, float*
 /* out[i] = sum_p part[p*n + i], fixed order. */
 int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out, void* stream);
 
-/* Same result as ddpb_conv1_wgrad, for callers that cannot pass scratch because they cannot
- * allocate device memory (a host that gave all of it to its own pool, or a plug-in barred from
+/* The same gradient as ddpb_conv1_wgrad up to rounding (the batch is split into a different number
+ * of partial blocks, so the summation order differs), for callers that cannot pass scratch because
+ * they cannot allocate device memory (a host that gave all of it to its own pool, or a plug-in barred from
  * cudaMalloc/cudaFree because those stall every stream on the device).  The partial sums live in
  * an 80 KB array inside the library's device image, held by every GPU that loads the library.
  * Limit: 64 partial blocks = batches of up to ddpb_conv1_wgrad_noalloc_max_batch(H,W) images
@@ -113,6 +114,74 @@ int ddpb_conv3x3_wgrad(const void* dout_planes, const void* in_planes, float* dw
 int ddpb_conv3x3_wgrad_partials(const void* dout_planes, const void* in_planes, float* scratch,
                                 int* nparts_out, int cin, int cout, int batch, int batch_cap, int H,
                                 int W, void* stream);
+
+/* ---- reference-precision mode ("bf16x3"): what torch runs for the reference is fp32 storage, TF32
+ * convolutions and an fp32 linear layer (reference model.py:8-16 through cuDNN/cuBLAS).  Here:
+ *   split planes  = every value as two bf16 terms x = hi + lo (C/8 hi planes then C/8 lo planes,
+ *                   4 bytes per value, 16-bit significand); GEMMs over split operands issue three
+ *                   tcgen05.mma per K step (hi.hi + lo.hi + hi.lo, fp32 accumulation);
+ *   fp32 planes   = 4 fp32 channels per 16-byte row, for tensors the fp32 CUDA-core ops read.
+ * packed = the split bf16 tile images of the conv weight [fwd hi | fwd lo | dgrad hi | dgrad lo]
+ * (ddpb_conv3x3_pack_split, or rewritten in place by ddpb_reduce_allreduce_sgd_pack).
+ * Measured error of every op against an fp64 oracle, next to torch's own path: profiles/precision.md. */
+int ddpb_conv1_fwd_tc_split(const float* x, const float* w, const float* b, void* out_split_planes,
+                            int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+size_t ddpb_conv3x3_pack_split_bytes(int cin, int cout);
+int ddpb_conv3x3_pack_split(const float* w, void* packed, int cin, int cout, void* stream);
+/* out: fp32 planes when out_f32 != 0, else split planes. */
+int ddpb_conv3x3_fwd_split(const void* in_split_planes, const void* packed, const float* bias,
+                           void* out_planes, int cin, int cout, int batch, int batch_cap, int H, int W,
+                           int out_f32, void* stream);
+int ddpb_conv3x3_dgrad_split(const void* dout_split_planes, const void* packed,
+                             const void* mask_split_planes, void* din_planes, int cin, int cout,
+                             int batch, int batch_cap, int H, int W, int out_f32, void* stream);
+/* bias_part/nsplit/nbx (optional): exact-fp32 bias-gradient parts left by ddpb_linear_bwd_f32;
+ * db is then their fixed-order sum instead of the tensor-core ones-column. */
+int ddpb_conv3x3_wgrad_split(const void* dout_split_planes, const void* in_split_planes, float* dw,
+                             float* db, float* scratch, const float* bias_part, int nsplit, int nbx,
+                             int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+int ddpb_conv3x3_wgrad_split_partials(const void* dout_split_planes, const void* in_split_planes,
+                                      float* scratch, int* nparts_out, int cin, int cout, int batch,
+                                      int batch_cap, int H, int W, void* stream);
+/* conv1 weight gradient from split dact planes on the tensor cores (two passes: hi, lo). */
+int ddpb_conv1_wgrad_tc_split(const void* dact_split_planes, const float* x, float* dw_db,
+                              float* scratch, int cin, int cout, int batch, int batch_cap, int H, int W,
+                              void* stream);
+int ddpb_conv1_wgrad_tc_split_partials(const void* dact_split_planes, const float* x, float* scratch,
+                                       int* nparts_out, int cin, int cout, int batch, int batch_cap,
+                                       int H, int W, void* stream);
+/* conv1 weight gradient in exact fp32 on the CUDA cores from fp32 dact planes (cuDNN runs this
+ * Cin = 1 layer in plain fp32 too); partials have the layout of ddpb_conv1_wgrad_tc_partials. */
+size_t ddpb_conv1_wgrad_f32_scratch_bytes(int cin, int cout);
+int ddpb_conv1_wgrad_f32(const void* dact_f32_planes, const float* x, float* dw_db, float* scratch,
+                         int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+int ddpb_conv1_wgrad_f32_partials(const void* dact_f32_planes, const float* x, float* scratch,
+                                  int* nparts_out, int cin, int cout, int batch, int batch_cap, int H,
+                                  int W, void* stream);
+/* fp32 linear layer (FMA on the CUDA cores, like cuBLAS with TF32 off) on fp32 activation planes.
+ * bwd: dact = split planes (split_out != 0) or fp32 planes rounded to tf32; bias_part (optional,
+ * ddpb_linear_bwd_f32_bias_part_bytes) receives exact-fp32 per-channel partial sums of dact and
+ * *nsplit_out / *nbx_out (host) their extents. */
+size_t ddpb_linear_fwd_f32_scratch_bytes(int nout, int C, int batch_cap, int H, int W);
+int ddpb_linear_fwd_f32(const void* act_f32_planes, const float* W_fl, float* partial, int* S_out,
+                        int nout, int C, int batch, int batch_cap, int H, int W, void* stream);
+size_t ddpb_linear_bwd_f32_bias_part_bytes(int C, int batch_cap, int H, int W);
+int ddpb_linear_bwd_f32(const void* act_f32_planes, const float* dlogits, const float* W_fl,
+                        void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,
+                        int batch_cap, int H, int W, int split_out, float* bias_part, int* nsplit_out,
+                        int* nbx_out, void* stream);
+/* tf32 building blocks on fp32 planes (forward / data gradient only: tcgen05 defines an MN-major tf32
+ * operand — the weight gradient's view of a plane — only for the 128B_BASE32B swizzled layout). */
+int ddpb_conv1_fwd_tc_f32(const float* x, const float* w, const float* b, void* out_f32_planes,
+                          int cin, int cout, int batch, int batch_cap, int H, int W, void* stream);
+size_t ddpb_conv3x3_pack_tf32_bytes(int cin, int cout);
+int ddpb_conv3x3_pack_tf32(const float* w, void* packed, int cin, int cout, void* stream);
+int ddpb_conv3x3_fwd_tf32(const void* in_f32_planes, const void* packed, const float* bias,
+                          void* out_f32_planes, int cin, int cout, int batch, int batch_cap, int H,
+                          int W, int round_out, void* stream);
+int ddpb_conv3x3_dgrad_tf32(const void* dout_f32_planes, const void* packed, const void* mask_f32_planes,
+                            void* din_f32_planes, int cin, int cout, int batch, int batch_cap, int H,
+                            int W, int round_out, void* stream);
 
 /* ---- linear layer over the flattened activation (NCHW flatten order).  reference model.py:16,19.
  * fwd writes per-slice partial logits partial[S][batch][nout]; *S_out (host) receives S. */
@@ -153,7 +222,7 @@ int ddpb_linear_bwd_tc(const void* act_planes, const void* dl_packed, const void
 int ddpb_zero_tail_rows(void* planes, int nplanes, int batch, int batch_cap, int H, int W,
                         void* stream);
 
-/* ---- symmetric-memory communicator (csrc/comm.cu): one process per GPU, world in {1,2,4,8}.
+/* ---- symmetric-memory communicator (csrc/comm.cu): one process per GPU, world 1..8.
  * ddpb_comm_create cudaMallocs this rank's buffer (header + payload, zero-filled);
  * ddpb_comm_get_handle / ddpb_comm_connect exchange CUDA IPC handles (host side, any transport).
  * Offsets are byte offsets into the payload, identical on all ranks, 16-byte aligned.
@@ -205,6 +274,14 @@ int ddpb_allreduce_sgd(void* comm, size_t grad_off, size_t param_off, long long 
 int ddpb_reduce_allreduce_sgd(void* comm, const float* partials, int nparts, long long n,
                               size_t grad_off, size_t param_off, const float* lr_dev, int algo,
                               int layout, int slot, void* stream);
+/* Same; with layout 1 it can also (a) rewrite `pack` — the split bf16 tile images of net.2.weight,
+ * ddpb_conv3x3_pack_split_bytes(32, 64) bytes — from the updated weights, and (b) take the net.2.bias
+ * gradient from the exact-fp32 parts of ddpb_linear_bwd_f32 (bias_part, extents bp_nsplit x bp_nbx,
+ * bp_hw = H*W) instead of the accumulator images' bias column.  Either pointer may be NULL. */
+int ddpb_reduce_allreduce_sgd_pack(void* comm, const float* partials, int nparts, long long n,
+                                   size_t grad_off, size_t param_off, const float* lr_dev, int algo,
+                                   int layout, int slot, void* pack, const float* bias_part,
+                                   int bp_nsplit, int bp_nbx, int bp_hw, void* stream);
 /* plain sum all-reduce, dtype 0 = fp32, 1 = bf16; out_off must not overlap in_off. */
 int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, int dtype, int algo,
                    int slot, void* stream);

@@ -158,33 +158,69 @@ class SimpleCNNB200(_ModelBase):
     """
 
     def __init__(self, batch_cap: int, device="cuda", params=None, grads=None, init: bool = True,
-                 generator: torch.Generator | None = None, alt_grads=None):
+                 generator: torch.Generator | None = None, alt_grads=None, precision: str | None = None):
+        """``precision``:
+
+        * ``"bf16x3"`` (default; env DDPB_PRECISION) — the reference's numerics as torch runs them
+          on CUDA (reference model.py:8-16: fp32 storage, TF32 convolutions, fp32 linear layer),
+          matched or exceeded everywhere: activations and activation gradients are stored at 4 bytes
+          per value — as split planes x = hi + lo (two bf16 terms, a 16-bit significand) where a
+          tensor-core GEMM consumes them, as plain fp32 where the linear layer does; the convolution
+          GEMMs multiply split operands with three MMAs per K step (hi.hi + lo.hi + hi.lo, fp32
+          accumulation: more operand bits than TF32's 11); conv1's forward is TF32 like cuDNN's; the
+          linear layer is fp32 FMA like cuBLAS with TF32 off.  tests/test_precision_gpu.py measures
+          the error of every op against an fp64 oracle next to torch's own CUDA path.
+        * ``"bf16"`` — fast mode: bf16 activation storage and single bf16 tensor-core operands;
+          NOT the reference's precision, never the default, reported separately.
+        """
+        import os
         from ..ops import native as nat
         self.nat = nat
         nat.lib()
         self.device = torch.device(device)
         self.batch_cap = int(batch_cap)
+        self.precision = precision or os.environ.get("DDPB_PRECISION", "bf16x3")
+        if self.precision not in nat.PRECISIONS:
+            raise ValueError(f"precision must be one of {nat.PRECISIONS}, got {self.precision!r}")
+        self.x3 = self.precision == "bf16x3"
         self.arena = ParamArena(SPECS, device=self.device, params=params, grads=grads)
         if init:
             _default_init_(self.arena, generator)
         H, W = IMG_H, IMG_W
         with torch.cuda.device(self.device):
             dev = self.device
-            self.act1 = nat.alloc_planes(C1, batch_cap, H, W, dev)
-            self.act2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
-            self.dact2 = nat.alloc_planes(C2, batch_cap, H, W, dev)
-            self.dact1 = nat.alloc_planes(C1, batch_cap, H, W, dev)
-            self.lin_partial = nat.scratch(nat.linear_fwd_tc_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
-            #: fl.weight pre-packed into bf16 tensor-core tiles (refresh with pack_weights() after
-            #: every change of fl.weight; the step engine does it right after the bucket-0 update)
-            self.lin_packed = torch.zeros(nat.linear_pack_bytes(NCLS, C2, H, W), dtype=torch.uint8,
-                                          device=dev)
+            tc_fmt = "split" if self.x3 else "bf16"   # tensors a tensor-core GEMM consumes
+            self.act1 = nat.alloc_planes(C1, batch_cap, H, W, dev, tc_fmt)
+            self.act2 = nat.alloc_planes(C2, batch_cap, H, W, dev, "f32" if self.x3 else "bf16")  # linear layer's input
+            self.dact2 = nat.alloc_planes(C2, batch_cap, H, W, dev, tc_fmt)
+            # bf16x3: dact1 feeds the exact-fp32 conv1 weight gradient (CUDA cores): plain fp32 planes
+            self.dact1 = nat.alloc_planes(C1, batch_cap, H, W, dev, "f32" if self.x3 else "bf16")
+            if self.x3:
+                #: exact-fp32 partial sums of dact2 per channel (net.2.bias gradient), written by the
+                #: linear backward; (nsplit, nbx) of the last backward_head() in self.db2_extent
+                self.db2_part = nat.scratch(nat.linear_bwd_f32_bias_part_bytes(C2, batch_cap, H, W), dev)
+                self.db2_extent = (0, 0)
+                self.lin_partial = nat.scratch(nat.linear_fwd_f32_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+                self.lin_bwd_scr = nat.scratch(nat.linear_bwd_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+                self.lin_packed = None
+                #: net.2.weight as split bf16 tensor-core tile images (forward + data gradient, hi + lo);
+                #: rewritten by the fused net.2 bucket update, or by pack_weights() after any other change
+                self.w2_packed = torch.zeros(nat.conv3x3_pack_split_bytes(C1, C2) // 2, dtype=torch.bfloat16,
+                                             device=dev)
+            else:
+                self.lin_partial = nat.scratch(nat.linear_fwd_tc_scratch_bytes(NCLS, C2, batch_cap, H, W), dev)
+                #: fl.weight pre-packed into bf16 tensor-core tiles (refresh with pack_weights() after
+                #: every change of fl.weight; the step engine does it right after the bucket-0 update)
+                self.lin_packed = torch.zeros(nat.linear_pack_bytes(NCLS, C2, H, W), dtype=torch.uint8,
+                                              device=dev)
+                self.w2_packed = None
             self.logits = torch.zeros(batch_cap, NCLS, device=dev)
             self.dlogits = torch.zeros(batch_cap, NCLS, device=dev)
             self.dl_packed = torch.zeros(nat.dl_packed_bytes(batch_cap), dtype=torch.uint8, device=dev)
             self.loss = torch.zeros(1, device=dev)
             self.scr_w2 = nat.scratch(nat.conv3x3_wgrad_scratch_bytes(C1, C2), dev)
-            self.scr_w1 = nat.scratch(nat.conv1_wgrad_tc_scratch_bytes(1, C1), dev)
+            self.scr_w1 = nat.scratch(max(nat.conv1_wgrad_tc_scratch_bytes(1, C1),
+                                          nat.conv1_wgrad_f32_scratch_bytes(1, C1)), dev)
             self.lr_dev = torch.full((1,), 0.01, device=dev)
         a = self.arena
         self.w1, self.b1 = a.view("net.0.weight"), a.view("net.0.bias")
@@ -206,9 +242,15 @@ class SimpleCNNB200(_ModelBase):
         self.pack_weights()  # the tensor-core tiles of fl.weight must follow the new values
 
     # ------------------------------------------------------------------ step pieces
-    def pack_weights(self, stream=None) -> None:
-        """fl.weight (fp32) -> bf16 tensor-core tiles used by the linear forward and backward."""
-        self.nat.linear_pack(self.wf, self.lin_packed, NCLS, C2, IMG_H, IMG_W, stream)
+    def pack_weights(self, stream=None, fl: bool = True, conv2: bool = True) -> None:
+        """Refresh the tensor-core tile copies of the master weights: bf16 mode — fl.weight -> bf16
+        hi+lo tiles of the linear forward/backward; bf16x3 mode — net.2.weight -> split tiles of the
+        conv2 forward/data gradient (the linear layer reads the fp32 master weights directly)."""
+        if self.x3:
+            if conv2:
+                self.nat.conv3x3_pack_split(self.w2, self.w2_packed, stream)
+        elif fl:
+            self.nat.linear_pack(self.wf, self.lin_packed, NCLS, C2, IMG_H, IMG_W, stream)
 
     def forward_loss(self, x: torch.Tensor, y: torch.Tensor, batch: int | None = None, stream=None,
                      parity: int = 0, pack: bool = True):
@@ -219,6 +261,15 @@ class SimpleCNNB200(_ModelBase):
         cap, H, W = self.batch_cap, IMG_H, IMG_W
         if pack:
             self.pack_weights(stream)
+        if self.x3:
+            nat.conv1_fwd_tc_split(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
+            # act2 feeds the fp32 linear layer: plain fp32 planes
+            nat.conv3x3_fwd_split(self.act1, self.w2_packed, self.b2, self.act2, C1, C2, b, cap, H, W,
+                                  stream, out_f32=True)
+            S = nat.linear_fwd_f32(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
+            nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, gs["bf"],
+                             self.loss, NCLS, b, stream)
+            return self.loss
         nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W, stream)
         nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W, stream)
         S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W, stream)
@@ -229,38 +280,53 @@ class SimpleCNNB200(_ModelBase):
     def backward_head(self, batch: int, stream=None, parity: int = 0):
         """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel)."""
         gs = self.grad_sets[parity]
+        if self.x3:
+            self.db2_extent = self.nat.linear_bwd_f32(
+                self.act2, self.dlogits, self.wf, self.dact2, gs["wf"], self.lin_bwd_scr, NCLS, C2, batch,
+                self.batch_cap, IMG_H, IMG_W, stream, split_out=True, bias_part=self.db2_part)
+            return
         self.nat.linear_bwd_tc(self.act2, self.dl_packed, self.lin_packed, self.dact2, gs["wf"],
                                NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):
         """conv2 weight + bias gradient (independent of the dgrad chain: may run on its own stream)."""
         gs = self.grad_sets[parity]
+        if self.x3:
+            self.nat.conv3x3_wgrad_split(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
+                                         self.batch_cap, IMG_H, IMG_W, stream,
+                                         bias_parts=(self.db2_part, *self.db2_extent))
+            return
         self.nat.conv3x3_wgrad(self.dact2, self.act1, gs["w2"], gs["b2"], self.scr_w2, C1, C2, batch,
                                self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_conv2_wgrad_partials(self, batch: int, stream=None) -> int:
         """Like backward_conv2_wgrad but leaves the gradient as per-CTA accumulator images in
         ``self.scr_w2`` (returns their count) for the fused reduce + all-reduce + SGD kernel."""
-        return self.nat.conv3x3_wgrad_partials(self.dact2, self.act1, self.scr_w2, C1, C2, batch,
-                                               self.batch_cap, IMG_H, IMG_W, stream)
+        fn = self.nat.conv3x3_wgrad_split_partials if self.x3 else self.nat.conv3x3_wgrad_partials
+        return fn(self.dact2, self.act1, self.scr_w2, C1, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_dgrad(self, batch: int, stream=None) -> None:
-        """conv2 data gradient (with ReLU'): dact1 from dact2.  The LAST reader of net.2.weight in a
-        step — the engine must not let the net.2 bucket update start before this has finished."""
+        """conv2 data gradient (with ReLU'): dact1 from dact2.  The LAST reader of net.2.weight (bf16
+        mode) / of its split tile images (bf16x3 mode) in a step — the engine must not let the net.2
+        bucket update start before this has finished."""
+        if self.x3:
+            self.nat.conv3x3_dgrad_split(self.dact2, self.w2_packed, self.act1, self.dact1, C1, C2, batch,
+                                         self.batch_cap, IMG_H, IMG_W, stream, out_f32=True)
+            return
         self.nat.conv3x3_dgrad(self.dact2, self.w2, self.act1, self.dact1, batch, self.batch_cap,
                                IMG_H, IMG_W, stream)
 
     def backward_conv1_wgrad(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0) -> None:
         """conv1 weight + bias gradient into the gradient arena (tensor-core kernel + split-K reduce)."""
         gs = self.grad_sets[parity]
-        self.nat.conv1_wgrad_tc(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, self.batch_cap,
-                                IMG_H, IMG_W, stream)
+        fn = self.nat.conv1_wgrad_f32 if self.x3 else self.nat.conv1_wgrad_tc
+        fn(self.dact1, x, gs["w1"], self.scr_w1, 1, C1, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_conv1_wgrad_partials(self, x: torch.Tensor, batch: int, stream=None) -> int:
         """conv1 gradient left as per-CTA partials in ``self.scr_w1`` (returns their count) for the
         fused reduce + all-reduce + SGD kernel."""
-        return self.nat.conv1_wgrad_tc_partials(self.dact1, x, self.scr_w1, 1, C1, batch, self.batch_cap,
-                                                IMG_H, IMG_W, stream)
+        fn = self.nat.conv1_wgrad_f32_partials if self.x3 else self.nat.conv1_wgrad_tc_partials
+        return fn(self.dact1, x, self.scr_w1, 1, C1, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_dgrad_conv1(self, x: torch.Tensor, batch: int, stream=None, parity: int = 0):
         """conv2 data gradient (with ReLU') followed by the conv1 weight + bias gradient."""
@@ -290,8 +356,9 @@ class SimpleCNNB200(_ModelBase):
         from ..ops import layout as lay
         tail = 1 if lay.tiles_for(batch, IMG_H, IMG_W) * lay.TILE_M > batch * 900 else 0
         # conv1, conv2, linear, loss | (tail zero) linear bwd | wgrad+reduce, dgrad, conv1 wgrad
-        # (its split-K reduce is fused into the bucket update kernel)
-        return 4 + (1 + tail) + 2 + 1 + 1
+        # (its split-K reduce is fused into the bucket update kernel); the fp32 linear backward adds
+        # the fixed-order reduce of its per-image-split dW partials
+        return 4 + (1 + tail) + 2 + 1 + 1 + (1 if self.x3 else 0)
 
     def sgd_step(self, lr: float | None = None, stream=None) -> None:
         if lr is not None:
@@ -314,9 +381,14 @@ class SimpleCNNB200(_ModelBase):
         y = torch.zeros(b, dtype=torch.int64, device=self.device)
         scratch_db = torch.empty(NCLS, device=self.device)
         self.pack_weights()
-        nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W)
-        nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W)
-        S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W)
+        if self.x3:
+            nat.conv1_fwd_tc_split(x, self.w1, self.b1, self.act1, b, cap, H, W)
+            nat.conv3x3_fwd_split(self.act1, self.w2_packed, self.b2, self.act2, C1, C2, b, cap, H, W)
+            S = nat.linear_fwd_f32(self.act2, self.wf, self.lin_partial, NCLS, C2, b, cap, H, W)
+        else:
+            nat.conv1_fwd_tc(x, self.w1, self.b1, self.act1, b, cap, H, W)
+            nat.conv3x3_fwd(self.act1, self.w2, self.b2, self.act2, b, cap, H, W)
+            S = nat.linear_fwd_tc(self.act2, self.lin_packed, self.lin_partial, NCLS, C2, b, cap, H, W)
         nat.softmax_xent(self.lin_partial, S, self.bf, y, self.logits, self.dlogits, scratch_db,
                          self.loss, NCLS, b)
         return self.logits[:b]

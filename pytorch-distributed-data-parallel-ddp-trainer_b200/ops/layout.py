@@ -30,24 +30,54 @@ def row_index(batch: int, H: int, W: int, device=None) -> torch.Tensor:
     return GUARD + b * PHW + (h + 1) * PW + (w + 1)
 
 
-def nchw_to_planes(x: torch.Tensor, batch_cap: int | None = None) -> torch.Tensor:
-    """[B,C,H,W] float -> zero-padded bf16 planes [C/8, rows, 8]."""
+def nchw_to_planes(x: torch.Tensor, batch_cap: int | None = None,
+                   dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """[B,C,H,W] float -> zero-padded planes: [C/8, rows, 8] bf16 or, for ``dtype=torch.float32``,
+    [C/4, rows, 4] fp32 (16-byte rows either way)."""
     B, C, H, W = x.shape
-    assert C % 8 == 0
+    ch = 4 if dtype == torch.float32 else 8
+    assert C % ch == 0
     rows = plane_rows(batch_cap or B, H, W)
-    planes = torch.zeros(C // 8, rows, 8, dtype=torch.bfloat16, device=x.device)
+    planes = torch.zeros(C // ch, rows, ch, dtype=dtype, device=x.device)
     idx = row_index(B, H, W, x.device).reshape(-1)
-    # [B,C,H,W] -> [C/8, B*H*W, 8]
-    v = x.reshape(B, C // 8, 8, H, W).permute(1, 0, 3, 4, 2).reshape(C // 8, B * H * W, 8)
-    planes[:, idx, :] = v.to(torch.bfloat16)
+    # [B,C,H,W] -> [C/ch, B*H*W, ch]
+    v = x.reshape(B, C // ch, ch, H, W).permute(1, 0, 3, 4, 2).reshape(C // ch, B * H * W, ch)
+    planes[:, idx, :] = v.to(dtype)
     return planes
 
 
+def nchw_to_split_planes(x: torch.Tensor, batch_cap: int | None = None) -> torch.Tensor:
+    """[B,C,H,W] fp32 -> split planes [2*C/8, rows, 8] bf16: hi = nearest bf16 of x (planes 0..C/8-1),
+    lo = nearest bf16 of (x - hi) (planes C/8..): what the producing kernels store (csrc/layout.cuh)."""
+    hi = x.to(torch.bfloat16)
+    lo = (x - hi.float()).to(torch.bfloat16)
+    return torch.cat([nchw_to_planes(hi.float(), batch_cap), nchw_to_planes(lo.float(), batch_cap)], 0)
+
+
+def split_value(x: torch.Tensor) -> torch.Tensor:
+    """The fp32 value hi + lo that split planes hold for x (a 16-bit significand)."""
+    hi = x.to(torch.bfloat16).float()
+    return hi + (x - hi).to(torch.bfloat16).float()
+
+
 def planes_to_nchw(planes: torch.Tensor, B: int, C: int, H: int, W: int) -> torch.Tensor:
-    """bf16 planes -> [B,C,H,W] float32 (interior pixels only)."""
+    """bf16, split or fp32 planes -> [B,C,H,W] float32 (interior pixels only); split planes are
+    recognised by their plane count (2*C/8) and returned as hi + lo."""
+    ch = planes.shape[-1]
+    if ch == 8 and planes.shape[0] == 2 * (C // 8):
+        n = C // 8
+        return planes_to_nchw(planes[:n], B, C, H, W) + planes_to_nchw(planes[n:], B, C, H, W)
     idx = row_index(B, H, W, planes.device).reshape(-1)
-    v = planes[:, idx, :].float().reshape(C // 8, B, H, W, 8)
+    v = planes[:, idx, :].float().reshape(C // ch, B, H, W, ch)
     return v.permute(1, 0, 4, 2, 3).reshape(B, C, H, W).contiguous()
+
+
+def round_tf32(x: torch.Tensor) -> torch.Tensor:
+    """Nearest tf32 (10 mantissa bits, ties away from zero) of an fp32 tensor, as fp32 — the
+    host-side restatement of ``cvt.rna.tf32.f32`` used by the kernels (csrc/ptx.cuh)."""
+    bits = x.contiguous().view(torch.int32)
+    out = ((bits + 0x1000) & ~0x1FFF).view(torch.float32)
+    return torch.where(torch.isfinite(x), out, x)
 
 
 def border_rows_are_zero(planes: torch.Tensor, B: int, H: int, W: int) -> bool:

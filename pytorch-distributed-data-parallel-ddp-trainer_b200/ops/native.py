@@ -56,7 +56,38 @@ _SIGNATURES = {
     "ddpb_linear_bwd_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_bwd": (I, [P, P, P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_sgd": (I, [P, P, P, LL, P]),
+    # split planes (x = hi + lo bf16, "bf16x3" GEMMs) + fp32 linear layer: the reference-precision mode
+    "ddpb_conv1_fwd_tc_split": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_tc_split": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_tc_split_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_pack_split_bytes": (c_size_t, [I, I]),
+    "ddpb_conv3x3_pack_split": (I, [P, P, I, I, P]),
+    "ddpb_conv3x3_fwd_split": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_dgrad_split": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_wgrad_split": (I, [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_wgrad_split_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_linear_fwd_f32_scratch_bytes": (c_size_t, [I, I, I, I, I]),
+    "ddpb_linear_fwd_f32": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_linear_bwd_f32_bias_part_bytes": (c_size_t, [I, I, I, I]),
+    "ddpb_linear_bwd_f32": (I, [P, P, P, P, P, P, I, I, I, I, I, I, I, P, POINTER(c_int), POINTER(c_int), P]),
+    "ddpb_conv1_wgrad_f32_scratch_bytes": (c_size_t, [I, I]),
+    "ddpb_conv1_wgrad_f32": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv1_wgrad_f32_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_zero_tail_rows": (I, [P, I, I, I, I, I, P]),
+    # fp32 planes, tf32 tensor-core operands: forward / data-gradient building blocks
+    "ddpb_conv1_fwd_tc_f32": (I, [P, P, P, P, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_pack_tf32_bytes": (c_size_t, [I, I]),
+    "ddpb_conv3x3_pack_tf32": (I, [P, P, I, I, P]),
+    "ddpb_conv3x3_fwd_tf32": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    "ddpb_conv3x3_dgrad_tf32": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
 }
+
+#: execution precisions of the step (models/simple_cnn.py): "bf16x3" = the reference's numerics
+#: (fp32-equivalent storage, >= TF32 operand precision for the convolutions, fp32 linear layer),
+#: "bf16" = fast mode
+PRECISIONS = ("bf16x3", "bf16")
+#: plane storage formats (csrc/layout.cuh)
+PLANE_FORMATS = ("bf16", "split", "f32")
 
 
 class NativeError(RuntimeError):
@@ -126,11 +157,20 @@ def guard_rows() -> int:
     return int(lib().ddpb_guard_rows())
 
 
-def alloc_planes(channels: int, batch_cap: int, H: int, W: int, device="cuda") -> torch.Tensor:
-    """Zero-filled activation buffer [C/8, plane_rows, 8] bf16."""
+def alloc_planes(channels: int, batch_cap: int, H: int, W: int, device="cuda",
+                 fmt: str = "bf16") -> torch.Tensor:
+    """Zero-filled activation buffer (16-byte rows in every format, csrc/layout.cuh):
+    "bf16"  [C/8, plane_rows, 8] bf16;
+    "split" [2*C/8, plane_rows, 8] bf16 — C/8 hi planes then C/8 lo planes, value = hi + lo;
+    "f32"   [C/4, plane_rows, 4] fp32."""
+    assert fmt in PLANE_FORMATS
+    rows = plane_rows(batch_cap, H, W)
+    if fmt == "f32":
+        assert channels % 4 == 0
+        return torch.zeros(channels // 4, rows, 4, dtype=torch.float32, device=device)
     assert channels % 8 == 0
-    return torch.zeros(channels // 8, plane_rows(batch_cap, H, W), 8, dtype=torch.bfloat16,
-                       device=device)
+    sets = 2 if fmt == "split" else 1
+    return torch.zeros(sets * channels // 8, rows, 8, dtype=torch.bfloat16, device=device)
 
 
 def scratch(nbytes: int, device="cuda") -> torch.Tensor:
@@ -279,3 +319,146 @@ def linear_bwd(act, dlogits, Wfl, dact, dW, scr, nout, C, batch, batch_cap, H, W
 
 def sgd(p, grad, lr_dev, stream=None):
     check(lib().ddpb_sgd(ptr(p), ptr(grad), ptr(lr_dev), p.numel(), stream_ptr(stream)), "sgd")
+
+
+# ----------------------------------------------------------------------------- split planes / fp32 linear
+def conv1_fwd_tc_split(x, w, b, out, batch, batch_cap, H, W, stream=None):
+    """conv1 + bias + ReLU into split planes (hi + lo bf16)."""
+    check(lib().ddpb_conv1_fwd_tc_split(ptr(x), ptr(w), ptr(b), ptr(out), w.shape[1], w.shape[0], batch,
+                                        batch_cap, H, W, stream_ptr(stream)), "conv1_fwd_tc_split")
+
+
+def conv1_wgrad_tc_split(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
+    check(lib().ddpb_conv1_wgrad_tc_split(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
+                                          batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad_tc_split")
+
+
+def conv1_wgrad_tc_split_partials(dact, x, scr, cin, cout, batch, batch_cap, H, W, stream=None) -> int:
+    n = c_int(0)
+    check(lib().ddpb_conv1_wgrad_tc_split_partials(ptr(dact), ptr(x), ptr(scr), ctypes.byref(n), cin, cout,
+                                                   batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv1_wgrad_tc_split_partials")
+    return n.value
+
+
+def conv3x3_pack_split_bytes(cin, cout) -> int:
+    return int(lib().ddpb_conv3x3_pack_split_bytes(cin, cout))
+
+
+def conv3x3_pack_split(w, packed, stream=None):
+    """fp32 conv weight [cout,cin,3,3] -> split bf16 tile images [fwd hi|fwd lo|dgrad hi|dgrad lo]."""
+    check(lib().ddpb_conv3x3_pack_split(ptr(w), ptr(packed), w.shape[1], w.shape[0], stream_ptr(stream)),
+          "conv3x3_pack_split")
+
+
+def conv3x3_fwd_split(inp, packed, bias, out, cin, cout, batch, batch_cap, H, W, stream=None,
+                      out_f32: bool = True):
+    """Split-plane input; ``out`` = fp32 planes (default: the consumer is the fp32 linear layer) or
+    split planes."""
+    check(lib().ddpb_conv3x3_fwd_split(ptr(inp), ptr(packed), ptr(bias), ptr(out), cin, cout, batch,
+                                       batch_cap, H, W, int(out_f32), stream_ptr(stream)),
+          "conv3x3_fwd_split")
+
+
+def conv3x3_dgrad_split(dout, packed, mask, din, cin, cout, batch, batch_cap, H, W, stream=None,
+                        out_f32: bool = False):
+    """``din`` = split planes, or unrounded fp32 planes with ``out_f32`` (for the exact-fp32 conv1
+    weight gradient)."""
+    check(lib().ddpb_conv3x3_dgrad_split(ptr(dout), ptr(packed), ptr(mask), ptr(din), cin, cout, batch,
+                                         batch_cap, H, W, int(out_f32), stream_ptr(stream)),
+          "conv3x3_dgrad_split")
+
+
+def conv3x3_wgrad_split(dout, inp, dw, db, scr, cin, cout, batch, batch_cap, H, W, stream=None,
+                        bias_parts=None):
+    """``bias_parts`` = (tensor, nsplit, nbx) from linear_bwd_f32: db becomes their exact-fp32 sum."""
+    bp, ns, nb = bias_parts if bias_parts is not None else (None, 0, 0)
+    check(lib().ddpb_conv3x3_wgrad_split(ptr(dout), ptr(inp), ptr(dw), ptr(db), ptr(scr), ptr(bp), ns, nb,
+                                         cin, cout, batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv3x3_wgrad_split")
+
+
+def conv3x3_wgrad_split_partials(dout, inp, scr, cin, cout, batch, batch_cap, H, W, stream=None) -> int:
+    n = c_int(0)
+    check(lib().ddpb_conv3x3_wgrad_split_partials(ptr(dout), ptr(inp), ptr(scr), ctypes.byref(n), cin,
+                                                  cout, batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv3x3_wgrad_split_partials")
+    return n.value
+
+
+def linear_fwd_f32_scratch_bytes(nout, C, batch_cap, H, W) -> int:
+    return int(lib().ddpb_linear_fwd_f32_scratch_bytes(nout, C, batch_cap, H, W))
+
+
+def linear_fwd_f32(act, Wfl, partial, nout, C, batch, batch_cap, H, W, stream=None) -> int:
+    """fp32 linear forward on fp32 planes; returns S, the number of partial slices written."""
+    s = c_int(0)
+    check(lib().ddpb_linear_fwd_f32(ptr(act), ptr(Wfl), ptr(partial), ctypes.byref(s), nout, C, batch,
+                                    batch_cap, H, W, stream_ptr(stream)), "linear_fwd_f32")
+    return s.value
+
+
+def linear_bwd_f32_bias_part_bytes(C, batch_cap, H, W) -> int:
+    return int(lib().ddpb_linear_bwd_f32_bias_part_bytes(C, batch_cap, H, W))
+
+
+def linear_bwd_f32(act, dlogits, Wfl, dact, dW, scr, nout, C, batch, batch_cap, H, W, stream=None,
+                   split_out: bool = True, bias_part=None):
+    """fp32 linear backward on fp32 activation planes; ``dact`` = split planes (default) or fp32
+    planes rounded to tf32.  With ``bias_part`` (linear_bwd_f32_bias_part_bytes) the kernel also leaves
+    the exact-fp32 per-channel sums of dact there; returns their extents (nsplit, nbx)."""
+    ns, nb = c_int(0), c_int(0)
+    check(lib().ddpb_linear_bwd_f32(ptr(act), ptr(dlogits), ptr(Wfl), ptr(dact), ptr(dW), ptr(scr),
+                                    nout, C, batch, batch_cap, H, W, int(split_out), ptr(bias_part),
+                                    ctypes.byref(ns), ctypes.byref(nb), stream_ptr(stream)),
+          "linear_bwd_f32")
+    return ns.value, nb.value
+
+
+def conv1_wgrad_f32_scratch_bytes(cin, cout) -> int:
+    return int(lib().ddpb_conv1_wgrad_f32_scratch_bytes(cin, cout))
+
+
+def conv1_wgrad_f32(dact, x, dw_db, scr, cin, cout, batch, batch_cap, H, W, stream=None):
+    """Exact-fp32 conv1 weight + bias gradient from fp32 planes (CUDA cores)."""
+    check(lib().ddpb_conv1_wgrad_f32(ptr(dact), ptr(x), ptr(dw_db), ptr(scr), cin, cout, batch,
+                                     batch_cap, H, W, stream_ptr(stream)), "conv1_wgrad_f32")
+
+
+def conv1_wgrad_f32_partials(dact, x, scr, cin, cout, batch, batch_cap, H, W, stream=None) -> int:
+    n = c_int(0)
+    check(lib().ddpb_conv1_wgrad_f32_partials(ptr(dact), ptr(x), ptr(scr), ctypes.byref(n), cin, cout,
+                                              batch, batch_cap, H, W, stream_ptr(stream)),
+          "conv1_wgrad_f32_partials")
+    return n.value
+
+
+# ----------------------------------------------------------------------------- fp32 planes / tf32 blocks
+def conv1_fwd_tc_f32(x, w, b, out, batch, batch_cap, H, W, stream=None):
+    """conv1 + bias + ReLU into fp32 planes (values rounded to tf32)."""
+    check(lib().ddpb_conv1_fwd_tc_f32(ptr(x), ptr(w), ptr(b), ptr(out), w.shape[1], w.shape[0], batch,
+                                      batch_cap, H, W, stream_ptr(stream)), "conv1_fwd_tc_f32")
+
+
+def conv3x3_pack_tf32_bytes(cin, cout) -> int:
+    return int(lib().ddpb_conv3x3_pack_tf32_bytes(cin, cout))
+
+
+def conv3x3_pack_tf32(w, packed, stream=None):
+    """fp32 conv weight [cout,cin,3,3] -> tf32 tile images (forward + data-gradient) in ``packed``."""
+    check(lib().ddpb_conv3x3_pack_tf32(ptr(w), ptr(packed), w.shape[1], w.shape[0], stream_ptr(stream)),
+          "conv3x3_pack_tf32")
+
+
+def conv3x3_fwd_tf32(inp, packed, bias, out, cin, cout, batch, batch_cap, H, W, stream=None,
+                     round_out: bool = False):
+    check(lib().ddpb_conv3x3_fwd_tf32(ptr(inp), ptr(packed), ptr(bias), ptr(out), cin, cout, batch,
+                                      batch_cap, H, W, int(round_out), stream_ptr(stream)),
+          "conv3x3_fwd_tf32")
+
+
+def conv3x3_dgrad_tf32(dout, packed, mask, din, cin, cout, batch, batch_cap, H, W, stream=None,
+                       round_out: bool = True):
+    check(lib().ddpb_conv3x3_dgrad_tf32(ptr(dout), ptr(packed), ptr(mask), ptr(din), cin, cout, batch,
+                                        batch_cap, H, W, int(round_out), stream_ptr(stream)),
+          "conv3x3_dgrad_tf32")

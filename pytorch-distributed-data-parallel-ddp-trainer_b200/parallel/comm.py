@@ -62,13 +62,15 @@ for _name, _res, _args in (
     ("ddpb_comm_multicast_ptr", c_void_p, [P]),
     ("ddpb_allreduce_sgd", I, [P, SZ, SZ, LL, P, I, I, P]),
     ("ddpb_reduce_allreduce_sgd", I, [P, P, I, LL, SZ, SZ, P, I, I, I, P]),
+    ("ddpb_reduce_allreduce_sgd_pack", I, [P, P, I, LL, SZ, SZ, P, I, I, I, P, P, I, I, I, P]),
     ("ddpb_allreduce", I, [P, SZ, SZ, LL, I, I, I, P]),
     ("ddpb_broadcast", I, [P, SZ, LL, I, I, P]),
 ):
     nat.declare(_name, _res, _args)
 
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_PUSH, ALGO_NVLS = 0, 1, 2, 3, 4
-SUPPORTED_WORLD_SIZES = (1, 2, 4, 8)  # the kernels are instantiated per world size (csrc/comm.cu)
+# one NVSwitch node; the kernels are instantiated for every world size 1..8 (csrc/comm.cu)
+SUPPORTED_WORLD_SIZES = (1, 2, 3, 4, 5, 6, 7, 8)
 DTYPE_CODES = {torch.float32: 0, torch.bfloat16: 1}
 # how partial element i maps into the gradient/parameter slice of reduce_allreduce_sgd
 LAYOUT_IDENTITY, LAYOUT_CONV3X3_WGRAD = 0, 1
@@ -308,13 +310,25 @@ class SymmetricComm:
 
     def reduce_allreduce_sgd(self, partials: torch.Tensor, nparts: int, n_floats: int, grad_off: int,
                              param_off: int, lr_dev: torch.Tensor, algo: int = ALGO_AUTO,
-                             layout: int = LAYOUT_IDENTITY, slot: int = 0, stream=None) -> None:
+                             layout: int = LAYOUT_IDENTITY, slot: int = 0, stream=None,
+                             pack: torch.Tensor | None = None, bias_parts=None) -> None:
         """One kernel: grads[slice] = sum of ``nparts`` local partial vectors (fixed order), then
         params[slice] -= lr * mean_over_ranks(grads[slice]).  ``algo``: ALGO_PUSH (default; every
         rank stores flag-carrying words straight into its peers' staging lines) or ALGO_ONESHOT
         (flag round, then pull).  ``layout`` LAYOUT_CONV3X3_WGRAD: the partials are the conv2
         weight-gradient accumulator images (``n_floats`` = CONV3X3_WGRAD_IMAGE) and the slice is
-        net.2.weight followed by net.2.bias."""
+        net.2.weight followed by net.2.bias; with ``pack`` (the split bf16 tile images of
+        net.2.weight, native.conv3x3_pack_split_bytes) the same kernel also rewrites those tiles from
+        the updated weights; with ``bias_parts`` = (tensor, nsplit, nbx, H*W) from
+        native.linear_bwd_f32 the net.2.bias gradient is their exact-fp32 sum instead of the
+        accumulator images' bias column."""
+        if pack is not None or bias_parts is not None:
+            bp, ns, nb, hw = bias_parts if bias_parts is not None else (None, 0, 0, 0)
+            nat.check(self.lib.ddpb_reduce_allreduce_sgd_pack(
+                self._h, nat.ptr(partials), nparts, n_floats, grad_off, param_off, nat.ptr(lr_dev), algo,
+                layout, slot, nat.ptr(pack), nat.ptr(bp), ns, nb, hw, nat.stream_ptr(stream)),
+                "reduce_allreduce_sgd_pack")
+            return
         nat.check(self.lib.ddpb_reduce_allreduce_sgd(self._h, nat.ptr(partials), nparts, n_floats,
                                                      grad_off, param_off, nat.ptr(lr_dev), algo, layout,
                                                      slot, nat.stream_ptr(stream)),

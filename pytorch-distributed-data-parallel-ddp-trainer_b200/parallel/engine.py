@@ -103,8 +103,11 @@ class CpuDataParallel(_EngineBase):
 class B200DataParallel(_EngineBase):
     def __init__(self, rank: int, world_size: int, device, batch_cap: int, lr: float = 0.01,
                  use_graph: bool = True, algo: int = 0, timeout_ms: int | None = None,
-                 tail_update: str | None = None, multicast: bool | None = None):
-        """``tail_update`` selects how the last (conv1) bucket of the step is updated:
+                 tail_update: str | None = None, multicast: bool | None = None,
+                 precision: str | None = None):
+        """``precision``: "bf16x3" (default — the reference's numerics or better: 4-byte storage, split
+        hi+lo tensor-core operands >= TF32 for the convolutions, fp32 linear layer) or "bf16" (fast
+        mode), see SimpleCNNB200.  ``tail_update`` selects how the last (conv1) bucket of the step is updated:
         "push" (default) / "pull" = split-K reduce + all-reduce + SGD in one kernel with the push or
         pull exchange, "split" = separate reduce kernel followed by the generic bucket update.
         Environment override: DDPB_TAIL_UPDATE.  ``multicast`` (default: DDPB_NVLS=1) asks for the
@@ -148,7 +151,8 @@ class B200DataParallel(_EngineBase):
         params = self.comm.tensor(self.param_off, n)
         grads = [self.comm.tensor(off, n) for off in self.grad_off]
         self.model = SimpleCNNB200(batch_cap, self.device, params=params, grads=grads[0],
-                                   alt_grads=grads[1])
+                                   alt_grads=grads[1], precision=precision)
+        self.precision = self.model.precision
         self.model.lr_dev.fill_(self.lr)
         # gradient buckets = contiguous arena slices (whole float4; the arena tail is zero padding),
         # one per point of the backward pass at which a group of gradients becomes complete
@@ -160,6 +164,7 @@ class B200DataParallel(_EngineBase):
         assert all(s % 4 == 0 and s + m <= n for s, m in self.buckets)
         self.verify_replicas(rank, world_size, engine="b200", tail_update=self.tail_update, algo=self.algo,
                              multicast=self.comm.multicast, net2_order=self.net2_order,
+                             precision=self.precision,
                              ablate=",".join(sorted(self._ablate)))
 
         self.main = torch.cuda.Stream(self.device)
@@ -209,7 +214,10 @@ class B200DataParallel(_EngineBase):
         # three bucket updates + the weight re-pack.  "push" folds the conv2 reduce into its update
         # kernel as well (-1), "split" runs the conv1 reduce separately (+1).
         extra = {"push": -1, "pull": 0, "split": 1}[self.tail_update]
-        return self.model.launches_per_step(batch) + 4 + extra
+        # bf16x3 mode has no fl.weight re-pack kernel; the net.2 tile re-pack is inside the fused update
+        # ("push") or one more small kernel otherwise
+        repack = (0 if self.tail_update == "push" else 1) if self.model.x3 else 1
+        return self.model.launches_per_step(batch) + 3 + repack + extra
 
     @contextlib.contextmanager
     def _plain_launch(self):
@@ -259,7 +267,7 @@ class B200DataParallel(_EngineBase):
         with nvtx_range("bucket fl: all-reduce+sgd, re-pack"):
             if "fl" not in self._ablate:
                 self._update(self.bucket_fl, parity, 0, self.side)
-            if "pack" not in self._ablate:
+            if "pack" not in self._ablate and not m.x3:
                 m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
         # side2: conv2 weight gradient (shares the SMs with the data gradient below: 112 KB + 112 KB of
@@ -288,9 +296,12 @@ class B200DataParallel(_EngineBase):
                 self.comm.reduce_allreduce_sgd(
                     m.scr_w2, nparts2, CONV3X3_WGRAD_IMAGE, self.grad_off[parity] + s2 * 4,
                     self.param_off + s2 * 4, m.lr_dev, algo=ALGO_PUSH, layout=LAYOUT_CONV3X3_WGRAD,
-                    slot=2, stream=self.side2)
+                    slot=2, stream=self.side2, pack=m.w2_packed,  # bf16x3: tiles rewritten in the same kernel
+                    bias_parts=(m.db2_part, *m.db2_extent, IMG_H * IMG_W) if m.x3 else None)
             elif "conv2" not in self._ablate:
                 self._update(self.bucket_conv2, parity, 2, self.side2)
+                if m.x3:
+                    m.pack_weights(self.side2)  # new net.2.weight -> split tiles for the next step
         self._ev_join2.record(self.side2)
         with nvtx_range("bwd conv1 wgrad + bucket net.0"):
             if self.tail_update == "split":

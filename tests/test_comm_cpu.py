@@ -5,8 +5,8 @@ import torch
 
 def test_unsupported_world_size_is_a_clear_error():
     from ddp_b200.parallel.comm import SUPPORTED_WORLD_SIZES, SymmetricComm
-    assert SUPPORTED_WORLD_SIZES == (1, 2, 4, 8)
-    for rank, world in ((0, 3), (0, 16), (2, 2), (-1, 2)):
+    assert SUPPORTED_WORLD_SIZES == tuple(range(1, 9))  # any size up to one NVSwitch node of 8
+    for rank, world in ((0, 9), (0, 16), (2, 2), (-1, 2), (0, 0)):
         with pytest.raises(ValueError, match="world sizes"):
             SymmetricComm(rank, world, 1024)
 

@@ -15,13 +15,21 @@ def cuda():
     return torch.device("cuda", 0)
 
 
+# Gradient error budgets against the full-fp32 oracle (cuDNN/cuBLAS with TF32 off), as a fraction of
+# max |gradient|.  bf16x3 (default mode): every op carries >= 16 operand bits except conv1's forward,
+# which is a TF32 GEMM like the reference's (measured: profiles/precision.md; the bound leaves ~4x).
+# bf16 (fast mode): 8-bit operands and activations.
+GRAD_BUDGET = {"bf16x3": 4e-3, "bf16": 5e-2}
+
+
 # 4096 = the large-batch benchmark configuration: many tiles per CTA in every persistent kernel
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
 @pytest.mark.parametrize("batch", [64, 4096])
-def test_gradients_match_oracle(cuda, batch):
+def test_gradients_match_oracle(cuda, batch, precision):
     from ddp_b200.models.simple_cnn import SimpleCNN, SimpleCNNB200
     torch.manual_seed(0)
     oracle = SimpleCNN(device=cuda)
-    gpu = SimpleCNNB200(batch_cap=batch, device=cuda, init=False)
+    gpu = SimpleCNNB200(batch_cap=batch, device=cuda, init=False, precision=precision)
     gpu.load_state_dict(oracle.state_dict())
     x = torch.rand(batch, 1, 28, 28, device=cuda)
     y = torch.randint(0, 10, (batch,), device=cuda)
@@ -29,23 +37,25 @@ def test_gradients_match_oracle(cuda, batch):
     for _ in range(3):  # repeated: a race between pipeline roles rarely shows on the first pass
         got = gpu.forward_backward(x, y)
     torch.cuda.synchronize()
-    assert abs(got.item() - want.item()) < 5e-3
+    assert abs(got.item() - want.item()) < (5e-4 if precision == "bf16x3" else 5e-3)
     for name in ("fl.bias", "fl.weight", "net.2.bias", "net.2.weight", "net.0.bias", "net.0.weight"):
         g, w = gpu.arena.grad_view(name), oracle.arena.grad_view(name)
         scale = w.abs().max().item()
         err = (g - w).abs().max().item()
-        assert err <= 5e-2 * scale + 1e-6, (name, err, scale)  # bf16 activations + tf32 conv1
+        print(f"[grad-vs-fp32] {precision} B={batch} {name}: err/scale = {err / scale:.2e}")
+        assert err <= GRAD_BUDGET[precision] * scale + 1e-7, (name, err, scale)
 
 
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_training_tracks_oracle_and_short_batches(cuda, use_graph):
+def test_training_tracks_oracle_and_short_batches(cuda, use_graph, precision):
     from ddp_b200.models.simple_cnn import SimpleCNN
     from ddp_b200.parallel.engine import B200DataParallel
     torch.manual_seed(1)
     oracle = SimpleCNN(device=cuda)
     lr = 0.01  # the reference's value; a larger one makes this tiny problem unstable, which amplifies
     # rounding differences into trajectory differences and tests chaos rather than the kernels
-    eng = B200DataParallel(0, 1, cuda, batch_cap=32, lr=lr, use_graph=use_graph)
+    eng = B200DataParallel(0, 1, cuda, batch_cap=32, lr=lr, use_graph=use_graph, precision=precision)
     eng.model.load_state_dict(oracle.state_dict())
     init = {n: oracle.arena.view(n).detach().clone() for n in ("fl.weight", "net.2.weight", "net.0.weight")}
     torch.manual_seed(2)
@@ -61,17 +71,19 @@ def test_training_tracks_oracle_and_short_batches(cuda, use_graph):
         losses_o.append(lo.item())
         losses_g.append(eng.read_loss())
     eng.synchronize()
+    loss_tol = 2e-3 if precision == "bf16x3" else 2e-2
     for a, b in zip(losses_o, losses_g):
-        assert abs(a - b) < 2e-2 * max(1.0, abs(a)), (losses_o, losses_g)
+        assert abs(a - b) < loss_tol * max(1.0, abs(a)), (losses_o, losses_g)
     assert losses_g[-1] < losses_g[0]
-    # drift check (the precision contract is per-op, tests/test_kernels_gpu.py): after 16 steps the
-    # bf16/tf32 tensor-core trajectory must still be close to the fp32 oracle's, either relative to
-    # the accumulated update or in absolute terms
+    # drift after 16 steps, relative to the accumulated update of the fp32 oracle's trajectory
+    # (the per-op precision contract is tests/test_precision_gpu.py)
+    drift_tol = 0.02 if precision == "bf16x3" else 0.15
     for name in ("fl.weight", "net.2.weight", "net.0.weight"):
         p, q = eng.model.arena.view(name), oracle.arena.view(name).detach()
         rel = ((p - q).norm() / (q - init[name]).norm()).item()
         mx = (p - q).abs().max().item()
-        assert rel < 0.15 or mx < 5e-3, (name, rel, mx)
+        print(f"[drift] {precision} graph={use_graph} {name}: rel {rel:.2e} max {mx:.2e}")
+        assert rel < drift_tol or mx < (2e-4 if precision == "bf16x3" else 5e-3), (name, rel, mx)
     eng.close()
 
 
