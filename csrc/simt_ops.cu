@@ -183,6 +183,9 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
   constexpr int PF = 4;          // gradient vectors kept in flight per thread
   extern __shared__ float xs[];  // [kConv1Group][CIN0][PHW]
   __shared__ float red[8][NV];
+  // launched through launch_k in the step (programmatic dependent launch): nothing the predecessor
+  // wrote (dact) may be read before this; a no-op for plain launches
+  pdl_sync();
   const int chunk = blockIdx.y;
   static_assert(NV == 80, "warp_reduce80 expects 8*(CIN0*9) + 8 == 80 accumulators (CIN0 == 1)");
   float acc[NV];  // [c*NW + j] weight taps, then [8*NW + c] bias

@@ -231,12 +231,14 @@ def scenario_dp_equiv():
         eng.step(xs[it, rank, :bb], ys[it, rank, :bb])
         lg = torch.tensor([eng.read_loss()], device=dev)
         dist.all_reduce(lg)
-        assert abs(lg.item() / world - lo.item()) < 2e-2 * max(1.0, abs(lo.item())), (it, lg.item() / world, lo.item())
+        assert abs(lg.item() / world - lo.item()) < 2e-3 * max(1.0, abs(lo.item())), (it, lg.item() / world, lo.item())
     eng.synchronize()
     dist.all_gather(gathered, eng.flat_params.clone())
     assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas diverged bitwise"
     diff = (eng.flat_params[:520586] - oracle.arena.params.detach()[:520586]).abs().max().item()
-    assert diff < 5e-3, diff  # bf16/tf32 tensor-core path vs fp32 oracle after 12 steps
+    if rank == 0:
+        print(f"dp_equiv: world {world} max |param - fp32 oracle| after 12 steps = {diff:.3e}", flush=True)
+    assert diff < 5e-4, diff  # reference-precision (bf16x3) path vs the full-fp32 oracle after 12 steps
     eng.close()
     dist.barrier()
     if rank == 0:

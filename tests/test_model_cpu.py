@@ -127,3 +127,34 @@ def test_staged_backward_equals_plain_backward():
     for b in m.buckets():
         covered[b.start:b.start + b.numel] = True
     assert torch.equal(m.arena.grads[covered], g0[covered])
+
+
+def test_every_kernel_launched_as_programmatic_dependent_waits_for_its_predecessor():
+    """launch_k() (csrc/launch.cuh) launches with the programmatic-stream-serialization attribute: such
+    a kernel may start while its stream predecessor is still running and MUST execute
+    griddepcontrol.wait (pdl_sync / pdl_wait) before touching anything the predecessor wrote.  A kernel
+    without it silently races (found once: the exact-fp32 conv1 weight gradient read dact1 early and
+    the replicas drifted from the single-GPU trajectory after a few steps).  Checked on the sources."""
+    import glob
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    srcs = {p: open(p).read() for p in glob.glob(os.path.join(root, "csrc", "*.cu"))}
+    everything = "\n".join(srcs.values())
+    launched = set(re.findall(r"launch_k\(\s*([A-Za-z_0-9]+)\s*[<,]", everything))
+    # `auto kern = some_kernel<...>; launch_k(kern, ...)`
+    launched |= set(re.findall(r"auto kern = ([A-Za-z_0-9]+)<", everything))
+    launched.discard("kern")
+    assert len(launched) >= 15, sorted(launched)
+    missing = []
+    for name in sorted(launched):
+        m = re.search(r"__global__[^;{]*?\b" + name + r"\s*\([^)]*\)\s*\{", everything, re.S)
+        assert m, f"definition of {name} not found"
+        depth, i = 1, m.end()
+        while depth and i < len(everything):
+            depth += {"{": 1, "}": -1}.get(everything[i], 0)
+            i += 1
+        body = everything[m.end():i]
+        if "pdl_sync()" not in body and "pdl_wait()" not in body:
+            missing.append(name)
+    assert not missing, f"launched through launch_k without griddepcontrol.wait: {missing}"

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NGPU = torch.cuda.device_count() if torch.cuda.is_available() else 0
-WORLDS = [w for w in (2, 4, 8) if w <= NGPU]
+WORLDS = [w for w in (2, 3, 4, 6, 8) if w <= NGPU]  # odd and non-power-of-two sizes included
 
 
 def _torchrun(world, script_args, cwd=None, env=None, timeout=600):
