@@ -1114,6 +1114,9 @@ int ddpb_linear_bwd_f32(const void* act, const float* dlogits, const float* Wt, 
                           ips * 10 * sizeof(float), st, static_cast<const float4*>(act), dlogits, Wt,
                           static_cast<float4*>(dact), scratch, bias_part, g, C, ips));
   }
+  // dW == NULL: the per-split partials stay in scratch[*nsplit_out][nout*C*H*W] and the caller sums them
+  // with ddpb_reduce_partials where it suits (the step engine does it on the bucket's side stream)
+  if (dW == nullptr) return 0;
   return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
 }
 
@@ -1185,7 +1188,9 @@ const char* ddpb_error_string(int code) {
 //  * The first call on each device looks the array's device address up (cudaGetSymbolAddress;
 //    the array's name is only a host-side stand-in in host code, never a pointer a kernel may
 //    be given).  That look-up is set-up work: make the first call on a device before starting
-//    any stream capture on it.
+//    any stream capture on it.  Two host threads that make that first call on one device at the
+//    same time both store the same address into the per-device slot: harmless, but the slot is not
+//    otherwise synchronised, so do not rely on more than that.
 //  * No call allocates or frees anything (no cudaMalloc/cudaFree, no library that would).
 //  * All calls on a device share the one array, and it keeps whatever the previous call left.
 //    Nothing in it has to start at zero: every partial slot the reduction reads is written by the

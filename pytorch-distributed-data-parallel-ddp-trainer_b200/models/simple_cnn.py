@@ -277,16 +277,26 @@ class SimpleCNNB200(_ModelBase):
                          self.loss, NCLS, b, stream, dl_packed=self.dl_packed)
         return self.loss
 
-    def backward_head(self, batch: int, stream=None, parity: int = 0):
-        """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel)."""
+    def backward_head(self, batch: int, stream=None, parity: int = 0, defer_reduce: bool = False):
+        """Linear-layer backward: completes bucket 0 (fl.weight; fl.bias came from the loss kernel).
+        bf16x3 mode with ``defer_reduce``: the fl.weight gradient stays as per-image-split partials and
+        backward_head_reduce() sums them later (the engine does it on the bucket's own stream, off the
+        critical path — only dact2 is needed by what follows on the main stream)."""
         gs = self.grad_sets[parity]
         if self.x3:
             self.db2_extent = self.nat.linear_bwd_f32(
-                self.act2, self.dlogits, self.wf, self.dact2, gs["wf"], self.lin_bwd_scr, NCLS, C2, batch,
-                self.batch_cap, IMG_H, IMG_W, stream, split_out=True, bias_part=self.db2_part)
+                self.act2, self.dlogits, self.wf, self.dact2, None if defer_reduce else gs["wf"],
+                self.lin_bwd_scr, NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream, split_out=True,
+                bias_part=self.db2_part)
             return
         self.nat.linear_bwd_tc(self.act2, self.dl_packed, self.lin_packed, self.dact2, gs["wf"],
                                NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
+
+    def backward_head_reduce(self, stream=None, parity: int = 0) -> None:
+        """Fixed-order sum of the deferred fl.weight gradient partials into the gradient arena."""
+        if self.x3:
+            self.nat.reduce_partials(self.lin_bwd_scr, self.db2_extent[0], NCLS * FEATURES,
+                                     self.grad_sets[parity]["wf"], stream)
 
     def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):
         """conv2 weight + bias gradient (independent of the dgrad chain: may run on its own stream)."""

@@ -74,6 +74,7 @@ _SIGNATURES = {
     "ddpb_conv1_wgrad_f32": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv1_wgrad_f32_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_zero_tail_rows": (I, [P, I, I, I, I, I, P]),
+    "ddpb_reduce_partials": (I, [P, I, LL, P, P]),
     # fp32 planes, tf32 tensor-core operands: forward / data-gradient building blocks
     "ddpb_conv1_fwd_tc_f32": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_pack_tf32_bytes": (c_size_t, [I, I]),
@@ -413,6 +414,11 @@ def linear_bwd_f32(act, dlogits, Wfl, dact, dW, scr, nout, C, batch, batch_cap, 
                                     ctypes.byref(ns), ctypes.byref(nb), stream_ptr(stream)),
           "linear_bwd_f32")
     return ns.value, nb.value
+
+
+def reduce_partials(part, nparts: int, n: int, out, stream=None):
+    """out[i] = sum_p part[p*n + i], fixed order."""
+    check(lib().ddpb_reduce_partials(ptr(part), nparts, n, ptr(out), stream_ptr(stream)), "reduce_partials")
 
 
 def conv1_wgrad_f32_scratch_bytes(cin, cout) -> int:

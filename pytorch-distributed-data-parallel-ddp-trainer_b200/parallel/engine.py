@@ -260,11 +260,12 @@ class B200DataParallel(_EngineBase):
         with nvtx_range("fwd+loss"):
             m.forward_loss(x, y, b, main, parity, pack=False)
         with nvtx_range("bwd linear"):
-            m.backward_head(b, main, parity)
+            m.backward_head(b, main, parity, defer_reduce=True)
         self._ev_fork.record(main)
         self.side.wait_event(self._ev_fork)
         self.side2.wait_event(self._ev_fork)
         with nvtx_range("bucket fl: all-reduce+sgd, re-pack"):
+            m.backward_head_reduce(self.side, parity)   # bf16x3: split partials -> fl.weight gradient
             if "fl" not in self._ablate:
                 self._update(self.bucket_fl, parity, 0, self.side)
             if "pack" not in self._ablate and not m.x3:

@@ -93,19 +93,72 @@ def synthetic_mnist(n: int = 60000, seed: int = 0, h: int = 28, w: int = 28,
     return ImageDataset(images, labels.to(torch.int64), source=f"synthetic(seed={seed})")
 
 
-def load_mnist(root: str = "./data", train: bool = True, synthetic_fallback: bool = True,
-               synthetic_size: int | None = None) -> ImageDataset:
-    """MNIST from ``<root>/MNIST/raw`` (plain or .gz IDX files), else the synthetic stand-in."""
+def _find_idx(raw: str, train: bool):
     img_name, lab_name = _IDX_FILES[train]
-    raw = os.path.join(root, "MNIST", "raw")
     for ext in ("", ".gz"):
         ip, lp = os.path.join(raw, img_name + ext), os.path.join(raw, lab_name + ext)
         if os.path.exists(ip) and os.path.exists(lp):
-            return ImageDataset(read_idx(ip), read_idx(lp).to(torch.int64), source=ip)
+            return ip, lp
+    return None
+
+
+def _try_download(root: str, train: bool) -> str | None:
+    """What the reference does (reference data.py:11-14: ``datasets.MNIST(..., download=True)``):
+    let torchvision fetch the files into ``<root>/MNIST/raw``.  Returns None on success, else the
+    reason (no torchvision, no network, ...).  DDP_B200_NO_DOWNLOAD=1 skips the attempt."""
+    if os.environ.get("DDP_B200_NO_DOWNLOAD", "0") == "1":
+        return "download disabled by DDP_B200_NO_DOWNLOAD=1"
+    try:
+        import socket
+        from torchvision import datasets
+        prev = socket.getdefaulttimeout()
+        socket.setdefaulttimeout(float(os.environ.get("DDP_B200_DOWNLOAD_TIMEOUT", "10")))
+        try:
+            datasets.MNIST(root=root, train=train, download=True)
+        finally:
+            socket.setdefaulttimeout(prev)
+        return None
+    except Exception as e:  # ImportError, URLError, RuntimeError("Error downloading ...")
+        return f"{type(e).__name__}: {str(e).splitlines()[0][:160] if str(e) else ''}"
+
+
+def load_mnist(root: str = "./data", train: bool = True, synthetic_fallback: bool = True,
+               synthetic_size: int | None = None, download: bool = True, verbose: bool = True) -> ImageDataset:
+    """MNIST for training, in the order the reference would get it (reference data.py:11-14):
+
+    1. the IDX files torchvision keeps under ``<root>/MNIST/raw`` (plain or .gz), if present;
+    2. else, with ``download`` (default), torchvision's own download into that directory;
+    3. else — only with ``synthetic_fallback`` — a deterministic synthetic stand-in of the same
+       shape, announced with a loud warning (it is NOT MNIST; it exists so that the offline
+       benchmark boxes and the tests can run: BASELINE.json).
+
+    ``verbose`` prints which source was used (``ImageDataset.source`` records it either way)."""
+    import warnings
+    raw = os.path.join(root, "MNIST", "raw")
+    found = _find_idx(raw, train)
+    why = None
+    if found is None and download:
+        why = _try_download(root, train)
+        if why is None:
+            found = _find_idx(raw, train)
+            why = None if found else "torchvision reported success but the IDX files are missing"
+    if found is not None:
+        ip, lp = found
+        ds = ImageDataset(read_idx(ip), read_idx(lp).to(torch.int64), source=ip)
+        if verbose:
+            print(f"[data] MNIST {'train' if train else 'test'} set: {len(ds)} images from {ip}", flush=True)
+        return ds
     if not synthetic_fallback:
-        raise FileNotFoundError(f"no MNIST IDX files under {raw} (no network to download them)")
+        raise FileNotFoundError(f"no MNIST IDX files under {raw} and they could not be downloaded ({why})")
     n = synthetic_size or int(os.environ.get("DDP_B200_SYNTHETIC_SIZE", 60000 if train else 10000))
-    return synthetic_mnist(n=n, seed=0 if train else 1)
+    ds = synthetic_mnist(n=n, seed=0 if train else 1)
+    msg = (f"no MNIST files under {raw} and no download ({why}): training on {n} SYNTHETIC MNIST-shaped "
+           f"images ({ds.source}), not on MNIST.  Put the four IDX files there, or pass "
+           f"synthetic_fallback=False to make this an error.")
+    warnings.warn(msg, RuntimeWarning, stacklevel=2)
+    if verbose:
+        print(f"[data] WARNING: {msg}", flush=True)
+    return ds
 
 
 # ----------------------------------------------------------------------------- batch loaders
@@ -161,6 +214,7 @@ def get_dataloader(batch_size: int, world_size: int, rank: int, device="cpu", ro
                    dataset: ImageDataset | None = None, target=None):
     """Same call shape and return value as the reference (reference data.py:6,27):
     ``(dataloader, sampler)``; call ``sampler.set_epoch(e)`` before iterating epoch ``e``."""
-    ds = dataset if dataset is not None else load_mnist(root=root, train=True)
+    # rank 0 announces the source; the other ranks load (or download) quietly
+    ds = dataset if dataset is not None else load_mnist(root=root, train=True, verbose=(rank == 0))
     sampler = ShardedSampler(len(ds), num_replicas=world_size, rank=rank, shuffle=True)
     return BatchLoader(ds, sampler, batch_size, device=device, target=target), sampler

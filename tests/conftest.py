@@ -9,6 +9,10 @@ import sys
 
 import pytest
 
+# the boxes the tests run on have no network: skip torchvision's download attempt (tests that want it
+# clear the variable themselves)
+os.environ.setdefault("DDP_B200_NO_DOWNLOAD", "1")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -51,3 +51,29 @@ def test_shards_partition_the_epoch():
 def test_bad_rank():
     with pytest.raises(ValueError):
         ShardedSampler(10, 2, 2)
+
+
+def test_load_mnist_names_its_source_and_warns_on_the_synthetic_fallback(tmp_path, capsys):
+    """reference data.py:11-14 trains on MNIST (download=True).  Offline there is a synthetic stand-in,
+    but never silently: the loader prints which source it used and warns loudly on the fallback."""
+    import warnings
+
+    import pytest
+    import torch
+    from ddp_b200.utils.data import load_mnist, synthetic_mnist, write_mnist_idx
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        ds = load_mnist(root=str(tmp_path), synthetic_size=64)
+    assert ds.source.startswith("synthetic") and len(ds) == 64
+    assert any("SYNTHETIC" in str(x.message) and "not on MNIST" in str(x.message) for x in w)
+    assert "WARNING" in capsys.readouterr().out
+    with pytest.raises(FileNotFoundError):
+        load_mnist(root=str(tmp_path), synthetic_fallback=False)
+    # real IDX files where torchvision keeps them: used, and announced
+    write_mnist_idx(str(tmp_path), synthetic_mnist(n=32, seed=3))
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        ds = load_mnist(root=str(tmp_path))
+    assert not w and len(ds) == 32 and "train-images-idx3-ubyte" in ds.source
+    assert "32 images from" in capsys.readouterr().out
+    assert torch.equal(ds.images, synthetic_mnist(n=32, seed=3).images)
