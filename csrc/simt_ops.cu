@@ -644,10 +644,26 @@ __global__ void zero_tail_rows_kernel(uint4* __restrict__ planes, int nplanes, G
 //
 // forward: same decomposition as linear_fwd_kernel (a thread owns one 4-channel vector of a pixel
 // for 8 images), partial[s][img][j].
+// Optional fused loss tail (small batches, where a separate 9 us loss kernel is a tenth of the step):
+// the block that finishes last (ticket counter, like softmax_xent_kernel) adds the slices and the bias
+// in slice order and computes loss, dlogits and the bias gradient for the whole batch — the same
+// arithmetic as softmax_xent_kernel with its own fixed summation order (deterministic; the two routes
+// agree to fp32 rounding).  Calls on one device must not overlap (one ticket word).
+constexpr int kFusedXentMaxBatch = 128;
+static __device__ unsigned int g_linfwd_ticket;
+struct XentArgs {
+  const float* bias;
+  const long long* labels;
+  float* logits;
+  float* dlogits;
+  float* dbias;
+  float* loss;
+};
+
 template <int NOUT, int IMG>
 __global__ void __launch_bounds__(256, 1)
 linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ W,
-                      float* __restrict__ partial, Geom g, int C, int vec_per_slice) {
+                      float* __restrict__ partial, Geom g, int C, int vec_per_slice, XentArgs xe) {
   pdl_sync();
   __shared__ float red[8][IMG * NOUT];
   const int HW = g.H * g.W;
@@ -702,6 +718,66 @@ linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
 #pragma unroll
     for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][t];
     partial[((long long)blockIdx.x * g.batch + img) * NOUT + j] = s;
+  }
+  if (xe.logits == nullptr) return;
+  // ---- fused loss tail
+  __shared__ bool is_last;
+  __shared__ float zs[kFusedXentMaxBatch * NOUT];
+  __shared__ float ls[kFusedXentMaxBatch];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int nblk = gridDim.x * gridDim.y;
+    const unsigned int t = atomicAdd(&g_linfwd_ticket, 1u);
+    is_last = (t == nblk - 1);
+    if (is_last) g_linfwd_ticket = 0;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int S = gridDim.x, batch = g.batch;
+  const int npair = batch * NOUT;
+  for (int p = threadIdx.x; p < npair; p += blockDim.x) {
+    float z = 0.f;
+    for (int sl = 0; sl < S; ++sl) z += __ldcg(partial + (long long)sl * npair + p);
+    z += xe.bias[p % NOUT];
+    zs[p] = z;
+    xe.logits[p] = z;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < batch; i += blockDim.x) {
+    const float inv = 1.0f / static_cast<float>(batch);
+    float z[NOUT];
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) z[j] = zs[i * NOUT + j];
+    float m = z[0];
+#pragma unroll
+    for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
+    float se = 0.f;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) se += expf(z[j] - m);
+    const float lse = m + logf(se);
+    const int y = static_cast<int>(xe.labels[i]);
+    float lsum = 0.f;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      const float pr = expf(z[j] - lse);
+      const float d = (pr - (j == y ? 1.f : 0.f)) * inv;
+      xe.dlogits[i * NOUT + j] = d;
+      zs[i * NOUT + j] = d;
+      if (j == y) lsum = lse - z[j];
+    }
+    ls[i] = lsum;
+  }
+  __syncthreads();
+  if (threadIdx.x < NOUT) {  // bias gradient: column sums in image order
+    float sacc = 0.f;
+    for (int i = 0; i < batch; ++i) sacc += zs[i * NOUT + threadIdx.x];
+    xe.dbias[threadIdx.x] = sacc;
+  } else if (threadIdx.x == 32) {
+    float sacc = 0.f;
+    for (int i = 0; i < batch; ++i) sacc += ls[i];
+    xe.loss[0] = sacc / static_cast<float>(batch);
   }
 }
 
@@ -1013,7 +1089,7 @@ int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out,
 
 static int linear_bwd_imgs_per_split(int batch) {
   // enough splits to fill the GPU at small batch, few enough that partial traffic stays small
-  if (batch <= 64) return 16;
+  if (batch <= 64) return 16;  // (8 was tried: 392 blocks no longer fit one wave, +8 us on the step)
   if (batch <= 512) return 32;
   return 128;
 }
@@ -1072,7 +1148,24 @@ int ddpb_linear_fwd_f32(const void* act, const float* Wt, float* partial, int* S
   if (S_out) *S_out = S;
   return static_cast<int>(launch_k(linear_fwd_f32_kernel<10, 8>, dim3(S, groups), dim3(256), 0,
                                    static_cast<cudaStream_t>(stream), static_cast<const float4*>(act),
-                                   Wt, partial, g, C, per));
+                                   Wt, partial, g, C, per, XentArgs{}));
+}
+// Linear forward with the loss fused into its tail (what ddpb_linear_fwd_f32 followed by
+// ddpb_softmax_xent compute, one launch): batch <= ddpb_linear_fwd_f32_xent_max_batch().
+int ddpb_linear_fwd_f32_xent_max_batch() { return kFusedXentMaxBatch; }
+int ddpb_linear_fwd_f32_xent(const void* act, const float* Wt, float* partial, const float* bias,
+                             const void* labels, float* logits, float* dlogits, float* dbias, float* loss,
+                             int nout, int C, int batch, int batch_cap, int H, int W, void* stream) {
+  if (nout != 10 || (C % 4) != 0 || logits == nullptr) return DDPB_ERR_SHAPE;
+  if (batch > kFusedXentMaxBatch) return DDPB_ERR_LIMIT;
+  const Geom g = make_geom(batch, batch_cap, H, W);
+  const int nvec = (C / 4) * H * W;
+  int S, per, groups;
+  linear_fwd_f32_geom(batch, nvec, S, per, groups);
+  XentArgs xe{bias, static_cast<const long long*>(labels), logits, dlogits, dbias, loss};
+  return static_cast<int>(launch_k(linear_fwd_f32_kernel<10, 8>, dim3(S, groups), dim3(256), 0,
+                                   static_cast<cudaStream_t>(stream), static_cast<const float4*>(act),
+                                   Wt, partial, g, C, per, xe));
 }
 // act: fp32 planes.  dact: split planes (split_out != 0: 2*C/8 bf16 planes) or fp32 planes rounded
 // to tf32 (C/4 planes).  bias_part (optional, ddpb_linear_bwd_f32_bias_part_bytes bytes): receives the

@@ -165,6 +165,15 @@ int ddpb_conv1_wgrad_f32_partials(const void* dact_f32_planes, const float* x, f
 size_t ddpb_linear_fwd_f32_scratch_bytes(int nout, int C, int batch_cap, int H, int W);
 int ddpb_linear_fwd_f32(const void* act_f32_planes, const float* W_fl, float* partial, int* S_out,
                         int nout, int C, int batch, int batch_cap, int H, int W, void* stream);
+/* Forward with the loss fused into its tail (one launch instead of ddpb_linear_fwd_f32 +
+ * ddpb_softmax_xent): the last block to finish adds the slices and computes loss / dlogits / dbias.
+ * batch <= ddpb_linear_fwd_f32_xent_max_batch() (128), else DDPB_ERR_LIMIT.  Calls on one device must
+ * not overlap.  reference model.py:16,19 + train_ddp.py:40,198. */
+int ddpb_linear_fwd_f32_xent_max_batch(void);
+int ddpb_linear_fwd_f32_xent(const void* act_f32_planes, const float* W_fl, float* partial,
+                             const float* bias, const void* labels_i64, float* logits, float* dlogits,
+                             float* dbias, float* loss, int nout, int C, int batch, int batch_cap, int H,
+                             int W, void* stream);
 size_t ddpb_linear_bwd_f32_bias_part_bytes(int C, int batch_cap, int H, int W);
 int ddpb_linear_bwd_f32(const void* act_f32_planes, const float* dlogits, const float* W_fl,
                         void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,

@@ -68,6 +68,8 @@ _SIGNATURES = {
     "ddpb_conv3x3_wgrad_split_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
     "ddpb_linear_fwd_f32_scratch_bytes": (c_size_t, [I, I, I, I, I]),
     "ddpb_linear_fwd_f32": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
+    "ddpb_linear_fwd_f32_xent_max_batch": (I, []),
+    "ddpb_linear_fwd_f32_xent": (I, [P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_linear_bwd_f32_bias_part_bytes": (c_size_t, [I, I, I, I]),
     "ddpb_linear_bwd_f32": (I, [P, P, P, P, P, P, I, I, I, I, I, I, I, P, POINTER(c_int), POINTER(c_int), P]),
     "ddpb_conv1_wgrad_f32_scratch_bytes": (c_size_t, [I, I]),
@@ -397,6 +399,19 @@ def linear_fwd_f32(act, Wfl, partial, nout, C, batch, batch_cap, H, W, stream=No
     check(lib().ddpb_linear_fwd_f32(ptr(act), ptr(Wfl), ptr(partial), ctypes.byref(s), nout, C, batch,
                                     batch_cap, H, W, stream_ptr(stream)), "linear_fwd_f32")
     return s.value
+
+
+def linear_fwd_f32_xent_max_batch() -> int:
+    return int(lib().ddpb_linear_fwd_f32_xent_max_batch())
+
+
+def linear_fwd_f32_xent(act, Wfl, partial, bias, labels, logits, dlogits, dbias, loss, nout, C, batch,
+                        batch_cap, H, W, stream=None):
+    """fp32 linear forward with the softmax cross-entropy loss, dlogits and dbias computed in the
+    tail of the same kernel (small batches: one launch less on the step's critical path)."""
+    check(lib().ddpb_linear_fwd_f32_xent(ptr(act), ptr(Wfl), ptr(partial), ptr(bias), ptr(labels),
+                                         ptr(logits), ptr(dlogits), ptr(dbias), ptr(loss), nout, C, batch,
+                                         batch_cap, H, W, stream_ptr(stream)), "linear_fwd_f32_xent")
 
 
 def linear_bwd_f32_bias_part_bytes(C, batch_cap, H, W) -> int:

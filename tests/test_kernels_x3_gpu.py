@@ -297,3 +297,32 @@ def test_conv3x3_fwd_dgrad_tf32(nat, batch, cap):
     want = F.conv_transpose2d(dout.double(), _t(w).double(), padding=1) * (a > 0)
     _check("conv3x3_dgrad_tf32", _lay().planes_to_nchw(din, batch, 32, H, W), want, 1e-5)
     assert _lay().border_rows_are_zero(out, batch, H, W) and _lay().border_rows_are_zero(din, batch, H, W)
+
+
+@pytest.mark.parametrize("batch,cap", [(1, 1), (3, 3), (64, 64), (37, 64), (128, 128)])
+def test_linear_fwd_with_fused_loss_matches_the_two_kernel_route(nat, batch, cap):
+    """ddpb_linear_fwd_f32_xent (loss in the tail of the linear forward) against ddpb_linear_fwd_f32 +
+    ddpb_softmax_xent and against an fp64 oracle; repeated, because the ticket word must reset itself."""
+    torch.manual_seed(40)
+    C, K = 64, 64 * H * W
+    act = torch.relu(torch.randn(batch, C, H, W, device="cuda"))
+    Wfl = torch.randn(10, K, device="cuda") * 0.01
+    bfl = torch.randn(10, device="cuda") * 0.1
+    y = torch.randint(0, 10, (batch,), device="cuda")
+    act_p = _lay().nchw_to_planes(act, cap, dtype=F32)
+    part = nat.scratch(nat.linear_fwd_f32_scratch_bytes(10, C, cap, H, W))
+    S = nat.linear_fwd_f32(act_p, Wfl, part, 10, C, batch, cap, H, W)
+    ref = [torch.zeros(batch, 10, device="cuda"), torch.zeros(batch, 10, device="cuda"),
+           torch.zeros(10, device="cuda"), torch.zeros(1, device="cuda")]
+    nat.softmax_xent(part, S, bfl, y, *ref, 10, batch)
+    z = act.double().reshape(batch, K) @ Wfl.double().t() + bfl.double()
+    for rep in range(3):
+        got = [torch.full((batch, 10), float("nan"), device="cuda"), torch.full((batch, 10), float("nan"), device="cuda"),
+               torch.full((10,), float("nan"), device="cuda"), torch.full((1,), float("nan"), device="cuda")]
+        nat.linear_fwd_f32_xent(act_p, Wfl, part, bfl, y, *got, 10, C, batch, cap, H, W)
+        torch.cuda.synchronize()
+        for name, g, r in zip(("logits", "dlogits", "dbias", "loss"), got, ref):
+            assert torch.allclose(g, r, rtol=1e-5, atol=1e-6 * max(1.0, r.abs().max().item())), (rep, name)
+        _check("fused logits", got[0], z, 2e-6)
+        assert abs(got[3].item() - F.cross_entropy(z, y).item()) < 2e-6 * max(1.0, abs(got[3].item()))
+    assert nat.linear_fwd_f32_xent_max_batch() == 128
