@@ -16,6 +16,8 @@
 // Every kernel is a template over the plane formats of layout.cuh.  The reference-precision mode
 // runs them on split planes (x = hi + lo, three MMAs per K step, "bf16x3"): at least the operand
 // precision of the TF32 convolutions cuDNN runs for the reference, fp32 accumulation.
+#include <stdlib.h>
+
 #include "ptx.cuh"
 #include "layout.cuh"
 #include "api_internal.cuh"
@@ -653,6 +655,22 @@ pack_conv3x3_tf32_kernel(const float* __restrict__ w, float* __restrict__ fwd, f
 
 static unsigned long long* g_prof = nullptr;  // set by ddpb_set_prof_buffer (tuning only)
 
+// Backward grids.  The split-plane data-gradient and weight-gradient CTAs each take ~220 KB of shared
+// memory, so two of them cannot share an SM the way the bf16 ones do.  Launched on different streams
+// with full grids they serialise; with each capped to about half of the SMs they run side by side on
+// disjoint SMs.  DDPB_BWD_GRID (CTAs per kernel, 0 = all SMs) overrides the per-mode default.
+static int bwd_grid_cap(int sms, bool split) {
+  static int env = -1;
+  if (env < 0) {
+    const char* e = getenv("DDPB_BWD_GRID");
+    env = e ? atoi(e) : 0;
+    if (env < 0) env = 0;
+  }
+  if (env > 0) return env < sms ? env : sms;
+  (void)split;
+  return sms;
+}
+
 template <class KernT>
 static int configure_smem(KernT kern, uint32_t bytes, bool (&configured)[64]) {
   int dev = 0;
@@ -675,7 +693,8 @@ static int launch_conv(const void* in, const void* w, const float* bias, const v
   static bool configured[64] = {};
   const int rc = configure_smem(kern, S::total, configured);
   if (rc != 0) return rc;
-  const int grid = g.ntiles < num_sms ? g.ntiles : num_sms;
+  const int cap = MODE == 1 ? bwd_grid_cap(num_sms, P::kSets == 2) : num_sms;
+  const int grid = g.ntiles < cap ? g.ntiles : cap;
   return static_cast<int>(launch_k(kern, dim3(grid), dim3(kConvThreads), S::total, st,
                                    static_cast<const uint4*>(in), static_cast<const float*>(w), bias,
                                    static_cast<const uint4*>(mask), static_cast<uint4*>(out), g,
@@ -695,7 +714,7 @@ static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch
   static bool configured[64] = {};
   const int rc = configure_smem(kern, S::total, configured);
   if (rc != 0) return rc;
-  const int sms = ddpb_num_sms();
+  const int sms = bwd_grid_cap(ddpb_num_sms(), P::kSets == 2);
   const int grid = g.ntiles < sms ? g.ntiles : sms;
   DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
                         static_cast<const uint4*>(dout), static_cast<const uint4*>(in), scratch, g,

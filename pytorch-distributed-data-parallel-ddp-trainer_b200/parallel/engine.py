@@ -126,10 +126,11 @@ class B200DataParallel(_EngineBase):
         # which stream is the critical path, e.g. DDPB_ABLATE=conv2 or DDPB_ABLATE=fl,pack
         self._ablate = set(filter(None, os.environ.get("DDPB_ABLATE", "").split(",")))
         # "event" (default): the net.2 bucket update waits for the conv2 data gradient, the last reader of
-        # net.2.weight in the step.  "legacy": the ordering every number in BASELINE.md was measured with,
-        # where the update only follows the weight gradient and can overtake the data gradient's weight
-        # staging (a real, timing-dependent race).  The event ordering was written after the round's GPU
-        # time ran out and has NOT run on hardware yet; "legacy" is the fallback if it misbehaves.
+        # net.2.weight (bf16 mode) / of its tile images (bf16x3 mode) in the step.  "legacy" (diagnostic
+        # only): the update follows the weight gradient alone and can overtake the data gradient — a real,
+        # timing-dependent race; tests/test_model_gpu.py::test_net2_update_waits_for_the_data_gradient
+        # provokes it with DDPB_TEST_DELAY_DGRAD (spin cycles inserted before the data gradient).
+        self._test_delay_dgrad = int(os.environ.get("DDPB_TEST_DELAY_DGRAD", "0"))
         self.net2_order = os.environ.get("DDPB_NET2_ORDER", "event")
         if self.net2_order not in ("event", "legacy"):
             raise ValueError(f"DDPB_NET2_ORDER must be event or legacy, got {self.net2_order!r}")
@@ -281,6 +282,8 @@ class B200DataParallel(_EngineBase):
                 m.backward_conv2_wgrad(b, self.side2, parity)
         # main: conv2 data gradient, the last reader of net.2.weight in this step
         with nvtx_range("bwd conv2 dgrad"):
+            if self._test_delay_dgrad:
+                torch.cuda._sleep(self._test_delay_dgrad)  # test hook: hold the data gradient back
             m.backward_dgrad(b, main)
         # side2: net.2.* may only be rewritten once the data gradient is done with it.  The update is
         # then the one kernel of the step with two predecessors (wgrad in stream order, dgrad through

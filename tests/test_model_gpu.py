@@ -123,3 +123,73 @@ def test_device_loader_matches_cpu_loader(cuda):
     for (xc, yc), (xg, yg) in zip(lc, lg):
         assert torch.equal(xc, xg.cpu()) and torch.equal(yc, yg.cpu())
         assert xg.shape[1:] == (1, 28, 28) and xg.dtype == torch.float32
+
+
+def test_net2_update_waits_for_the_data_gradient(cuda, monkeypatch):
+    """Regression test for the update-after-last-reader ordering.  The conv2 data gradient
+    is the last reader of net.2's weights in a step; the fused net.2 bucket update runs on another
+    stream.  Hold the data gradient back by ~1 ms (DDPB_TEST_DELAY_DGRAD): with the default ordering the
+    update waits for it and the conv1 gradients are bit-identical to an undelayed step; with
+    DDPB_NET2_ORDER=legacy the update overtakes it, the data gradient reads the UPDATED weights and the
+    conv1 gradients change."""
+    from ddp_b200.parallel.engine import B200DataParallel
+
+    def conv1_grad(order, delay):
+        monkeypatch.setenv("DDPB_NET2_ORDER", order)
+        monkeypatch.setenv("DDPB_TEST_DELAY_DGRAD", str(delay))
+        torch.manual_seed(11)
+        eng = B200DataParallel(0, 1, cuda, batch_cap=64, lr=1.0, use_graph=False)  # lr 1: a visible update
+        torch.manual_seed(12)
+        x = torch.rand(64, 1, 28, 28, device=cuda)
+        y = torch.randint(0, 10, (64,), device=cuda)
+        eng.step(x, y)
+        eng.synchronize()
+        g = eng.model.grad_sets[0]["flat"][:320].clone()   # net.0.weight + net.0.bias gradients of the step
+        eng.close()
+        return g
+
+    clean = conv1_grad("event", 0)
+    assert torch.isfinite(clean).all() and clean.abs().max() > 0
+    assert torch.equal(conv1_grad("event", 2_000_000), clean), "event ordering must be immune to the delay"
+    raced = conv1_grad("legacy", 2_000_000)
+    assert not torch.equal(raced, clean), "legacy ordering + delayed data gradient should expose the race"
+
+
+def test_nn_module_with_a_torch_optimizer_matches_the_engine(cuda):
+    """`from model import SimpleCNN` is an nn.Module (reference model.py:4-20) whose CUDA forward and
+    backward are the native kernels: three steps of torch.optim.SGD + nn.CrossEntropyLoss on it must
+    land where three engine steps land (same kernels, same order of operations up to the optimizer)."""
+    import sys
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from model import SimpleCNN
+    from ddp_b200.parallel.engine import B200DataParallel
+    torch.manual_seed(21)
+    mod = SimpleCNN().to(cuda)
+    assert isinstance(mod, torch.nn.Module)
+    eng = B200DataParallel(0, 1, cuda, batch_cap=32, lr=0.01, use_graph=False)
+    eng.model.load_state_dict(mod.state_dict())
+    opt = torch.optim.SGD(mod.parameters(), lr=0.01)
+    loss_fn = torch.nn.CrossEntropyLoss()
+    torch.manual_seed(22)
+    xs = torch.rand(3, 32, 1, 28, 28, device=cuda)
+    ys = torch.randint(0, 10, (3, 32), device=cuda)
+    for i in range(3):
+        b = 32 if i != 1 else 20            # a shorter batch in the middle reuses the larger workspace
+        opt.zero_grad()
+        loss = loss_fn(mod(xs[i, :b]), ys[i, :b])
+        loss.backward()
+        opt.step()
+        eng.step(xs[i, :b], ys[i, :b])
+        assert abs(loss.item() - eng.read_loss()) < 1e-5 * max(1.0, abs(loss.item()))
+    eng.synchronize()
+    sd = mod.state_dict()
+    for name in ("net.0.weight", "net.0.bias", "net.2.weight", "net.2.bias", "fl.weight", "fl.bias"):
+        a, b_ = sd[name], eng.model.arena.view(name)
+        assert torch.allclose(a, b_, rtol=0, atol=2e-7), (name, (a - b_).abs().max().item())
+    # hooks and a second forward before backward behave like any module / fail clearly
+    out = mod(xs[0])
+    mod(xs[1])
+    with pytest.raises(RuntimeError, match="most recent forward"):
+        out.sum().backward()
+    eng.close()
