@@ -786,8 +786,11 @@ linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
 // vector of one pixel.  dact is what the conv2 gradient GEMMs consume: SPLIT_OUT writes it as split
 // planes (hi + lo bf16, half a 16-byte row per thread and set), otherwise as fp32 planes rounded to
 // tf32.
-template <int NOUT, bool SPLIT_OUT>
-__global__ void __launch_bounds__(256, 2)
+// DO_DX / DO_DW select the halves: the step engine runs the dX half (with the bias sums) on the main
+// stream — only dact is needed by the convolution backward that follows — and the dW half on the fl
+// bucket's side stream, where it overlaps the convolution backward.
+template <int NOUT, bool SPLIT_OUT, bool DO_DX, bool DO_DW>
+__global__ void __launch_bounds__(256, (DO_DX && DO_DW) ? 2 : 3)
 linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ dlogits,
                       const float* __restrict__ W, float4* __restrict__ dact,
                       float* __restrict__ dw_partial, float* __restrict__ bias_part, Geom g, int C,
@@ -796,7 +799,7 @@ linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
   extern __shared__ float sdl[];  // [imgs_per_split][NOUT]
   __shared__ float bred[8][8];
   static_assert(kBiasBlock == 256, "one bias block per thread block");
-  constexpr int PF = 8;           // image vectors kept in flight per thread
+  constexpr int PF = DO_DX ? 4 : 8;  // image vectors kept in flight per thread (register budget)
   const int HW = g.H * g.W;
   const int nvec = (C / 4) * HW;
   const long long K = (long long)C * HW;
@@ -816,7 +819,7 @@ linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
   for (int j = 0; j < NOUT; ++j)
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      wv[j][c] = W[j * K + (long long)(chunk * 4 + c) * HW + pix];
+      wv[j][c] = DO_DX ? W[j * K + (long long)(chunk * 4 + c) * HW + pix] : 0.f;
       dwv[j][c] = 0.f;
     }
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};  // sum over this split's images of the masked dX (exact fp32)
@@ -838,10 +841,11 @@ linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
           const float d = dl[j];
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            gr[c] = fmaf(d, wv[j][c], gr[c]);
-            dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
+            if (DO_DX) gr[c] = fmaf(d, wv[j][c], gr[c]);
+            if (DO_DW) dwv[j][c] = fmaf(d, a[c], dwv[j][c]);
           }
         }
+        if constexpr (!DO_DX) continue;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           gr[c] = a[c] > 0.f ? gr[c] : 0.f;
@@ -864,13 +868,15 @@ linear_bwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
         }
       }
     }
-    float* dst = dw_partial + (long long)blockIdx.y * NOUT * K;
+    if constexpr (DO_DW) {
+      float* dst = dw_partial + (long long)blockIdx.y * NOUT * K;
 #pragma unroll
-    for (int j = 0; j < NOUT; ++j)
+      for (int j = 0; j < NOUT; ++j)
 #pragma unroll
-      for (int c = 0; c < 4; ++c) dst[j * K + (long long)(chunk * 4 + c) * HW + pix] = dwv[j][c];
+        for (int c = 0; c < 4; ++c) dst[j * K + (long long)(chunk * 4 + c) * HW + pix] = dwv[j][c];
+    }
   }
-  if (bias_part == nullptr) return;
+  if (!DO_DX || bias_part == nullptr) return;
   // fixed-shape reduction of the block's bias sums: a block spans at most two 4-channel groups
   const int slot = chunk - (blockIdx.x * kBiasBlock) / HW;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1180,37 +1186,61 @@ size_t ddpb_linear_bwd_f32_bias_part_bytes(int C, int batch_cap, int H, int W) {
     const size_t splits = (cands[i] + ips - 1) / ips;
     if (splits > worst) worst = splits;
   }
-  return worst * ((nvec + kBiasBlock - 1) / kBiasBlock) * 8 * sizeof(float);
+  // x2: the dX-only launch (mode 1) uses twice the image splits of the combined one
+  return 2 * worst * ((nvec + kBiasBlock - 1) / kBiasBlock) * 8 * sizeof(float);
 }
-int ddpb_linear_bwd_f32(const void* act, const float* dlogits, const float* Wt, void* dact, float* dW,
-                        float* scratch, int nout, int C, int batch, int batch_cap, int H, int W,
-                        int split_out, float* bias_part, int* nsplit_out, int* nbx_out, void* stream) {
-  if (nout != 10 || (C % 8) != 0) return DDPB_ERR_SHAPE;
+}  // extern "C"
+template <bool DX, bool DW>
+static int linear_bwd_f32_launch(bool split_out, dim3 grid, size_t smem, cudaStream_t st, const float4* act,
+                                 const float* dl, const float* Wt, float4* dact, float* scratch,
+                                 float* bias_part, const Geom& g, int C, int ips) {
+  if (split_out)
+    return static_cast<int>(launch_k(linear_bwd_f32_kernel<10, true, DX, DW>, grid, dim3(256), smem, st, act,
+                                     dl, Wt, dact, scratch, bias_part, g, C, ips));
+  return static_cast<int>(launch_k(linear_bwd_f32_kernel<10, false, DX, DW>, grid, dim3(256), smem, st, act,
+                                   dl, Wt, dact, scratch, bias_part, g, C, ips));
+}
+extern "C" {
+// mode 0: everything (dact, bias parts, dW).  mode 1: dact + bias parts only.  mode 2: the dW half
+// only (partials in scratch; summed into dW unless dW == NULL).  Modes 1 and 2 together equal mode 0.
+int ddpb_linear_bwd_f32_mode(const void* act, const float* dlogits, const float* Wt, void* dact, float* dW,
+                             float* scratch, int nout, int C, int batch, int batch_cap, int H, int W,
+                             int split_out, float* bias_part, int* nsplit_out, int* nbx_out, int mode,
+                             void* stream) {
+  if (nout != 10 || (C % 8) != 0 || mode < 0 || mode > 2) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nvec = (C / 4) * H * W;
-  const int ips = linear_bwd_imgs_per_split(batch);
+  // the dX half writes no partials, so it can afford twice the image splits of the dW half
+  const int ips_dw = linear_bwd_imgs_per_split(batch);
+  const int ips = (mode == 1 && ips_dw >= 16) ? ips_dw / 2 : ips_dw;
   const int splits = (batch + ips - 1) / ips;
   const int nbx = (nvec + kBiasBlock - 1) / kBiasBlock;
   if (nsplit_out) *nsplit_out = splits;
   if (nbx_out) *nbx_out = nbx;
-  if (g.ntiles * kTileM > batch * g.PHW) {
+  if (mode != 2 && g.ntiles * kTileM > batch * g.PHW) {
     DDPB_CUDA_OK(launch_k(zero_tail_rows_kernel, dim3(8), dim3(256), 0, st, static_cast<uint4*>(dact),
                           C / 4, g));  // C/4 planes in either format (split: hi + lo sets of C/8)
   }
-  if (split_out) {
-    DDPB_CUDA_OK(launch_k(linear_bwd_f32_kernel<10, true>, dim3(nbx, splits), dim3(256),
-                          ips * 10 * sizeof(float), st, static_cast<const float4*>(act), dlogits, Wt,
-                          static_cast<float4*>(dact), scratch, bias_part, g, C, ips));
-  } else {
-    DDPB_CUDA_OK(launch_k(linear_bwd_f32_kernel<10, false>, dim3(nbx, splits), dim3(256),
-                          ips * 10 * sizeof(float), st, static_cast<const float4*>(act), dlogits, Wt,
-                          static_cast<float4*>(dact), scratch, bias_part, g, C, ips));
-  }
+  const dim3 grid(nbx, splits);
+  const size_t smem = ips * 10 * sizeof(float);
+  const float4* a4 = static_cast<const float4*>(act);
+  float4* d4 = static_cast<float4*>(dact);
+  int rc;
+  if (mode == 0) rc = linear_bwd_f32_launch<true, true>(split_out, grid, smem, st, a4, dlogits, Wt, d4, scratch, bias_part, g, C, ips);
+  else if (mode == 1) rc = linear_bwd_f32_launch<true, false>(split_out, grid, smem, st, a4, dlogits, Wt, d4, scratch, bias_part, g, C, ips);
+  else rc = linear_bwd_f32_launch<false, true>(split_out, grid, smem, st, a4, dlogits, Wt, d4, scratch, nullptr, g, C, ips);
+  if (rc != 0) return rc;
   // dW == NULL: the per-split partials stay in scratch[*nsplit_out][nout*C*H*W] and the caller sums them
-  // with ddpb_reduce_partials where it suits (the step engine does it on the bucket's side stream)
-  if (dW == nullptr) return 0;
+  // with ddpb_reduce_partials where it suits
+  if (mode == 1 || dW == nullptr) return 0;
   return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
+}
+int ddpb_linear_bwd_f32(const void* act, const float* dlogits, const float* Wt, void* dact, float* dW,
+                        float* scratch, int nout, int C, int batch, int batch_cap, int H, int W,
+                        int split_out, float* bias_part, int* nsplit_out, int* nbx_out, void* stream) {
+  return ddpb_linear_bwd_f32_mode(act, dlogits, Wt, dact, dW, scratch, nout, C, batch, batch_cap, H, W,
+                                  split_out, bias_part, nsplit_out, nbx_out, 0, stream);
 }
 
 // Zero the rows of `nplanes` planes between the end of the batch and the end of its last tile.

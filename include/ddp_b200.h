@@ -179,6 +179,13 @@ int ddpb_linear_bwd_f32(const void* act_f32_planes, const float* dlogits, const 
                         void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,
                         int batch_cap, int H, int W, int split_out, float* bias_part, int* nsplit_out,
                         int* nbx_out, void* stream);
+/* The same in two halves: mode 1 = dact + bias parts only, mode 2 = the dW half only (mode 0 = both).
+ * The step engine runs mode 1 on its main stream and mode 2 on the fl bucket's side stream, where it
+ * overlaps the convolution backward. */
+int ddpb_linear_bwd_f32_mode(const void* act_f32_planes, const float* dlogits, const float* W_fl,
+                             void* dact_planes, float* dW, float* scratch, int nout, int C, int batch,
+                             int batch_cap, int H, int W, int split_out, float* bias_part,
+                             int* nsplit_out, int* nbx_out, int mode, void* stream);
 /* tf32 building blocks on fp32 planes (forward / data gradient only: tcgen05 defines an MN-major tf32
  * operand — the weight gradient's view of a plane — only for the 128B_BASE32B swizzled layout). */
 int ddpb_conv1_fwd_tc_f32(const float* x, const float* w, const float* b, void* out_f32_planes,

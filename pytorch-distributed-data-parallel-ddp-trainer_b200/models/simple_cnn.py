@@ -292,19 +292,24 @@ class SimpleCNNB200(_ModelBase):
         critical path — only dact2 is needed by what follows on the main stream)."""
         gs = self.grad_sets[parity]
         if self.x3:
+            # defer_reduce: only the dX half (dact2 + the exact bias sums) runs here; the dW half is
+            # backward_head_reduce()'s job
             self.db2_extent = self.nat.linear_bwd_f32(
                 self.act2, self.dlogits, self.wf, self.dact2, None if defer_reduce else gs["wf"],
                 self.lin_bwd_scr, NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream, split_out=True,
-                bias_part=self.db2_part)
+                bias_part=self.db2_part, mode=1 if defer_reduce else 0)
+            self._head_batch = batch
             return
         self.nat.linear_bwd_tc(self.act2, self.dl_packed, self.lin_packed, self.dact2, gs["wf"],
                                NCLS, C2, batch, self.batch_cap, IMG_H, IMG_W, stream)
 
     def backward_head_reduce(self, stream=None, parity: int = 0) -> None:
-        """Fixed-order sum of the deferred fl.weight gradient partials into the gradient arena."""
+        """The deferred dW half of the linear backward: fl.weight gradient (per-image-split partials +
+        their fixed-order sum) into the gradient arena.  Reads act2 and dlogits only."""
         if self.x3:
-            self.nat.reduce_partials(self.lin_bwd_scr, self.db2_extent[0], NCLS * FEATURES,
-                                     self.grad_sets[parity]["wf"], stream)
+            self.nat.linear_bwd_f32(self.act2, self.dlogits, self.wf, self.dact2, self.grad_sets[parity]["wf"],
+                                    self.lin_bwd_scr, NCLS, C2, self._head_batch, self.batch_cap, IMG_H, IMG_W,
+                                    stream, split_out=True, mode=2)
 
     def backward_conv2_wgrad(self, batch: int, stream=None, parity: int = 0):
         """conv2 weight + bias gradient (independent of the dgrad chain: may run on its own stream)."""
@@ -377,7 +382,8 @@ class SimpleCNNB200(_ModelBase):
         # (its split-K reduce is fused into the bucket update kernel); the fp32 linear backward adds
         # the fixed-order reduce of its per-image-split dW partials
         fused_loss = 1 if (self.x3 and batch <= self.fused_loss_max) else 0
-        return 4 - fused_loss + (1 + tail) + 2 + 1 + 1 + (1 if self.x3 else 0)
+        # bf16x3: the linear backward is two kernels (dX half, dW half) + the reduce of the dW partials
+        return 4 - fused_loss + (1 + tail) + 2 + 1 + 1 + (2 if self.x3 else 0)
 
     def sgd_step(self, lr: float | None = None, stream=None) -> None:
         if lr is not None:

@@ -72,6 +72,7 @@ _SIGNATURES = {
     "ddpb_linear_fwd_f32_xent": (I, [P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_linear_bwd_f32_bias_part_bytes": (c_size_t, [I, I, I, I]),
     "ddpb_linear_bwd_f32": (I, [P, P, P, P, P, P, I, I, I, I, I, I, I, P, POINTER(c_int), POINTER(c_int), P]),
+    "ddpb_linear_bwd_f32_mode": (I, [P, P, P, P, P, P, I, I, I, I, I, I, I, P, POINTER(c_int), POINTER(c_int), I, P]),
     "ddpb_conv1_wgrad_f32_scratch_bytes": (c_size_t, [I, I]),
     "ddpb_conv1_wgrad_f32": (I, [P, P, P, P, I, I, I, I, I, I, P]),
     "ddpb_conv1_wgrad_f32_partials": (I, [P, P, P, POINTER(c_int), I, I, I, I, I, I, P]),
@@ -419,14 +420,15 @@ def linear_bwd_f32_bias_part_bytes(C, batch_cap, H, W) -> int:
 
 
 def linear_bwd_f32(act, dlogits, Wfl, dact, dW, scr, nout, C, batch, batch_cap, H, W, stream=None,
-                   split_out: bool = True, bias_part=None):
+                   split_out: bool = True, bias_part=None, mode: int = 0):
     """fp32 linear backward on fp32 activation planes; ``dact`` = split planes (default) or fp32
     planes rounded to tf32.  With ``bias_part`` (linear_bwd_f32_bias_part_bytes) the kernel also leaves
-    the exact-fp32 per-channel sums of dact there; returns their extents (nsplit, nbx)."""
+    the exact-fp32 per-channel sums of dact there; returns the extents (nsplit, nbx) of this launch.
+    ``mode`` 1 = the dX half only (dact + bias parts), 2 = the dW half only, 0 = both."""
     ns, nb = c_int(0), c_int(0)
-    check(lib().ddpb_linear_bwd_f32(ptr(act), ptr(dlogits), ptr(Wfl), ptr(dact), ptr(dW), ptr(scr),
-                                    nout, C, batch, batch_cap, H, W, int(split_out), ptr(bias_part),
-                                    ctypes.byref(ns), ctypes.byref(nb), stream_ptr(stream)),
+    check(lib().ddpb_linear_bwd_f32_mode(ptr(act), ptr(dlogits), ptr(Wfl), ptr(dact), ptr(dW), ptr(scr),
+                                         nout, C, batch, batch_cap, H, W, int(split_out), ptr(bias_part),
+                                         ctypes.byref(ns), ctypes.byref(nb), int(mode), stream_ptr(stream)),
           "linear_bwd_f32")
     return ns.value, nb.value
 

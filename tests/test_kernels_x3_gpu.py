@@ -326,3 +326,35 @@ def test_linear_fwd_with_fused_loss_matches_the_two_kernel_route(nat, batch, cap
         _check("fused logits", got[0], z, 2e-6)
         assert abs(got[3].item() - F.cross_entropy(z, y).item()) < 2e-6 * max(1.0, abs(got[3].item()))
     assert nat.linear_fwd_f32_xent_max_batch() == 128
+
+
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (300, 300)])
+def test_linear_bwd_halves_equal_the_whole(nat, batch, cap):
+    """mode 1 (dX + bias parts, main stream) + mode 2 (dW, side stream) == mode 0."""
+    torch.manual_seed(41)
+    C, K = 64, 64 * H * W
+    lay = _lay()
+    act_p = lay.nchw_to_planes(torch.relu(torch.randn(batch, C, H, W, device="cuda")), cap, dtype=F32)
+    Wfl = torch.randn(10, K, device="cuda") * 0.01
+    dl = torch.randn(batch, 10, device="cuda") * 0.01
+    scr = nat.scratch(nat.linear_bwd_scratch_bytes(10, C, cap, H, W))
+    out = {}
+    for tag, modes in (("whole", (0,)), ("halves", (1, 2))):
+        dact = nat.alloc_planes(C, cap, H, W, fmt="split")
+        dW = torch.full((10, K), float("nan"), device="cuda")
+        bp = nat.scratch(nat.linear_bwd_f32_bias_part_bytes(C, cap, H, W))
+        ext = None
+        for m in modes:
+            e = nat.linear_bwd_f32(act_p, dl, Wfl, dact, dW, scr, 10, C, batch, cap, H, W, split_out=True,
+                                   bias_part=bp, mode=m)
+            ext = e if m != 2 else ext
+        db = torch.zeros(64, device="cuda")
+        dw2 = torch.zeros(64, 32, 3, 3, device="cuda")
+        a1 = lay.nchw_to_split_planes(torch.zeros(batch, 32, H, W, device="cuda"), cap)
+        nat.conv3x3_wgrad_split(dact, a1, dw2, db, nat.scratch(nat.conv3x3_wgrad_scratch_bytes(32, 64)), 32, 64,
+                                batch, cap, H, W, bias_parts=(bp, *ext))
+        torch.cuda.synchronize()
+        out[tag] = (dact.clone(), dW, db)
+    assert torch.equal(out["whole"][0].view(torch.int16), out["halves"][0].view(torch.int16))
+    assert torch.equal(out["whole"][1], out["halves"][1])
+    assert torch.allclose(out["whole"][2], out["halves"][2], rtol=1e-5, atol=1e-6 * out["whole"][2].abs().max().item())  # different split count
