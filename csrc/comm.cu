@@ -403,18 +403,16 @@ reduce_allreduce_sgd_ll_kernel(const __grid_constant__ PeerPtrs pp, int rank, in
     *pr = nv;
     if (MAP == 1 && pack != nullptr && dest < 64 * 32 * 9) {
       // keep the split (hi + lo bf16) tensor-core tile images of net.2.weight (csrc/conv_tc.cu:
-      // [fwd hi | fwd lo | dgrad hi | dgrad lo]) in step with the master weights: the next forward /
+      // [fwd image | dgrad image], hi/lo rows adjacent) in step with the master weights: the next forward /
       // data gradient bulk-copy them without any conversion
       constexpr int n = 9 * 32 * 64;
       const int co = dest / (32 * 9), rem = dest - co * 32 * 9, ci = rem / 9, tap = rem - ci * 9;
       float hi, lo;
       split_bf16(nv, hi, lo);
-      const int f = conv3x3_fwd_tile_index<32, 64, 8>(co, ci, tap);
-      const int d = conv3x3_dgrad_tile_index<32, 64, 8>(co, ci, tap);
-      pack[f] = __float2bfloat16_rn(hi);
-      pack[n + f] = __float2bfloat16_rn(lo);
-      pack[2 * n + d] = __float2bfloat16_rn(hi);
-      pack[3 * n + d] = __float2bfloat16_rn(lo);
+      pack[conv3x3_fwd_split_index<32, 64>(co, ci, tap, 0)] = __float2bfloat16_rn(hi);
+      pack[conv3x3_fwd_split_index<32, 64>(co, ci, tap, 1)] = __float2bfloat16_rn(lo);
+      pack[2 * n + conv3x3_dgrad_split_index<32, 64>(co, ci, tap, 0)] = __float2bfloat16_rn(hi);
+      pack[2 * n + conv3x3_dgrad_split_index<32, 64>(co, ci, tap, 1)] = __float2bfloat16_rn(lo);
     }
   }
   // the last block to finish publishes the new epoch for the next launch on this slot

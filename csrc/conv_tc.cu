@@ -39,10 +39,14 @@ struct ConvSmem {
   // weights; the k-chunk stride (UMMA LBO) is skewed by 16 B so that the conversion writes shared
   // memory without bank conflicts.  Split / tf32: the tile images (one per set) are pre-packed in
   // global memory (pack kernels below / the fused bucket update) and arrive with one bulk copy.
-  static constexpr uint32_t w_lbo = CO * 16 + (kPrepacked ? 0 : 16);
+  // Split: the hi and lo rows of a K chunk are adjacent ([W_hi | W_lo] along N), so ONE MMA with
+  // N = 2*CO multiplies an operand by both terms; w_rows = B rows per K chunk.
+  static constexpr uint32_t w_rows = (P::kSets == 2 ? 2 : 1) * CO;
+  static constexpr uint32_t w_lbo = w_rows * 16 + (kPrepacked ? 0 : 16);
   static constexpr uint32_t w_tap_bytes = KP * w_lbo;
-  static constexpr uint32_t w_set_bytes = 9 * w_tap_bytes;
-  static constexpr uint32_t w_bytes = (P::kSets * w_set_bytes + 127) / 128 * 128;
+  static constexpr uint32_t w_img_bytes = 9 * w_tap_bytes;   // whole image (split: both sets)
+  static constexpr uint32_t w_bytes = (w_img_bytes + 127) / 128 * 128;
+  static constexpr uint32_t acc_cols = w_rows;               // accumulator columns per TMEM buffer
   static constexpr uint32_t a_stage_bytes = NPL * kStagePlaneBytes;
   static constexpr uint32_t off_a = w_bytes;
   // plain bf16: fp32 master weights are bulk-copied (TMA, one copy) into a staging area and converted
@@ -129,7 +133,7 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
                   uint4* __restrict__ out, Geom g, int round_out, unsigned long long* prof) {
   using S = ConvSmem<P, CI, CO, STAGES>;
   constexpr uint32_t KP = CI / P::kCh;
-  constexpr uint32_t TMEM_COLS = pow2_cols(2 * CO);
+  constexpr uint32_t TMEM_COLS = pow2_cols(2 * S::acc_cols);
   extern __shared__ __align__(128) uint8_t smem[];
 
   const int tid = threadIdx.x;
@@ -160,8 +164,8 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
     fence_mbar_init();
     if constexpr (S::kPrepacked) {
       // pre-packed tile images (all sets): one bulk async copy straight into the B-tile area
-      mbar_arrive_expect_tx(bar_w, P::kSets * S::w_set_bytes);
-      bulk_g2s(s_w, w, P::kSets * S::w_set_bytes, bar_w);
+      mbar_arrive_expect_tx(bar_w, S::w_img_bytes);
+      bulk_g2s(s_w, w, S::w_img_bytes, bar_w);
     } else {
       // fp32 master weights: one bulk async copy into the staging area
       mbar_arrive_expect_tx(bar_w, S::wstage_bytes);
@@ -251,6 +255,8 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
   } else if (warp == 1) {
     // MMA issuer: the whole warp stays converged, one elected lane issues (see elect_one()).
     constexpr uint32_t idesc = umma_idesc_p<P>(kTileM, CO, 0, 0);
+    constexpr uint32_t idesc2 = umma_idesc_p<P>(kTileM, S::acc_cols, 0, 0);  // split: N = 2*CO
+    (void)idesc2;
     uint32_t tap_off[9];
 #pragma unroll
     for (int tap = 0; tap < 9; ++tap)
@@ -266,7 +272,7 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
       tc_fence_after();
       if (it == 0 && lane == 0) prof_stamp(prof, 4);
       const uint32_t a_stage = s_a + stage * S::a_stage_bytes;
-      const uint32_t d_tmem = tmem_base + acc * CO;
+      const uint32_t d_tmem = tmem_base + acc * S::acc_cols;
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
 #pragma unroll
@@ -276,16 +282,16 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
           const uint64_t bdesc =
               umma_smem_desc(s_w + tap * S::w_tap_bytes + kk * 2 * S::w_lbo, S::w_lbo, 128);
           if constexpr (P::kSets == 2) {
-            // split operands: hi.hi + lo.hi + hi.lo (lo planes / lo tile image follow the hi ones)
+            // split operands, two MMAs per K step instead of three: A_hi x [W_hi | W_lo] (N = 2*CO:
+            // columns [0,CO) += hi.hi, [CO,2CO) += hi.lo) and A_lo x W_hi (N = CO: columns [0,CO) +=
+            // lo.hi); the epilogue adds the two column halves.  (A tcgen05.mma costs ~max(45, N/2)
+            // cycles whatever M is, so the wider N is nearly free.)
             const uint64_t adesc_lo =
                 umma_smem_desc(a_stage + KP * kStagePlaneBytes + tap_off[tap] + kk * 2 * kStagePlaneBytes,
                                kStagePlaneBytes, 128);
-            const uint64_t bdesc_lo = umma_smem_desc(
-                s_w + S::w_set_bytes + tap * S::w_tap_bytes + kk * 2 * S::w_lbo, S::w_lbo, 128);
             if (elect_one()) {
-              umma_p<P>(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
+              umma_p<P>(d_tmem, adesc, bdesc, idesc2, (tap | kk) != 0);
               umma_p<P>(d_tmem, adesc_lo, bdesc, idesc, 1);
-              umma_p<P>(d_tmem, adesc, bdesc_lo, idesc, 1);
             }
           } else {
             if (elect_one()) umma_p<P>(d_tmem, adesc, bdesc, idesc, (tap | kk) != 0);
@@ -323,9 +329,17 @@ conv3x3_tc_kernel(const uint4* __restrict__ in, const float* __restrict__ w,
       tc_fence_after();
       if (it == 0 && tid == 64) prof_stamp(prof, 6);
       uint32_t v[COLS];
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * CO + c0;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * S::acc_cols + c0;
       if constexpr (COLS == 32) tmem_ld32(taddr, v);
       else tmem_ld16(taddr, v);
+      if constexpr (P::kSets == 2) {  // second column half: the hi.lo products
+        uint32_t v2[COLS];
+        if constexpr (COLS == 32) tmem_ld32(taddr + CO, v2);
+        else tmem_ld16(taddr + CO, v2);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+      }
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_tempty + acc * 8);  // accumulator is in registers: release it early
@@ -398,7 +412,7 @@ struct WgradSmem {
 template <class P, int CI, int CO, int STAGES>
 __global__ void __launch_bounds__(kWgradThreads, 1)
 conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ in,
-                        float* __restrict__ partial, Geom g, unsigned long long* prof) {
+                        float* __restrict__ partial, Geom g, int want_bias, unsigned long long* prof) {
   using S = WgradSmem<P, CI, CO, STAGES>;
   static_assert(CO == 64 || CO == 128, "UMMA M must be 64 or 128");
   static_assert(S::n0 <= 128, "one filter row must fit a 128-column TMEM allocation");
@@ -473,6 +487,9 @@ conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict_
   } else if (warp == 1) {
     constexpr uint32_t idesc0 = umma_idesc_bf16(CO, S::n0, 1, 1);
     constexpr uint32_t idesc1 = umma_idesc_bf16(CO, S::n1, 1, 1);
+    constexpr uint32_t idesc_s = umma_idesc_bf16(2 * CO, S::n1, 1, 1);  // split: stacked hi/lo rows
+    constexpr uint32_t idesc_b = umma_idesc_bf16(2 * CO, 16, 1, 1);
+    (void)idesc_s; (void)idesc_b; (void)idesc0; (void)idesc1;
     uint32_t row_off[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) row_off[r] = (kHalo + (r - 1) * g.PW) * kRowBytes;
@@ -494,13 +511,22 @@ conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict_
           const uint64_t bdesc =
               umma_smem_desc(sb + row_off[r] + ks * 16 * kRowBytes, 128, kStagePlaneBytes);
           if constexpr (P::kSets == 2) {
-            const uint64_t adesc_lo = umma_smem_desc(sa + S::a_set + ks * 16 * kRowBytes, 128, S::a_plane);
+            // The hi and lo plane sets of dout are adjacent in the stage, so ONE descriptor with
+            // M = 2*CO = 128 spans [dout_hi ; dout_lo]: two MMAs per filter row (x in_hi, x in_lo) give
+            // all four products — rows 0..63 accumulate hi.hi + hi.lo, rows 64..127 lo.hi + lo.lo — and
+            // the epilogue adds the two row halves.  (M = 128 costs the same issue time as M = 64.)
             const uint64_t bdesc_lo =
                 umma_smem_desc(sb + S::b_set + row_off[r] + ks * 16 * kRowBytes, 128, kStagePlaneBytes);
             if (elect_one()) {
-              umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
-              umma_bf16(tmem_row[r], adesc_lo, bdesc, r == 0 ? idesc0 : idesc1, 1);
-              umma_bf16(tmem_row[r], adesc, bdesc_lo, idesc1, 1);  // lo set: taps only, no ones plane
+              umma_bf16(tmem_row[r], adesc, bdesc, idesc_s, accum);
+              umma_bf16(tmem_row[r], adesc, bdesc_lo, idesc_s, 1);
+              if (r == 0 && want_bias) {
+                // bias block: [dout_hi ; dout_lo] x ones, 16 columns at column n1 (the second 8 read
+                // the plane after the ones plane and are never used)
+                const uint64_t bdesc_1 = umma_smem_desc(sb + 3 * S::BP * kStagePlaneBytes + row_off[0] +
+                                                        ks * 16 * kRowBytes, 128, kStagePlaneBytes);
+                umma_bf16(tmem_row[0] + S::n1, adesc, bdesc_1, idesc_b, accum);
+              }
             }
           } else {
             if (elect_one()) umma_bf16(tmem_row[r], adesc, bdesc, r == 0 ? idesc0 : idesc1, accum);
@@ -518,6 +544,49 @@ conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict_
     mbar_wait(bar_done, 0);
     tc_fence_after();
     if (tid == 64) prof_stamp(prof, 6);
+    if constexpr (P::kSets == 2) {
+      // M = 128: accumulator row m sits in TMEM lane m; rows m and m + 64 belong to output channel m.
+      // Warps of lanes 64..127 park their rows in shared memory (the stage ring is idle now), the
+      // warps of lanes 0..63 add them to their own and write the partial image.
+      static_assert(CO == 64, "stacked hi/lo rows need 2*CO == 128");
+      float* park = reinterpret_cast<float*>(smem);  // [64 rows][ncols]
+      const int m = (q & 1) * 32 + lane;             // output channel of this thread's row
+      const bool upper = q >= 2;
+      float* dst = partial + ((long long)blockIdx.x * CO + m) * S::ncols;
+      float* prow = park + m * S::ncols;
+      for (int pass = 0; pass < 2; ++pass) {
+        if ((pass == 0) == upper) {
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const uint32_t tb = tmem_row[r] + (static_cast<uint32_t>(q * 32) << 16);
+            const int cbase = r == 0 ? 0 : S::n0 + (r - 1) * S::n1;
+            const int ncol = (r == 0 && want_bias) ? S::n1 + 8 : S::n1;
+#pragma unroll 1
+            for (int c0 = 0; c0 < ncol; c0 += 8) {
+              uint32_t v[8];
+              tmem_ld8(tb + c0, v);
+              tmem_ld_wait();
+              float4 a = make_float4(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]),
+                                     __uint_as_float(v[3]));
+              float4 b = make_float4(__uint_as_float(v[4]), __uint_as_float(v[5]), __uint_as_float(v[6]),
+                                     __uint_as_float(v[7]));
+              if (upper) {
+                *reinterpret_cast<float4*>(prow + cbase + c0) = a;
+                *reinterpret_cast<float4*>(prow + cbase + c0 + 4) = b;
+              } else {
+                const float4 pa = *reinterpret_cast<const float4*>(prow + cbase + c0);
+                const float4 pb = *reinterpret_cast<const float4*>(prow + cbase + c0 + 4);
+                a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
+                b.x += pb.x; b.y += pb.y; b.z += pb.z; b.w += pb.w;
+                *reinterpret_cast<float4*>(dst + cbase + c0) = a;
+                *reinterpret_cast<float4*>(dst + cbase + c0 + 4) = b;
+              }
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
+      }
+    } else {
     // M=64: accumulator row m sits in TMEM lane (m%16) + 32*(m/16); M=128: lane m.
     const int rows_per_q = CO / 4;
     const int m = q * rows_per_q + lane;
@@ -548,6 +617,7 @@ conv3x3_wgrad_tc_kernel(const uint4* __restrict__ dout, const uint4* __restrict_
           *reinterpret_cast<uint4*>(drow + S::n1 + 4) = make_uint4(v[4], v[5], v[6], v[7]);
         }
       }
+    }
     }
     if (tid == 64) prof_stamp(prof, 7);
   }
@@ -615,7 +685,8 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, float* __rest
 // ------------------------------------------------------------------------------------------
 // fp32 master weights w[CO_L][CI_L][3][3] -> the pre-packed B-tile images the split / fp32-plane
 // kernels bulk-copy into shared memory (index maps: layout.cuh):
-//   split : [fwd hi | fwd lo | dgrad hi | dgrad lo], each 9*CI_L*CO_L bf16   (w = hi + lo)
+//   split : [fwd image | dgrad image], each 2*9*CI_L*CO_L bf16, hi and lo rows of a K chunk adjacent
+//           (layout.cuh: conv3x3_{fwd,dgrad}_split_index; w = hi + lo)
 //   tf32  : [fwd | dgrad], each 9*CI_L*CO_L floats rounded to nearest tf32
 // The fused bucket update (comm.cu, MAP 1) rewrites the split images in place after every step; these
 // kernels are for initialisation, checkpoint load and the non-fused update modes.
@@ -631,12 +702,10 @@ pack_conv3x3_split_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict
   const int co = idx / (9 * CI_L);
   float hi, lo;
   split_bf16(w[idx], hi, lo);
-  const int f = conv3x3_fwd_tile_index<CI_L, CO_L, 8>(co, ci, t);
-  const int d = conv3x3_dgrad_tile_index<CI_L, CO_L, 8>(co, ci, t);
-  packed[f] = __float2bfloat16_rn(hi);
-  packed[n + f] = __float2bfloat16_rn(lo);
-  packed[2 * n + d] = __float2bfloat16_rn(hi);
-  packed[3 * n + d] = __float2bfloat16_rn(lo);
+  packed[conv3x3_fwd_split_index<CI_L, CO_L>(co, ci, t, 0)] = __float2bfloat16_rn(hi);
+  packed[conv3x3_fwd_split_index<CI_L, CO_L>(co, ci, t, 1)] = __float2bfloat16_rn(lo);
+  packed[2 * n + conv3x3_dgrad_split_index<CI_L, CO_L>(co, ci, t, 0)] = __float2bfloat16_rn(hi);
+  packed[2 * n + conv3x3_dgrad_split_index<CI_L, CO_L>(co, ci, t, 1)] = __float2bfloat16_rn(lo);
 }
 
 template <int CI_L, int CO_L>
@@ -705,7 +774,8 @@ static int launch_conv(const void* in, const void* w, const float* bias, const v
 
 template <class P>
 static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch, int* nparts, int cin,
-                                int cout, int batch, int batch_cap, int H, int W, void* stream) {
+                                int cout, int batch, int batch_cap, int H, int W, void* stream,
+                                int want_bias = 1) {
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (W + 3 > kHalo) return DDPB_ERR_SHAPE;
@@ -720,7 +790,7 @@ static int conv3x3_wgrad_launch(const void* dout, const void* in, float* scratch
   const int grid = g.ntiles < sms ? g.ntiles : sms;
   DDPB_CUDA_OK(launch_k(kern, dim3(grid), dim3(kWgradThreads), S::total, st,
                         static_cast<const uint4*>(dout), static_cast<const uint4*>(in), scratch, g,
-                        g_prof));
+                        want_bias, g_prof));
   *nparts = grid;
   return 0;
 }
@@ -730,7 +800,9 @@ static int conv3x3_wgrad_full(const void* dout, const void* in, float* dw, float
                               int cin, int cout, int batch, int batch_cap, int H, int W, void* stream,
                               const float* bias_part = nullptr, int nsplit = 0, int nbx = 0) {
   int grid = 0;
-  const int rc = conv3x3_wgrad_launch<P>(dout, in, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream);
+  // with bias parts from the linear backward the tensor-core bias column is not needed
+  const int rc = conv3x3_wgrad_launch<P>(dout, in, scratch, &grid, cin, cout, batch, batch_cap, H, W, stream,
+                                         bias_part == nullptr);
   if (rc != 0) return rc;
   constexpr int CI = 32, CO = 64;
   const int n = CO * (9 * CI + 8);

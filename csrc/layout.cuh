@@ -148,5 +148,16 @@ template <int CI_L, int CO_L, int E>
 __host__ __device__ constexpr int conv3x3_dgrad_tile_index(int co, int ci, int tap) {
   return (((8 - tap) * (CO_L / E) + co / E) * CI_L + ci) * E + co % E;
 }
+// Split (hi + lo bf16) tile images keep BOTH terms of a K chunk next to each other along N:
+//   forward   [tap][ci/8][set][co][ci%8],   data-grad [8-tap][co/8][set][ci][co%8]   (set 0 = hi, 1 = lo)
+// so one MMA with N = 2 x (rows of one set) multiplies an operand by [W_hi | W_lo] at once.
+template <int CI_L, int CO_L>
+__host__ __device__ constexpr int conv3x3_fwd_split_index(int co, int ci, int tap, int set) {
+  return (((tap * (CI_L / 8) + ci / 8) * 2 + set) * CO_L + co) * 8 + ci % 8;
+}
+template <int CI_L, int CO_L>
+__host__ __device__ constexpr int conv3x3_dgrad_split_index(int co, int ci, int tap, int set) {
+  return ((((8 - tap) * (CO_L / 8) + co / 8) * 2 + set) * CI_L + ci) * 8 + co % 8;
+}
 
 }  // namespace ddpb
