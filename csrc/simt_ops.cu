@@ -86,6 +86,7 @@ __global__ void gather_u8_kernel(const uint8_t* __restrict__ images,
 // (zero-bordered) input tile is staged in shared memory so the 3x3 window needs no bounds tests;
 // the chunk's 8x(CIN0*9) weights live in registers.  Border rows are written as zeros.
 constexpr int kConv1Group = 8;  // images staged in shared memory per round
+constexpr int kConv1Guard = 64;  // zeroed floats before/after the staged tiles (>= padded width + 1)
 
 // Stage `ng` zero-bordered images [CIN0][PHW] each into shared memory.
 template <int CIN0>
@@ -93,11 +94,20 @@ __device__ __forceinline__ void stage_padded_images(float* xs, const float* __re
                                                     int ng, const Geom& g) {
   const int per = CIN0 * g.PHW;
   for (int i = threadIdx.x; i < ng * per; i += blockDim.x) {
-    const int li = i / per;
-    const int rem = i - li * per;
-    const int ci = rem / g.PHW;
-    const int pos = rem - ci * g.PHW;
-    const int hp = pos / g.PW, wp = pos - hp * g.PW;
+    int li, ci, pos, hp;
+    if (CIN0 == 1 && g.mul_phw) {  // exact multiply-high division (layout.cuh), ~10x fewer instructions
+      li = static_cast<int>(__umulhi(static_cast<uint32_t>(i), g.mul_phw) >> g.sh_phw);
+      ci = 0;
+      pos = i - li * g.PHW;
+      hp = static_cast<int>(__umulhi(static_cast<uint32_t>(pos), g.mul_pw));
+    } else {
+      li = i / per;
+      const int rem = i - li * per;
+      ci = rem / g.PHW;
+      pos = rem - ci * g.PHW;
+      hp = pos / g.PW;
+    }
+    const int wp = pos - hp * g.PW;
     const bool in = hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W;
     xs[i] = in ? x[((long long)(img0 + li) * CIN0 + ci) * g.H * g.W + (hp - 1) * g.W + (wp - 1)] : 0.f;
   }
@@ -181,8 +191,12 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
   constexpr int NW = CIN0 * 9;
   constexpr int NV = 8 * NW + 8;
   constexpr int PF = 4;          // gradient vectors kept in flight per thread
-  extern __shared__ float xs[];  // [kConv1Group][CIN0][PHW]
+  extern __shared__ float xs_raw[];  // [guard][kConv1Group][CIN0][PHW][guard], guards zeroed once
+  float* xs = xs_raw + kConv1Guard;
   __shared__ float red[8][NV];
+  // everything a border row's window can touch must be finite (it is multiplied by zero): clear the
+  // guards and the tiles once; afterwards tiles only ever hold staged images
+  for (int i = threadIdx.x; i < kConv1Group * CIN0 * g.PHW + 2 * kConv1Guard; i += blockDim.x) xs_raw[i] = 0.f;
   // launched through launch_k in the step (programmatic dependent launch): nothing the predecessor
   // wrote (dact) may be read before this; a no-op for plain launches
   pdl_sync();
@@ -218,10 +232,10 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
       for (int u = 0; u < PF; ++u) {
         const int idx = base + u * blockDim.x;
         if (idx >= nidx) break;
-        const int li = idx / g.PHW;
-        const int pos = idx - li * g.PHW;
-        const int hp = pos / g.PW, wp = pos - hp * g.PW;
-        if (!(hp >= 1 && hp <= g.H && wp >= 1 && wp <= g.W)) continue;
+        // No row decode and no interior test: the staged tiles have the planes' row structure (row idx
+        // of the group = xs[idx]), border rows of dact are zero, and the 3x3 window of a border row
+        // only reaches into a neighbouring tile or the zeroed guard around the staging area, i.e.
+        // finite values that are multiplied by zero.
         float d[8];
         if (F32IN) {
           d[0] = __uint_as_float(dv[u].x); d[1] = __uint_as_float(dv[u].y);
@@ -231,15 +245,13 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
         } else {
           unpack8(dv[u], d);
         }
-        const float* xi = xs + li * CIN0 * g.PHW;
+        static_assert(CIN0 == 1, "window addressing below assumes one input channel");
+        const float* xi = xs + idx;
         float in[NW];
 #pragma unroll
-        for (int ci = 0; ci < CIN0; ++ci)
+        for (int r = 0; r < 3; ++r)
 #pragma unroll
-          for (int r = 0; r < 3; ++r)
-#pragma unroll
-            for (int s2 = 0; s2 < 3; ++s2)
-              in[ci * 9 + r * 3 + s2] = xi[ci * g.PHW + (hp + r - 1) * g.PW + (wp + s2 - 1)];
+          for (int s2 = 0; s2 < 3; ++s2) in[r * 3 + s2] = xi[(r - 1) * g.PW + (s2 - 1)];
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           acc[8 * NW + c] += d[c];
@@ -983,7 +995,7 @@ int ddpb_conv1_wgrad(const void* dact, const float* x, float* dw_db, float* scra
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int bx = conv1_wgrad_blocks(batch, H, W);
-  conv1_wgrad_kernel<1, 32, false><<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
+  conv1_wgrad_kernel<1, 32, false><<<dim3(bx, cout / 8), 256, ((size_t)kConv1Group * cin * g.PHW + 2 * kConv1Guard) * sizeof(float), st>>>(
       dact, x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = (long long)cout * cin * 9 + cout;
@@ -1013,8 +1025,9 @@ int ddpb_conv1_wgrad_f32_partials(const void* dact, const float* x, float* scrat
   if (!(cin == 1 && cout == 32)) return DDPB_ERR_SHAPE;
   const Geom g = make_geom(batch, batch_cap, H, W);
   const int bx = conv1_wgrad_f32_blocks(batch);
+  if (g.PW + 1 > kConv1Guard) return DDPB_ERR_SHAPE;
   DDPB_CUDA_OK(launch_k(conv1_wgrad_kernel<1, 32, true>, dim3(bx, cout / 8), dim3(256),
-                        (size_t)kConv1Group * cin * g.PHW * sizeof(float),
+                        ((size_t)kConv1Group * cin * g.PHW + 2 * kConv1Guard) * sizeof(float),
                         static_cast<cudaStream_t>(stream), dact, x, scratch, g));
   *nparts_out = bx;
   return 0;
@@ -1355,7 +1368,7 @@ extern "C" int ddpb_conv1_wgrad_noalloc(const void* dact, const float* x, float*
   const Geom g = make_geom(batch, batch_cap, H, W);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   conv1_wgrad_kernel<kNoAllocCin, kNoAllocCout, false>
-      <<<dim3(bx, cout / 8), 256, (size_t)kConv1Group * cin * g.PHW * sizeof(float), st>>>(
+      <<<dim3(bx, cout / 8), 256, ((size_t)kConv1Group * cin * g.PHW + 2 * kConv1Guard) * sizeof(float), st>>>(
           dact, x, scratch, g);
   DDPB_CUDA_OK(cudaGetLastError());
   const long long n = kNoAllocFloatsPerBlock;
