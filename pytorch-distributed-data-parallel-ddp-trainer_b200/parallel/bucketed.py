@@ -20,6 +20,23 @@ def _align(n: int, a: int) -> int:
     return (n + a - 1) // a * a
 
 
+def plan_buckets(spans, bucket_mb: float):
+    """[(start, end)] float ranges covering the arena front to back, each a multiple of 4 floats and at
+    most ``bucket_mb`` MiB; ``spans`` = (offset, numel) of the parameters in arena order.  A cut may fall
+    inside a parameter."""
+    cap = max(4, int(bucket_mb * (1 << 20) / 4) // 4 * 4)
+    total = _align(spans[-1][0] + spans[-1][1], 4)
+    cuts, start = [], 0
+    for i, (o, n) in enumerate(spans):
+        end = _align(o + n, 4) if i < len(spans) - 1 else total
+        while end - start >= cap:          # close full buckets, cutting through this parameter if needed
+            cuts.append((start, start + cap))
+            start += cap
+        if i == len(spans) - 1 and end > start:
+            cuts.append((start, end))
+    return cuts
+
+
 class BucketedDataParallel:
     def __init__(self, module: torch.nn.Module, rank: int, world_size: int, lr: float = 0.01,
                  bucket_mb: float = 25.0, algo: int = ALGO_AUTO):
@@ -50,23 +67,24 @@ class BucketedDataParallel:
                 v.copy_(p.data)
                 p.data = v
                 self._views.append((p, o))
-        # buckets: contiguous [start, end) float ranges, multiples of 4 floats
-        cap = int(bucket_mb * (1 << 20) / 4)
-        self.buckets, start, members = [], 0, []
-        for i, (p, o) in enumerate(self._views):
-            members.append(i)
-            end = _align(o + p.numel(), 4)
-            if end - start >= cap or i == len(self._views) - 1:
-                self.buckets.append({"start": start, "n": end - start, "members": members, "pending": 0})
-                start, members = end, []
-        self._bucket_of = {}
-        for b_i, b in enumerate(self.buckets):
-            for m in b["members"]:
-                self._bucket_of[m] = b_i
+        # buckets: contiguous [start, end) float ranges, multiples of 4 floats, at most `bucket_mb` each.
+        # Like DDP's Reducer (25 MiB cap) — but a bucket boundary may also fall INSIDE a parameter, so one
+        # very large gradient (the widened CNN's 94 MB fc1 weight) leaves as several exchanges that run
+        # side by side on different streams instead of one long kernel.
+        cuts = plan_buckets([(o, p.numel()) for p, o in self._views], bucket_mb)
+        self.buckets = []
+        self._buckets_of = {i: [] for i in range(len(self._views))}
+        for (b0, b1) in cuts:
+            members = [i for i, (p, o) in enumerate(self._views) if o < b1 and o + p.numel() > b0]
+            for m in members:
+                self._buckets_of[m].append(len(self.buckets))
+            self.buckets.append({"start": b0, "n": b1 - b0, "members": members, "pending": 0})
         self.lr_dev = torch.full((1,), lr, device=self.device)
-        self.side = torch.cuda.Stream(self.device)
+        # bucket exchanges are spread over a few side streams so several can be in flight at once
+        self.sides = [torch.cuda.Stream(self.device) for _ in range(min(3, max(1, len(self.buckets))))]
+        self.side = self.sides[0]
         self._ready = [torch.cuda.Event() for _ in self.buckets]
-        self._done = torch.cuda.Event()
+        self._done = [torch.cuda.Event() for _ in self.sides]
         self.step_count = 0
         self._parity = 0
         for i, (p, _) in enumerate(self._views):
@@ -81,21 +99,27 @@ class BucketedDataParallel:
 
     def _make_hook(self, idx: int):
         def hook(_param):
-            b_i = self._bucket_of[idx]
-            b = self.buckets[b_i]
-            b["pending"] -= 1
-            if b["pending"] == 0:
-                self._launch_bucket(b_i)
+            for b_i in self._buckets_of[idx]:
+                b = self.buckets[b_i]
+                b["pending"] -= 1
+                if b["pending"] == 0:
+                    self._launch_bucket(b_i)
+                elif b["pending"] < 0:
+                    raise RuntimeError("BucketedDataParallel: a parameter received a second gradient in one "
+                                       "step (gradient accumulation / two backward passes are not supported: "
+                                       "one backward per step())")
         return hook
 
     def _launch_bucket(self, b_i: int) -> None:
         b = self.buckets[b_i]
         cur = torch.cuda.current_stream(self.device)
+        side = self.sides[b_i % len(self.sides)]
         self._ready[b_i].record(cur)
-        self.side.wait_event(self._ready[b_i])
+        side.wait_event(self._ready[b_i])
         goff = self.grad_off[self._parity]
+        b["launched"] = True
         self.comm.allreduce_sgd(goff + b["start"] * 4, self.param_off + b["start"] * 4, b["n"],
-                                self.lr_dev, self.algo, slot=b_i % 6, stream=self.side)
+                                self.lr_dev, self.algo, slot=b_i % 6, stream=side)
 
     def step(self, x: torch.Tensor, y: torch.Tensor, loss_fn) -> torch.Tensor:
         """forward + backward (+ per-bucket fused all-reduce/SGD from the grad hooks)."""
@@ -106,11 +130,19 @@ class BucketedDataParallel:
             p.grad = g[o:o + p.numel()].view(p.shape)
         for b in self.buckets:
             b["pending"] = len(b["members"])
+            b["launched"] = False
         loss = loss_fn(self.module(x), y)
         loss.backward()
+        # A parameter that got no gradient this step (a branch not taken, a frozen path) never fires its
+        # hook: its bucket is exchanged now with the zero-filled gradient, so every rank issues the same
+        # sequence of collectives whatever its local graph looked like.
+        for b_i, b in enumerate(self.buckets):
+            if not b["launched"]:
+                self._launch_bucket(b_i)
         cur = torch.cuda.current_stream(self.device)
-        self._done.record(self.side)
-        cur.wait_event(self._done)  # parameters are final before the next forward
+        for side, ev in zip(self.sides, self._done):
+            ev.record(side)
+            cur.wait_event(ev)  # parameters are final before the next forward
         self.step_count += 1
         return loss.detach()
 

@@ -26,3 +26,23 @@ def test_conv3x3_wgrad_image_dest_is_a_bijection_onto_the_bucket():
     col = (3 * 32 + 8) + 3 * 32 + sx * 32 + ci          # row 2 block starts after row 0 (104) and row 1 (96)
     assert int(dest[co * 296 + col]) == (co * 32 + ci) * 9 + r * 3 + sx
     assert int(dest[co * 296 + 96]) == 64 * 32 * 9 + co  # first bias column
+
+
+def test_bucket_plan_cuts_inside_large_parameters():
+    """DDP caps buckets at 25 MiB; a single 94 MB gradient (the widened CNN's fc1) must not become one
+    94 MB exchange: the plan cuts through it, covers the arena exactly once and keeps 16-byte alignment."""
+    from ddp_b200.parallel.bucketed import plan_buckets
+    # arena order of the widened CNN (reverse registration): fc2.b, fc2.w, fc1.b, fc1.w, conv2.b, conv2.w, ...
+    sizes = [10, 7500, 750, 32768 * 750, 128, 128 * 64 * 9, 64, 64 * 3 * 9]
+    spans, off = [], 0
+    for n in sizes:
+        off = (off + 3) // 4 * 4
+        spans.append((off, n))
+        off += n
+    cuts = plan_buckets(spans, 25.0)
+    cap = 25 * (1 << 20) // 4
+    assert cuts[0][0] == 0 and cuts[-1][1] == (off + 3) // 4 * 4
+    assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+    assert all((e - s) % 4 == 0 and 0 < e - s <= cap for s, e in cuts)
+    assert len(cuts) >= 4                      # 94 MB / 25 MiB
+    assert plan_buckets(spans, 1000.0) == [(0, cuts[-1][1])]
