@@ -176,7 +176,12 @@ class SymmetricComm:
         self._h = None
         self.multicast = False
         if multicast is None:
-            multicast = os.environ.get("DDPB_NVLS", "0") == "1"
+            # Default: the multicast (NVLS) communicator from four GPUs up — measured on 8 B200s at
+            # per-rank batch 64: 0.120 ms/step against 0.137 with CUDA IPC, and it wins the all-reduce
+            # sweep at every size.  DDPB_NVLS=0/1 forces either.  Where multicast
+            # cannot be set up, all ranks agree to fall back to CUDA IPC (RuntimeWarning on rank 0).
+            env = os.environ.get("DDPB_NVLS")
+            multicast = (env == "1") if env is not None else world_size >= 4
         if multicast and world_size > 1:
             self._h = self._create_vmm(rank, world_size, payload_bytes)
         if self._h is None:

@@ -110,7 +110,7 @@ class B200DataParallel(_EngineBase):
         mode), see SimpleCNNB200.  ``tail_update`` selects how the last (conv1) bucket of the step is updated:
         "push" (default) / "pull" = split-K reduce + all-reduce + SGD in one kernel with the push or
         pull exchange, "split" = separate reduce kernel followed by the generic bucket update.
-        Environment override: DDPB_TAIL_UPDATE.  ``multicast`` (default: DDPB_NVLS=1) asks for the
+        Environment override: DDPB_TAIL_UPDATE.  ``multicast`` (default: from four GPUs up; DDPB_NVLS=0/1 forces it) asks for the
         VMM + multicast communicator; with it, buckets above 256 KB on more than two GPUs are
         reduced inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
         from .comm import SymmetricComm

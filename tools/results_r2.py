@@ -52,8 +52,9 @@ def throughput_table():
 def variants_table():
     out = ["| GPUs | variant | ms/step | img/s |", "|---:|---|---:|---:|"]
     for n in (1, 2, 4, 8):
-        for tag, name in (("", "bf16x3 (default), CUDA-IPC communicator"),
-                          ("_nvls", "bf16x3, VMM + multicast communicator (DDPB_NVLS=1)"),
+        for tag, name in (("", "bf16x3 (default mode and communicator: multicast from 4 GPUs up, else CUDA IPC)"),
+                          ("_ipc", "bf16x3, CUDA-IPC communicator forced (DDPB_NVLS=0)"),
+                          ("_nvls", "bf16x3, VMM + multicast communicator forced (DDPB_NVLS=1)"),
                           ("_bf16", "bf16 fast mode (--dtype bf16; NOT the reference's precision)")):
             d = load(f"ours_b64_n{n}{tag}.json")
             if d:

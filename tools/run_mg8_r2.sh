@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 run() { timeout 300 python bench.py --gpus 8 --steps 200 --warmup 20 "$@"; }
 run > gpurun_out/ours_b64_n8.json 2> gpurun_out/ours_b64_n8.err; tail -1 gpurun_out/ours_b64_n8.json | cut -c1-260
 run --impl reference > gpurun_out/ref_b64_n8.json 2> gpurun_out/ref_b64_n8.err; tail -1 gpurun_out/ref_b64_n8.json | cut -c1-200
-DDPB_NVLS=1 run > gpurun_out/ours_b64_n8_nvls.json 2> gpurun_out/ours_b64_n8_nvls.err; tail -1 gpurun_out/ours_b64_n8_nvls.json | cut -c1-200
+DDPB_NVLS=0 run > gpurun_out/ours_b64_n8_ipc.json 2> gpurun_out/ours_b64_n8_ipc.err; tail -1 gpurun_out/ours_b64_n8_ipc.json | cut -c1-200
 run --dtype bf16 > gpurun_out/ours_b64_n8_bf16.json 2> gpurun_out/ours_b64_n8_bf16.err; tail -1 gpurun_out/ours_b64_n8_bf16.json | cut -c1-200
 timeout 600 python -m pytest tests/test_multi_gpu.py -q -k "dp_equiv-6 or dp_equiv-8 or fused_sgd-6 or fused_sgd-8 or stress-8 or allreduce-6 or multicast_communicator" 2>&1 | tail -4
 timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29544 \
