@@ -312,6 +312,18 @@ reduce_allreduce_sgd_kernel(const __grid_constant__ PeerPtrs pp, int rank, int s
 // The epoch is one word per slot (all blocks read it on entry; the last block to finish bumps
 // it), so the grid is not limited by the per-block flag words of the pull kernels.
 //
+// Forward progress.  Block i of this rank polls words that block i of every peer sends, so the
+// kernel needs, for every i, block i to become resident on ALL ranks at some point — not all blocks
+// at once.  That holds because (a) a block sends before it polls and never waits for another block
+// of its own grid, so resident blocks always finish once their peers' same-index blocks have run,
+// and (b) the hardware dispatches the blocks of a grid in ascending order as SMs free up, on every
+// rank alike, so the lowest unfinished index is always resident (or next) everywhere.  Up to 592
+// blocks of 256 threads and ~1 KB of shared memory each: they fit beside the 220 KB convolution CTAs
+// (which hold an SM's shared memory, not its thread slots).  Exercised under SM pressure by the
+// step itself (this kernel runs beside the conv2 data gradient and the conv1 weight gradient in every
+// multi-GPU test and bench run, per-rank batch up to 4096) and by tests/mp_workers.py: stress.
+// Every wait is bounded: a peer that never sends becomes a trap, not a hang.
+//
 // MAP selects where output idx of the partial vectors lives in the gradient / parameter slices:
 //   0  identity
 //   1  the conv3x3 <CI=32, CO=64> weight-gradient accumulator image (csrc/conv_tc.cu):

@@ -173,6 +173,7 @@ class B200DataParallel(_EngineBase):
         self.side2 = torch.cuda.Stream(self.device)
         self.copy = torch.cuda.Stream(self.device)
         self._ev_fork = torch.cuda.Event()
+        self._ev_loss_done = torch.cuda.Event()
         self._ev_join = torch.cuda.Event()
         self._ev_join2 = torch.cuda.Event()
         self._ev_dgrad = torch.cuda.Event()
@@ -261,14 +262,26 @@ class B200DataParallel(_EngineBase):
         with nvtx_range("fwd+loss"):
             m.forward_loss(x, y, b, main, parity, pack=False)
         with nvtx_range("bwd linear"):
+            if m.x3:
+                # the dW half of the linear backward needs only act2 and dlogits: its stream forks right
+                # after the loss, so the fl bucket's chain (dW half -> reduce -> exchange+SGD) starts while
+                # the dX half still runs here
+                self._ev_loss_done.record(main)
+                self.side.wait_event(self._ev_loss_done)
             m.backward_head(b, main, parity, defer_reduce=True)
         self._ev_fork.record(main)
-        self.side.wait_event(self._ev_fork)
+        if not m.x3:
+            self.side.wait_event(self._ev_fork)
         self.side2.wait_event(self._ev_fork)
         with nvtx_range("bucket fl: all-reduce+sgd, re-pack"):
-            m.backward_head_reduce(self.side, parity)   # bf16x3: split partials -> fl.weight gradient
+            m.backward_head_reduce(self.side, parity)   # bf16x3: dW half + its split-partial sum
+            if m.x3:
+                # fl.weight may only be rewritten once its last reader, the dX half on the main stream,
+                # is done; the update then has two predecessors -> ordinary (non-programmatic) launch
+                self.side.wait_event(self._ev_fork)
             if "fl" not in self._ablate:
-                self._update(self.bucket_fl, parity, 0, self.side)
+                with (self._plain_launch() if m.x3 else contextlib.nullcontext()):
+                    self._update(self.bucket_fl, parity, 0, self.side)
             if "pack" not in self._ablate and not m.x3:
                 m.pack_weights(self.side)  # new fl.weight -> tensor-core tiles for the next step
         self._ev_join.record(self.side)
