@@ -168,9 +168,14 @@ class B200DataParallel(_EngineBase):
                              precision=self.precision,
                              ablate=",".join(sorted(self._ablate)))
 
-        self.main = torch.cuda.Stream(self.device)
-        self.side = torch.cuda.Stream(self.device)
-        self.side2 = torch.cuda.Stream(self.device)
+        # Stream priorities (lower number = its blocks are dispatched first): the two bucket streams run
+        # above the main stream, so a bucket's exchange never queues behind the long convolution backward
+        # for SM slots (2 GPUs, batch 64: 0.1130 -> 0.1088 ms/step; raising the main stream instead:
+        # 0.1184).  DDPB_STREAM_PRIO="main,side,side2" overrides.
+        prio = [int(v) for v in os.environ.get("DDPB_STREAM_PRIO", "0,-1,-1").split(",")]
+        self.main = torch.cuda.Stream(self.device, priority=prio[0])
+        self.side = torch.cuda.Stream(self.device, priority=prio[1])
+        self.side2 = torch.cuda.Stream(self.device, priority=prio[2])
         self.copy = torch.cuda.Stream(self.device)
         self._ev_fork = torch.cuda.Event()
         self._ev_loss_done = torch.cuda.Event()
