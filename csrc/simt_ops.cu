@@ -54,6 +54,29 @@ __device__ __forceinline__ void warp_reduce80(float (&v)[80], int lane) {
 #pragma unroll
   for (int i = 0; i < 5; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);
 }
+// Same scheme for 40 values: v[0..4] of lane l end up as the totals of elements
+// 20*b4 + 10*b3 + 5*b2 + (0..4); lanes l, l^1, l^2, l^3 hold the same five totals.
+__device__ __forceinline__ void warp_reduce40(float (&v)[40], int lane) {
+#define DDPB_HALVE(H, BIT)                                          \
+  _Pragma("unroll") for (int i = 0; i < H; ++i) {                   \
+    const bool up = (lane & BIT) != 0;                              \
+    const float send = up ? v[i] : v[i + H];                        \
+    const float keep = up ? v[i + H] : v[i];                        \
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, BIT);          \
+  }
+  DDPB_HALVE(20, 16)
+  DDPB_HALVE(10, 8)
+  DDPB_HALVE(5, 4)
+#undef DDPB_HALVE
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    v[i] += __shfl_xor_sync(0xffffffffu, v[i], 2);
+    v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);
+  }
+}
+__device__ __forceinline__ int warp_reduce40_base(int lane) {
+  return ((lane >> 4) & 1) * 20 + ((lane >> 3) & 1) * 10 + ((lane >> 2) & 1) * 5;
+}
 __device__ __forceinline__ int warp_reduce80_base(int lane) {
   return ((lane >> 4) & 1) * 40 + ((lane >> 3) & 1) * 20 + ((lane >> 2) & 1) * 10 +
          ((lane >> 1) & 1) * 5;
@@ -184,12 +207,16 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
 // 2*chunk+1) and the whole computation is exact fp32 FMA — the reference-precision mode uses this
 // for the Cin = 1 layer, which cuDNN also runs in plain fp32 (profiles/precision.md); otherwise bf16
 // planes.
+// A thread accumulates CH channels x 9 taps (+ CH bias sums): 8 channels from bf16 planes (80
+// accumulators), 4 — one fp32 plane — in the exact-fp32 variant (40 accumulators: three CTAs per SM
+// instead of one, a cheaper final reduction).
 template <int CIN0, int C1, bool F32IN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, F32IN ? 3 : 1)
 conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
                    float* __restrict__ partial, Geom g) {
   constexpr int NW = CIN0 * 9;
-  constexpr int NV = 8 * NW + 8;
+  constexpr int CH = F32IN ? 4 : 8;  // channels per thread (= per blockIdx.y)
+  constexpr int NV = CH * NW + CH;
   constexpr int PF = 4;          // gradient vectors kept in flight per thread
   extern __shared__ float xs_raw[];  // [guard][kConv1Group][CIN0][PHW][guard], guards zeroed once
   float* xs = xs_raw + kConv1Guard;
@@ -201,16 +228,15 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
   // wrote (dact) may be read before this; a no-op for plain launches
   pdl_sync();
   const int chunk = blockIdx.y;
-  static_assert(NV == 80, "warp_reduce80 expects 8*(CIN0*9) + 8 == 80 accumulators (CIN0 == 1)");
-  float acc[NV];  // [c*NW + j] weight taps, then [8*NW + c] bias
+  static_assert(NV == 80 || NV == 40, "warp reductions exist for 80 and 40 accumulators (CIN0 == 1)");
+  float acc[NV];  // [c*NW + j] weight taps, then [CH*NW + c] bias
 #pragma unroll
   for (int i = 0; i < NV; ++i) acc[i] = 0.f;
   const int ipb = (g.batch + gridDim.x - 1) / gridDim.x;
   const int lo = blockIdx.x * ipb;
   const int hi = min(g.batch, lo + ipb);
-  // 16-byte rows: bf16 -> plane `chunk`; fp32 -> planes 2*chunk (channels 0-3) and 2*chunk+1 (4-7)
-  const uint4* plane = static_cast<const uint4*>(dact_v) +
-                       (long long)(F32IN ? 2 * chunk : chunk) * g.plane_rows + kGuard;
+  // 16-byte rows: plane `chunk` holds this thread's channels in either format
+  const uint4* plane = static_cast<const uint4*>(dact_v) + (long long)chunk * g.plane_rows + kGuard;
   for (int img0 = lo; img0 < hi; img0 += kConv1Group) {
     const int ng = min(kConv1Group, hi - img0);
     const int nidx = ng * g.PHW;
@@ -220,13 +246,11 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
     // border rows of dact are zero, so every row of the group can be accumulated unconditionally;
     // the window read stays inside the image's padded tile for interior rows only -> test those.
     for (int base = threadIdx.x; base < nidx; base += PF * blockDim.x) {
-      uint4 dv[PF], dv2[PF];
+      uint4 dv[PF];
 #pragma unroll
       for (int u = 0; u < PF; ++u) {
         const int idx = base + u * blockDim.x;
         dv[u] = idx < nidx ? plane[(long long)img0 * g.PHW + idx] : make_uint4(0, 0, 0, 0);
-        if (F32IN)
-          dv2[u] = idx < nidx ? plane[g.plane_rows + (long long)img0 * g.PHW + idx] : make_uint4(0, 0, 0, 0);
       }
 #pragma unroll
       for (int u = 0; u < PF; ++u) {
@@ -240,8 +264,6 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
         if (F32IN) {
           d[0] = __uint_as_float(dv[u].x); d[1] = __uint_as_float(dv[u].y);
           d[2] = __uint_as_float(dv[u].z); d[3] = __uint_as_float(dv[u].w);
-          d[4] = __uint_as_float(dv2[u].x); d[5] = __uint_as_float(dv2[u].y);
-          d[6] = __uint_as_float(dv2[u].z); d[7] = __uint_as_float(dv2[u].w);
         } else {
           unpack8(dv[u], d);
         }
@@ -253,8 +275,8 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
 #pragma unroll
           for (int s2 = 0; s2 < 3; ++s2) in[r * 3 + s2] = xi[(r - 1) * g.PW + (s2 - 1)];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          acc[8 * NW + c] += d[c];
+        for (int c = 0; c < CH; ++c) {
+          acc[CH * NW + c] += d[c];
 #pragma unroll
           for (int j = 0; j < NW; ++j) acc[c * NW + j] = fmaf(d[c], in[j], acc[c * NW + j]);
         }
@@ -262,11 +284,20 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
     }
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  warp_reduce80(acc, lane);
-  if ((lane & 1) == 0) {
-    const int base = warp_reduce80_base(lane);
+  if constexpr (NV == 80) {
+    warp_reduce80(acc, lane);
+    if ((lane & 1) == 0) {
+      const int base = warp_reduce80_base(lane);
 #pragma unroll
-    for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+      for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+    }
+  } else {
+    warp_reduce40(acc, lane);
+    if ((lane & 3) == 0) {
+      const int base = warp_reduce40_base(lane);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+    }
   }
   __syncthreads();
   float* dst = partial + (long long)blockIdx.x * (C1 * NW + C1);
@@ -274,8 +305,8 @@ conv1_wgrad_kernel(const void* __restrict__ dact_v, const float* __restrict__ x,
     float s = 0.f;
 #pragma unroll
     for (int wdx = 0; wdx < 8; ++wdx) s += red[wdx][i];
-    if (i < 8 * NW) dst[chunk * 8 * NW + i] = s;
-    else dst[C1 * NW + chunk * 8 + (i - 8 * NW)] = s;
+    if (i < CH * NW) dst[chunk * CH * NW + i] = s;
+    else dst[C1 * NW + chunk * CH + (i - CH * NW)] = s;
   }
 }
 
@@ -672,8 +703,10 @@ struct XentArgs {
   float* loss;
 };
 
+// IMG = images per thread: 8 (80 accumulators, one CTA per SM) for small batches, 4 (two CTAs per SM:
+// twice the loads in flight) for large ones, where the kernel is bound by DRAM latency, not by FMAs.
 template <int NOUT, int IMG>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, IMG == 8 ? 1 : 2)
 linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ W,
                       float* __restrict__ partial, Geom g, int C, int vec_per_slice, XentArgs xe) {
   pdl_sync();
@@ -684,7 +717,7 @@ linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
   const int img0 = blockIdx.y * IMG;
   const int v_begin = blockIdx.x * vec_per_slice;
   const int v_end = min(nvec, v_begin + vec_per_slice);
-  static_assert(IMG * NOUT == 80, "warp_reduce80 expects 80 accumulators");
+  static_assert(IMG * NOUT == 80 || IMG * NOUT == 40, "warp reductions exist for 80 and 40 accumulators");
   float acc[IMG * NOUT];
 #pragma unroll
   for (int i = 0; i < IMG * NOUT; ++i) acc[i] = 0.f;
@@ -715,11 +748,20 @@ linear_fwd_f32_kernel(const float4* __restrict__ act, const float* __restrict__ 
     }
   }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  warp_reduce80(acc, lane);
-  if ((lane & 1) == 0) {
-    const int base = warp_reduce80_base(lane);
+  if constexpr (IMG * NOUT == 80) {
+    warp_reduce80(acc, lane);
+    if ((lane & 1) == 0) {
+      const int base = warp_reduce80_base(lane);
 #pragma unroll
-    for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+      for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+    }
+  } else {
+    warp_reduce40(acc, lane);
+    if ((lane & 3) == 0) {
+      const int base = warp_reduce40_base(lane);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) red[warp][base + i] = acc[i];
+    }
   }
   __syncthreads();
   for (int t = threadIdx.x; t < IMG * NOUT; t += blockDim.x) {
@@ -1011,10 +1053,12 @@ int ddpb_reduce_partials(const float* part, int nparts, long long n, float* out,
 // reduce + all-reduce + SGD kernel consumes them unchanged); scratch size:
 // ddpb_conv1_wgrad_f32_scratch_bytes.
 static int conv1_wgrad_f32_blocks(int batch) {
-  // one block per image up to two per SM-quarter: each block ends in an 80-value reduction whose
-  // partial is re-read by the reduce, so more blocks than ~2 waves only add reduction work
-  int bx = batch < 74 ? batch : 74;
-  return bx < 1 ? 1 : bx;
+  // x-blocks (each times 8 channel groups in y).  Three CTAs fit an SM (444 slots on 148 SMs): small
+  // batches get one image per block, large ones 55 x 8 = 440 blocks with an even share of images each
+  // (every block ends in a 40-value reduction whose partial the update kernel re-reads).
+  if (batch <= 74) return batch < 1 ? 1 : batch;
+  const int ipb = (batch + 54) / 55;
+  return (batch + ipb - 1) / ipb;
 }
 size_t ddpb_conv1_wgrad_f32_scratch_bytes(int cin, int cout) {
   return static_cast<size_t>(74) * (cout * cin * 9 + cout) * sizeof(float);
@@ -1026,7 +1070,7 @@ int ddpb_conv1_wgrad_f32_partials(const void* dact, const float* x, float* scrat
   const Geom g = make_geom(batch, batch_cap, H, W);
   const int bx = conv1_wgrad_f32_blocks(batch);
   if (g.PW + 1 > kConv1Guard) return DDPB_ERR_SHAPE;
-  DDPB_CUDA_OK(launch_k(conv1_wgrad_kernel<1, 32, true>, dim3(bx, cout / 8), dim3(256),
+  DDPB_CUDA_OK(launch_k(conv1_wgrad_kernel<1, 32, true>, dim3(bx, cout / 4), dim3(256),
                         ((size_t)kConv1Group * cin * g.PHW + 2 * kConv1Guard) * sizeof(float),
                         static_cast<cudaStream_t>(stream), dact, x, scratch, g));
   *nparts_out = bx;
@@ -1143,10 +1187,11 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
 
 // ---- fp32-plane (precision-parity) linear layer.  Scratch sizes: ddpb_linear_fwd_f32_scratch_bytes /
 // ddpb_linear_bwd_scratch_bytes (the partial layout of the backward is the same as the bf16 one).
+static int linear_fwd_f32_img(int batch) { return batch >= 512 ? 4 : 8; }
 static void linear_fwd_f32_geom(int batch, int nvec, int& S, int& per, int& groups) {
-  constexpr int IMG = 8;
+  const int IMG = linear_fwd_f32_img(batch);
   groups = (batch + IMG - 1) / IMG;
-  const int want = ddpb_num_sms() / groups;  // one CTA per SM (~200 registers), one wave
+  const int want = (IMG == 8 ? 1 : 2) * ddpb_num_sms() / groups;  // one wave of resident CTAs
   const int maxS = (nvec + 255) / 256;
   S = want < 1 ? 1 : (want > maxS ? maxS : want);
   per = ((nvec + S - 1) / S + 255) / 256 * 256;
@@ -1165,6 +1210,10 @@ int ddpb_linear_fwd_f32(const void* act, const float* Wt, float* partial, int* S
   int S, per, groups;
   linear_fwd_f32_geom(batch, nvec, S, per, groups);
   if (S_out) *S_out = S;
+  if (linear_fwd_f32_img(batch) == 4)
+    return static_cast<int>(launch_k(linear_fwd_f32_kernel<10, 4>, dim3(S, groups), dim3(256), 0,
+                                     static_cast<cudaStream_t>(stream), static_cast<const float4*>(act),
+                                     Wt, partial, g, C, per, XentArgs{}));
   return static_cast<int>(launch_k(linear_fwd_f32_kernel<10, 8>, dim3(S, groups), dim3(256), 0,
                                    static_cast<cudaStream_t>(stream), static_cast<const float4*>(act),
                                    Wt, partial, g, C, per, XentArgs{}));

@@ -173,7 +173,8 @@ def test_conv1_wgrad_split(nat, batch, cap):
     _check("conv1_wgrad_split db", out[288:], bref.grad, 2e-5)
 
 
-@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (130, 130)])
+# 600: the large-batch forward variant (4 images per thread, two CTAs per SM)
+@pytest.mark.parametrize("batch,cap", [(3, 3), (64, 64), (37, 64), (130, 130), (600, 600)])
 def test_linear_f32_fwd_loss_bwd(nat, batch, cap):
     torch.manual_seed(25)
     C = 64
