@@ -589,6 +589,74 @@ softmax_xent_kernel(const float* __restrict__ partial, int S, const float* __res
   }
 }
 
+// Small batches (batch * NOUT <= 1024 threads, no packed output): ONE block, no ticket and no
+// second phase across blocks — at per-rank batch 64 the multi-block version above spends ~9.6 us on
+// 640 numbers, most of it in its cross-block hand-over.  Thread (image, class) adds its S slices (in
+// slice order) and the bias; one thread per image does the softmax; NOUT threads add the bias-gradient
+// columns and one the loss, each in image order (deterministic).
+template <int NOUT>
+__global__ void __launch_bounds__(1024)
+softmax_xent_small_kernel(const float* __restrict__ partial, int S, const float* __restrict__ bias,
+                          const long long* __restrict__ labels, float* __restrict__ logits,
+                          float* __restrict__ dlogits, float* __restrict__ dbias, float* __restrict__ loss,
+                          int batch) {
+  __shared__ float zs[1024];
+  __shared__ float ls[128];
+  pdl_sync();
+  const int npair = batch * NOUT;
+  const int p = threadIdx.x;
+  if (p < npair) {
+    float z = 0.f;
+    int sl = 0;
+    for (; sl + 4 <= S; sl += 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = partial[(long long)(sl + u) * npair + p];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) z += v[u];
+    }
+    for (; sl < S; ++sl) z += partial[(long long)sl * npair + p];
+    z += bias[p % NOUT];
+    zs[p] = z;
+    logits[p] = z;
+  }
+  __syncthreads();
+  if (p < batch) {
+    const float inv = 1.0f / static_cast<float>(batch);
+    float z[NOUT];
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) z[j] = zs[p * NOUT + j];
+    float m = z[0];
+#pragma unroll
+    for (int j = 1; j < NOUT; ++j) m = fmaxf(m, z[j]);
+    float se = 0.f;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) se += expf(z[j] - m);
+    const float lse = m + logf(se);
+    const int y = static_cast<int>(labels[p]);
+    float lsum = 0.f;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      const float pr = expf(z[j] - lse);
+      const float d = (pr - (j == y ? 1.f : 0.f)) * inv;
+      dlogits[p * NOUT + j] = d;
+      zs[p * NOUT + j] = d;
+      if (j == y) lsum = lse - z[j];
+    }
+    ls[p] = lsum;
+  }
+  __syncthreads();
+  if (p < NOUT) {
+    float sacc = 0.f;
+    for (int i = 0; i < batch; ++i) sacc += zs[i * NOUT + p];
+    dbias[p] = sacc;
+  } else if (p == 32) {
+    float sacc = 0.f;
+    for (int i = 0; i < batch; ++i) sacc += ls[i];
+    loss[0] = sacc / static_cast<float>(batch);
+  }
+}
+
 // ------------------------------------------------------------------ linear backward
 // dact[img][k] = relu'(act[img][k]) * sum_j dlogits[img][j] W[j][k]     (bf16 planes)
 // dW[j][k]    = sum_img dlogits[img][j] act[img][k]                      (fp32, via partials)
@@ -1138,6 +1206,13 @@ static int softmax_xent_launch(const float* partial, int S, const float* bias, c
                                float* logits, float* dlogits, float* dbias, float* loss, int nout,
                                int batch, void* dl_packed, void* stream) {
   if (nout != 10 || batch <= 0 || logits == nullptr) return DDPB_ERR_SHAPE;
+  if (dl_packed == nullptr && batch * 10 <= 1024) {  // one block does it all
+    const int threads = (batch * 10 + 31) / 32 * 32 < 64 ? 64 : (batch * 10 + 31) / 32 * 32;
+    return static_cast<int>(launch_k(softmax_xent_small_kernel<10>, dim3(1), dim3(threads), 0,
+                                     static_cast<cudaStream_t>(stream), partial, S, bias,
+                                     static_cast<const long long*>(labels), logits, dlogits, dbias, loss,
+                                     batch));
+  }
   // with packed output the grid also covers the zero rows up to the end of the last 128-image tile
   const int covered = dl_packed ? (batch + 127) / 128 * 128 : batch;
   const int blocks = (covered + kXentImgs - 1) / kXentImgs;
