@@ -303,6 +303,41 @@ int ddpb_allreduce(void* comm, size_t in_off, size_t out_off, long long nbytes, 
                    int slot, void* stream);
 int ddpb_broadcast(void* comm, size_t off, long long nbytes, int root, int slot, void* stream);
 
+/* ---- fully connected layers of any shape on the tensor cores (csrc/gemm_tc.cu); replaces the
+ * cuBLAS GEMMs behind nn.Linear (reference model.py:16, train_ddp.py:199) for shapes beyond the
+ * 10-class head of the step engine (BASELINE.json config 4: fc 32768 -> 750 -> 10).
+ * A matrix of `rows` x `k` fp32 values is packed once into "split row planes" (x = hi + lo, both
+ * bf16; [2 sets][k/8 planes][rows][8], rows and k zero-padded to ddpb_gemm_pad() elements); the same
+ * packed tensor is a K-major operand (reduce over k) or an MN-major operand (reduce over rows) of
+ * tcgen05.mma, so x, W and dy are packed once each for the layer's three GEMMs.  Every K step issues
+ * hi.hi + lo.hi + hi.lo ("bf16x3": above TF32 operand precision), fp32 accumulation.
+ *   pack_rows_split: `packed` must be zero-filled when it is allocated; `mask` (optional, same shape
+ *     and ld as src) zeroes the elements whose mask value is <= 0 (ReLU backward fused in the pack).
+ *   gemm_split: out[m][n] (or out[n][m] when transposed) = sum_k A[m][k] B[n][k]; a_rows/a_k and
+ *     b_rows/b_k are the shapes the operands were packed from, a_mn/b_mn = 1 reads an operand
+ *     MN-major.  Supported majors: (0,0), (1,0), (1,1).  k_splits > 1 writes that many partial images
+ *     split_stride floats apart (sum them, add a bias, apply ReLU with ddpb_splitk_reduce).
+ *   colsum: out[c] = sum_r src[r][c] (masked like the pack): the bias gradient. */
+int ddpb_gemm_pad(void);
+size_t ddpb_pack_rows_split_bytes(int rows, int k);
+int ddpb_pack_rows_split(const float* src, const float* mask, long long ld, int rows, int k, void* packed,
+                         void* stream);
+int ddpb_gemm_split(const void* a, int a_rows, int a_k, int a_mn, const void* b, int b_rows, int b_k, int b_mn,
+                    int M, int N, int K, float* out, long long ld, int transposed, int k_splits,
+                    long long split_stride, void* stream);
+int ddpb_gemm_split_suggest_splits(int M, int N, int K);
+int ddpb_splitk_reduce(const float* partial, int nsplit, long long split_stride, int rows, int cols, long long ld,
+                       const float* bias, int relu, float* out, long long ld_out, void* stream);
+int ddpb_colsum(const float* src, const float* mask, int rows, int cols, long long ld, float* out, void* stream);
+/* ---- fused (bias +) ReLU + 2x2 max pool over NCHW fp32 (what nn.ReLU -> nn.MaxPool2d(2) compute,
+ * one pass); `code` [batch][C][H/2][W/2] bytes: index of the winning input (first maximum, row-major)
+ * or 4 where the pooled value is <= 0.  H even, W a multiple of 4.  No reference counterpart (its
+ * model has no pooling layer, model.py:8-16); BASELINE.json names the op for the widened CNN. */
+int ddpb_relu_maxpool2_fwd(const float* in, const float* bias, float* out, unsigned char* code, int batch, int C,
+                           int H, int W, void* stream);
+int ddpb_relu_maxpool2_bwd(const float* dout, const unsigned char* code, float* din, int batch, int C, int H, int W,
+                           void* stream);
+
 /* ---- p -= lr*g with lr read from device memory (single-GPU path; multi-GPU runs fuse the
  * update into the all-reduce).  reference train_ddp.py:41,200. */
 int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream);

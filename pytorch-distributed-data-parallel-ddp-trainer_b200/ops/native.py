@@ -84,6 +84,16 @@ _SIGNATURES = {
     "ddpb_conv3x3_pack_tf32": (I, [P, P, I, I, P]),
     "ddpb_conv3x3_fwd_tf32": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
     "ddpb_conv3x3_dgrad_tf32": (I, [P, P, P, P, I, I, I, I, I, I, I, P]),
+    # fully connected layers of any shape (csrc/gemm_tc.cu) + fused ReLU/max-pool
+    "ddpb_gemm_pad": (I, []),
+    "ddpb_pack_rows_split_bytes": (c_size_t, [I, I]),
+    "ddpb_pack_rows_split": (I, [P, P, LL, I, I, P, P]),
+    "ddpb_gemm_split": (I, [P, I, I, I, P, I, I, I, I, I, I, P, LL, I, I, LL, P]),
+    "ddpb_gemm_split_suggest_splits": (I, [I, I, I]),
+    "ddpb_splitk_reduce": (I, [P, I, LL, I, I, LL, P, I, P, LL, P]),
+    "ddpb_colsum": (I, [P, P, I, I, LL, P, P]),
+    "ddpb_relu_maxpool2_fwd": (I, [P, P, P, P, I, I, I, I, P]),
+    "ddpb_relu_maxpool2_bwd": (I, [P, P, P, I, I, I, I, P]),
 }
 
 #: execution precisions of the step (models/simple_cnn.py): "bf16x3" = the reference's numerics
@@ -485,3 +495,61 @@ def conv3x3_dgrad_tf32(dout, packed, mask, din, cin, cout, batch, batch_cap, H, 
     check(lib().ddpb_conv3x3_dgrad_tf32(ptr(dout), ptr(packed), ptr(mask), ptr(din), cin, cout, batch,
                                         batch_cap, H, W, int(round_out), stream_ptr(stream)),
           "conv3x3_dgrad_tf32")
+
+
+# ----------------------------------------------------------------------------- general linear layers
+class PackedMatrix:
+    """A fp32 matrix [rows, k] packed as split row planes (csrc/gemm_tc.cu): the operand format of
+    ``gemm_split``.  ``rows`` may change from call to call up to the capacity it was created with."""
+
+    def __init__(self, rows_cap: int, k: int, device="cuda"):
+        self.rows_cap, self.k, self.rows = int(rows_cap), int(k), 0
+        nbytes = int(lib().ddpb_pack_rows_split_bytes(self.rows_cap, self.k))
+        self.buf = torch.zeros(nbytes // 2, dtype=torch.bfloat16, device=device)
+
+    def pack(self, src: torch.Tensor, mask: torch.Tensor | None = None, stream=None) -> "PackedMatrix":
+        assert src.dim() == 2 and src.dtype == torch.float32 and src.stride(1) == 1, "row-major fp32 matrix"
+        rows, k = src.shape
+        assert k == self.k and rows <= self.rows_cap, (src.shape, self.rows_cap, self.k)
+        if mask is not None:
+            assert mask.shape == src.shape and mask.dtype == torch.float32 and mask.stride() == src.stride()
+        check(lib().ddpb_pack_rows_split(ptr(src), ptr(mask), src.stride(0), rows, k, ptr(self.buf),
+                                         stream_ptr(stream)), "pack_rows_split")
+        self.rows = rows
+        return self
+
+
+def gemm_split(a: PackedMatrix, a_mn: bool, b: PackedMatrix, b_mn: bool, M: int, N: int, K: int,
+               out: torch.Tensor, ld: int, transposed: bool, k_splits: int = 1, split_stride: int = 0,
+               stream=None):
+    """out[m][n] (out[n][m] when ``transposed``) = sum_k A[m][k] * B[n][k] on the tensor cores (bf16x3)."""
+    check(lib().ddpb_gemm_split(ptr(a.buf), a.rows_cap, a.k, int(a_mn), ptr(b.buf), b.rows_cap, b.k, int(b_mn),
+                                M, N, K, ptr(out), ld, int(transposed), k_splits, split_stride,
+                                stream_ptr(stream)), "gemm_split")
+
+
+def gemm_suggest_splits(M: int, N: int, K: int) -> int:
+    return int(lib().ddpb_gemm_split_suggest_splits(M, N, K))
+
+
+def splitk_reduce(partial, nsplit, split_stride, rows, cols, ld, bias, relu, out, ld_out=None, stream=None):
+    check(lib().ddpb_splitk_reduce(ptr(partial), nsplit, split_stride, rows, cols, ld, ptr(bias), int(relu),
+                                   ptr(out), ld if ld_out is None else ld_out, stream_ptr(stream)),
+          "splitk_reduce")
+
+
+def colsum(src, mask, out, stream=None):
+    rows, cols = src.shape
+    check(lib().ddpb_colsum(ptr(src), ptr(mask), rows, cols, src.stride(0), ptr(out), stream_ptr(stream)), "colsum")
+
+
+def relu_maxpool2_fwd(x, bias, out, code, stream=None):
+    b, c, h, w = x.shape
+    check(lib().ddpb_relu_maxpool2_fwd(ptr(x), ptr(bias), ptr(out), ptr(code), b, c, h, w, stream_ptr(stream)),
+          "relu_maxpool2_fwd")
+
+
+def relu_maxpool2_bwd(dout, code, din, stream=None):
+    b, c, h, w = din.shape
+    check(lib().ddpb_relu_maxpool2_bwd(ptr(dout), ptr(code), ptr(din), b, c, h, w, stream_ptr(stream)),
+          "relu_maxpool2_bwd")

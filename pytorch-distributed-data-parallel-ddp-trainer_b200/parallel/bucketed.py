@@ -89,6 +89,14 @@ class BucketedDataParallel:
         self._parity = 0
         for i, (p, _) in enumerate(self._views):
             p.register_post_accumulate_grad_hook(self._make_hook(i))
+        # Layers that can write a weight gradient straight into a caller-given buffer (models/linear.py:
+        # ``weight_grad_out``) get their slice of the arena: no zero-fill and no accumulate pass over it.
+        self._direct = {}
+        for mod in module.modules():
+            if hasattr(mod, "weight_grad_out") and isinstance(getattr(mod, "weight", None), torch.nn.Parameter):
+                for i, (p, _) in enumerate(self._views):
+                    if p is mod.weight:
+                        self._direct[i] = mod
         self.sync_params()
 
     def sync_params(self, src: int = 0) -> None:
@@ -98,7 +106,12 @@ class BucketedDataParallel:
             torch.cuda.synchronize(self.device)
 
     def _make_hook(self, idx: int):
-        def hook(_param):
+        def hook(param):
+            if idx in self._direct:
+                p, o = self._views[idx]
+                dst = self.flat_grads[self._parity][o:o + p.numel()]
+                if param.grad.data_ptr() != dst.data_ptr():  # autograd cloned instead of adopting the buffer
+                    dst.view(p.shape).copy_(param.grad)
             for b_i in self._buckets_of[idx]:
                 b = self.buckets[b_i]
                 b["pending"] -= 1
@@ -125,9 +138,14 @@ class BucketedDataParallel:
         """forward + backward (+ per-bucket fused all-reduce/SGD from the grad hooks)."""
         self._parity = self.step_count & 1
         g = self.flat_grads[self._parity]
-        g.zero_()
-        for p, o in self._views:  # gradients accumulate in place into this step's arena copy
-            p.grad = g[o:o + p.numel()].view(p.shape)
+        for i, (p, o) in enumerate(self._views):
+            v = g[o:o + p.numel()].view(p.shape)
+            if i in self._direct:      # the layer's backward writes the whole gradient into the arena itself
+                self._direct[i].weight_grad_out = v
+                p.grad = None
+            else:                      # gradients accumulate in place into this step's arena copy
+                v.zero_()
+                p.grad = v
         for b in self.buckets:
             b["pending"] = len(b["members"])
             b["launched"] = False

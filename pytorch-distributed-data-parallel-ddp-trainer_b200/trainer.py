@@ -110,6 +110,11 @@ def ddp_train(rank: int, world_size: int, epochs: int, batch_size: int, *, data_
                     stats.setdefault("img_per_s", []).append(imgs / max(secs, 1e-9))
                     stats.setdefault("device_ms_per_step", []).append(step_stats["ms_mean"])
                 ckpt.save_checkpoint(epoch, engine.state_dict(), engine.optimizer_state_dict(), ckpt_dir)
+    except Exception as e:
+        # The parent reports whichever rank's exception it sees first, often a peer's "connection closed":
+        # every rank names its own failure before the group is torn down, so the root cause is in the log.
+        print(f"Rank {rank}: failed with {type(e).__name__}: {e}", file=sys.stderr, flush=True)
+        raise
     finally:
         if engine is not None:
             try:

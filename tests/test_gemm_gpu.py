@@ -1,0 +1,213 @@
+"""General linear layers on the tensor cores (csrc/gemm_tc.cu, models/linear.py) against fp64 oracles:
+the packed operand format, the three operand-major combinations of the GEMM, split-K reduction, the
+fused ReLU + max-pool pass, ``LinearB200`` and ``WideCNNB200`` as autograd modules.
+What the reference delegates to cuBLAS through nn.Linear (reference model.py:16, train_ddp.py:199)."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    from ddp_b200.ops import native
+    native.lib()
+    return native
+
+
+def _rel(a, ref):
+    return float((a.double() - ref).abs().max() / ref.abs().max())
+
+
+def test_pack_rows_split_layout_and_padding(nat):
+    dev = "cuda"
+    torch.manual_seed(0)
+    rows, k = 37, 750                       # k is neither a multiple of 8 nor of 4 floats per row start
+    x = torch.randn(rows, k, device=dev)
+    pm = nat.PackedMatrix(100, k, dev)
+    pm.buf.fill_(7.0)                       # poison: everything the pack must define gets overwritten
+    pm.pack(x)
+    rp, kp = 256, 768
+    planes = pm.buf.view(2, kp // 8, rp, 8).float()
+    hi = x.bfloat16().float()
+    lo = (x - hi).bfloat16().float()
+    got_hi = planes[0].permute(1, 0, 2).reshape(rp, kp)
+    got_lo = planes[1].permute(1, 0, 2).reshape(rp, kp)
+    assert torch.equal(got_hi[:rows, :k], hi) and torch.equal(got_lo[:rows, :k], lo)
+    # the tail of the last real chunk and the rows up to the next multiple of 32 are written as zeros
+    assert float(got_hi[:rows, k:752].abs().max()) == 0 and float(got_lo[:rows, k:752].abs().max()) == 0
+    assert float(got_hi[rows:64, :752].abs().max()) == 0 and float(got_lo[rows:64, :752].abs().max()) == 0
+    # a mask zeroes where it is <= 0
+    m = torch.randn(rows, k, device=dev)
+    pm.pack(x, m)
+    got_hi = pm.buf.view(2, kp // 8, rp, 8)[0].float().permute(1, 0, 2).reshape(rp, kp)
+    assert torch.equal(got_hi[:rows, :k], torch.where(m > 0, hi, torch.zeros_like(hi)))
+
+
+@pytest.mark.parametrize("M,N,K", [(750, 100, 1000), (10, 37, 750), (300, 256, 4096), (128, 300, 64)])
+def test_gemm_forward_majors_against_fp64(nat, M, N, K):
+    """A = W[M][K] K-major, B = x[N][K] K-major, stored transposed (y[N][M]) with split-K + bias + ReLU."""
+    dev = "cuda"
+    torch.manual_seed(1)
+    w = torch.randn(M, K, device=dev)
+    x = torch.randn(N, K, device=dev)
+    bias = torch.randn(M, device=dev)
+    a = nat.PackedMatrix(M, K, dev).pack(w)
+    b = nat.PackedMatrix(N, K, dev).pack(x)
+    ref = x.double() @ w.double().t()
+    y = torch.full((N, M), float("nan"), device=dev)
+    nat.gemm_split(a, False, b, False, M, N, K, y, M, True)
+    assert _rel(y, ref) < 2e-5
+    for splits in (2, 5):
+        part = torch.full((splits, N, M), float("nan"), device=dev)
+        nat.gemm_split(a, False, b, False, M, N, K, part, M, True, splits, N * M)
+        out = torch.empty(N, M, device=dev)
+        nat.splitk_reduce(part, min(splits, (K + 31) // 32), N * M, N, M, M, bias, True, out)
+        assert _rel(out, torch.relu(ref + bias.double())) < 2e-5
+    # error relative to what torch's own paths make of the same product
+    tf32 = torch.backends.cuda.matmul.allow_tf32
+    try:
+        torch.backends.cuda.matmul.allow_tf32 = True
+        e_tf32 = _rel(x @ w.t(), ref)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+    assert _rel(y, ref) < e_tf32 / 8
+
+
+@pytest.mark.parametrize("O,B,K", [(750, 100, 1000), (10, 37, 750), (750, 256, 2048)])
+def test_gemm_backward_majors_against_fp64(nat, O, B, K):
+    """Data gradient (A MN-major, B K-major, transposed store) and weight gradient (both MN-major)."""
+    dev = "cuda"
+    torch.manual_seed(2)
+    w = torch.randn(O, K, device=dev)
+    x = torch.randn(B, K, device=dev)
+    dy = torch.randn(B, O, device=dev)
+    pw = nat.PackedMatrix(O, K, dev).pack(w)
+    px = nat.PackedMatrix(B, K, dev).pack(x)
+    pdy = nat.PackedMatrix(B, O, dev).pack(dy)
+    dx = torch.full((B, K), float("nan"), device=dev)
+    nat.gemm_split(pw, True, pdy, False, K, B, O, dx, K, True)
+    assert _rel(dx, dy.double() @ w.double()) < 2e-5
+    dw = torch.full((O, K), float("nan"), device=dev)
+    nat.gemm_split(pdy, True, px, True, O, K, B, dw, K, False)
+    assert _rel(dw, dy.double().t() @ x.double()) < 2e-5
+    # split-K over the batch rows, summed in fixed order
+    part = torch.full((3, O, K), float("nan"), device=dev)
+    nat.gemm_split(pdy, True, px, True, O, K, B, part, K, False, 3, O * K)
+    out = torch.empty(O, K, device=dev)
+    nat.splitk_reduce(part, min(3, (B + 31) // 32), O * K, O, K, K, None, False, out)
+    assert _rel(out, dy.double().t() @ x.double()) < 2e-5
+    db = torch.empty(O, device=dev)
+    nat.colsum(dy, None, db)
+    assert _rel(db, dy.double().sum(0)) < 1e-6
+
+
+def test_gemm_rejects_bad_arguments(nat):
+    dev = "cuda"
+    a = nat.PackedMatrix(16, 64, dev).pack(torch.randn(16, 64, device=dev))
+    out = torch.empty(16, 16, device=dev)
+    with pytest.raises(nat.NativeError):
+        nat.gemm_split(a, False, a, False, 32, 16, 64, out, 16, False)   # M beyond the packed rows
+    with pytest.raises(nat.NativeError):
+        nat.gemm_split(a, False, a, True, 16, 16, 64, out, 16, False)    # unsupported major pair
+
+
+def test_relu_maxpool_matches_torch(nat):
+    dev = "cuda"
+    torch.manual_seed(3)
+    x = torch.randn(5, 7, 32, 32, device=dev, requires_grad=True)
+    from ddp_b200.models.linear import ReLUMaxPool2dB200
+    y = ReLUMaxPool2dB200(native=True)(x)
+    ref = F.max_pool2d(F.relu(x), 2)
+    assert torch.equal(y, ref)
+    g = torch.randn_like(y)
+    (dx,) = torch.autograd.grad(y, x, g)
+    (dref,) = torch.autograd.grad(ref, x, g)
+    assert torch.equal(dx, dref)
+    # with a bias: relu(max(x) + b)
+    bias = torch.randn(7, device=dev)
+    out = torch.empty(5, 7, 16, 16, device=dev)
+    code = torch.empty(5, 7, 16, 16, dtype=torch.uint8, device=dev)
+    nat.relu_maxpool2_fwd(x.detach(), bias, out, code)
+    assert torch.allclose(out, F.max_pool2d(F.relu(x.detach() + bias.view(1, 7, 1, 1)), 2), atol=1e-6)
+
+
+@pytest.mark.parametrize("batch,in_f,out_f,relu", [(37, 750, 10, False), (256, 4096, 750, True), (64, 1000, 333, True)])
+def test_linear_b200_against_fp64_and_torch(nat, batch, in_f, out_f, relu):
+    from ddp_b200.models.linear import LinearB200
+    dev = "cuda"
+    torch.manual_seed(4)
+    lin = LinearB200(in_f, out_f, fused_relu=relu, native=True).to(dev)
+    ref = nn.Linear(in_f, out_f).to(dev).double()
+    ref.load_state_dict({k: v.double() for k, v in lin.state_dict().items()})
+    tl = nn.Linear(in_f, out_f).to(dev)
+    tl.load_state_dict(lin.state_dict())
+    act = torch.relu if relu else (lambda t: t)
+    for b in (batch, max(1, batch // 3)):       # a smaller batch afterwards reuses the packed buffers
+        x = torch.randn(b, in_f, device=dev, requires_grad=True)
+        g = torch.randn(b, out_f, device=dev)
+        y = lin(x)
+        dx, dw, db = torch.autograd.grad(y, (x, lin.weight, lin.bias), g)
+        xr = x.detach().double().requires_grad_(True)
+        yr = act(ref(xr))
+        dxr, dwr, dbr = torch.autograd.grad(yr, (xr, ref.weight, ref.bias), g.double())
+        xt = x.detach().clone().requires_grad_(True)
+        yt = act(tl(xt))
+        dxt, dwt, dbt = torch.autograd.grad(yt, (xt, tl.weight, tl.bias), g)
+        for name, ours, oracle, theirs in (("y", y, yr, yt), ("dx", dx, dxr, dxt), ("dw", dw, dwr, dwt),
+                                           ("db", db, dbr, dbt)):
+            e_ours, e_torch = _rel(ours, oracle), _rel(theirs, oracle)
+            assert e_ours < 2e-5, (name, b, e_ours, e_torch)
+
+
+def test_linear_b200_weight_grad_sink_and_module_protocol(nat):
+    """``weight_grad_out``: the backward writes the weight gradient into a caller's buffer and autograd
+    adopts it; a second forward before backward is refused; optimizers work on the parameters."""
+    from ddp_b200.models.linear import LinearB200
+    dev = "cuda"
+    torch.manual_seed(5)
+    lin = LinearB200(512, 300, native=True).to(dev)
+    sink = torch.full((300, 512), float("nan"), device=dev)
+    lin.weight_grad_out = sink
+    x = torch.randn(48, 512, device=dev)
+    lin(x).square().sum().backward()
+    ref = torch.autograd.grad(F.linear(x, lin.weight, lin.bias).square().sum(), lin.weight)[0]
+    assert torch.allclose(sink, ref, rtol=1e-4, atol=1e-3)
+    assert torch.equal(lin.weight.grad, sink)
+    import os
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/grad_sink.txt", "w") as f:   # informative: did autograd adopt the buffer (no copy)?
+        f.write(f"adopted={lin.weight.grad.data_ptr() == sink.data_ptr()}\n")
+    y1 = lin(x)
+    lin(x)
+    with pytest.raises(RuntimeError, match="most recent forward"):
+        y1.sum().backward()
+    opt = torch.optim.SGD(lin.parameters(), lr=0.1)
+    w0 = lin.weight.detach().clone()
+    opt.zero_grad()
+    lin(x).sum().backward()
+    opt.step()
+    assert not torch.equal(w0, lin.weight)
+
+
+def test_wide_cnn_b200_gradients_match_the_torch_model(nat):
+    from ddp_b200.models.wide_cnn import WideCNN, WideCNNB200
+    dev = "cuda"
+    torch.manual_seed(6)
+    a = WideCNNB200(native=True).to(dev)
+    b = WideCNN().to(dev)
+    b.load_state_dict(a.state_dict())
+    x = torch.rand(32, 3, 32, 32, device=dev)
+    y = torch.randint(0, 10, (32,), device=dev)
+    la = F.cross_entropy(a(x), y)
+    la.backward()
+    lb = F.cross_entropy(b(x), y)
+    lb.backward()
+    assert abs(float(la) - float(lb)) < 1e-4
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        scale = float(q.grad.abs().max())
+        assert float((p.grad - q.grad).abs().max()) < 2e-3 * scale + 1e-7, n

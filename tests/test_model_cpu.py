@@ -158,3 +158,26 @@ def test_every_kernel_launched_as_programmatic_dependent_waits_for_its_predecess
         if "pdl_sync()" not in body and "pdl_wait()" not in body:
             missing.append(name)
     assert not missing, f"launched through launch_k without griddepcontrol.wait: {missing}"
+
+
+def test_linear_b200_and_wide_cnn_b200_fall_back_to_torch_ops_on_cpu():
+    """models/linear.py on CPU tensors: same parameters, keys and results as nn.Linear / WideCNN."""
+    import torch.nn as nn
+    from ddp_b200.models.linear import LinearB200, ReLUMaxPool2dB200
+    from ddp_b200.models.wide_cnn import WideCNN, WideCNNB200
+    torch.manual_seed(0)
+    a = LinearB200(20, 7, fused_relu=True)
+    torch.manual_seed(0)
+    b = nn.Linear(20, 7)
+    assert list(a.state_dict()) == list(b.state_dict())
+    x = torch.randn(5, 20)
+    assert torch.equal(a(x), torch.relu(b(x)))
+    p = torch.randn(2, 3, 8, 8)
+    assert torch.equal(ReLUMaxPool2dB200()(p), nn.functional.max_pool2d(torch.relu(p), 2))
+    torch.manual_seed(1)
+    wa = WideCNNB200(hidden=16)
+    torch.manual_seed(1)
+    wb = WideCNN(hidden=16)
+    assert list(wa.state_dict()) == list(wb.state_dict())
+    xi = torch.rand(2, 3, 32, 32)
+    assert torch.equal(wa(xi), wb(xi))

@@ -1,7 +1,10 @@
 """BASELINE.json config 4: widened CNN (~25 M params, 3x32x32 synthetic), DP on N GPUs.
-ours  = BucketedDataParallel (fused all-reduce+SGD per bucket on a side stream, our communicator)
-torch = DistributedDataParallel + NCCL + torch.optim.SGD on the same module and inputs.
-Both arms run the model's forward/backward through torch ops; only the data-parallel layer differs.
+native = WideCNNB200 (fully connected layers on the tcgen05 GEMM of csrc/gemm_tc.cu, fused ReLU+max-pool;
+         convolutions through cuDNN) under BucketedDataParallel, fc1's weight gradient written straight
+         into the gradient arena
+ours   = the torch module under BucketedDataParallel (fused all-reduce+SGD per bucket on side streams,
+         our communicator): isolates the data-parallel layer
+torch  = DistributedDataParallel + NCCL + torch.optim.SGD on the torch module and the same inputs.
 
     python -m torch.distributed.run --nproc-per-node 8 tools/bench_wide.py [--batch 256] [--steps 30]
 """
@@ -15,7 +18,7 @@ import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 
-from ddp_b200.models.wide_cnn import WideCNN, param_count
+from ddp_b200.models.wide_cnn import WideCNN, WideCNNB200, param_count
 
 
 def timed_steps(step, xs, ys, steps, warmup, world, dev):
@@ -58,6 +61,15 @@ def main():
 
     from ddp_b200.parallel.bucketed import BucketedDataParallel
     torch.manual_seed(0)
+    mn = WideCNNB200(native=True).to(dev)
+    eng = BucketedDataParallel(mn, rank, world, lr=0.01, bucket_mb=a.bucket_mb)
+    ms, loss = timed_steps(lambda x, y: eng.step(x, y, F.cross_entropy), xs, ys, a.steps, a.warmup, world, dev)
+    out["native_ms_per_step"], out["native_img_s"], out["native_loss"] = ms, world * a.batch / ms * 1e3, loss
+    eng.close()
+    del eng, mn
+    torch.cuda.empty_cache()
+
+    torch.manual_seed(0)
     m = WideCNN().to(dev)
     out["params"] = param_count(m)
     eng = BucketedDataParallel(m, rank, world, lr=0.01, bucket_mb=a.bucket_mb)
@@ -65,6 +77,8 @@ def main():
     ms, loss = timed_steps(lambda x, y: eng.step(x, y, F.cross_entropy), xs, ys, a.steps, a.warmup, world, dev)
     out["ours_ms_per_step"], out["ours_img_s"], out["ours_loss"] = ms, world * a.batch / ms * 1e3, loss
     eng.close()
+    del eng, m
+    torch.cuda.empty_cache()
 
     from torch.nn.parallel import DistributedDataParallel as DDP
     torch.manual_seed(0)
@@ -81,6 +95,7 @@ def main():
 
     ms, loss = timed_steps(torch_step, xs, ys, a.steps, a.warmup, world, dev)
     out["torch_ddp_ms_per_step"], out["torch_ddp_img_s"], out["torch_loss"] = ms, world * a.batch / ms * 1e3, loss
+    out["native_speedup_vs_torch_ddp"] = out["torch_ddp_ms_per_step"] / out["native_ms_per_step"]
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
