@@ -21,11 +21,20 @@
 // train_ddp.py:199) for layer shapes beyond the 10-class head the step engine hard-codes (simt_ops.cu):
 // BASELINE.json config 4's fc 32768 -> 750 -> 10.
 //
-// Warp roles (192 threads, one output tile (x one K split) per CTA):
-//   warp 0    bulk-copy producer (all 32 lanes issue copies)
+// Operand tiles arrive by TMA tensor copies (cp.async.bulk.tensor, one instruction per operand and
+// stage: a 4-D box [set][plane][row block][32 rows x 16 B] lands exactly in the no-swizzle canonical
+// layout, whichever major it is read in).  Measured on B200: the first version issued the same bytes as
+// 16..96 one-dimensional bulk copies per stage and was bound by ~50 ns per copy per SM (weight gradient
+// of fc 32768->750 at batch 256: 195 us); DDPB_GEMM_TMA=0 selects that path for comparison.
+//
+// Warp roles (192 threads, one output tile (x one K split) per CTA, two CTAs per SM so that one's
+// epilogue overlaps the other's main loop):
+//   warp 0    TMA producer (one lane; the 1-D fallback path issues from all 32 lanes)
 //   warp 1    TMEM allocator + MMA issuer (one elected lane issues tcgen05.mma)
 //   warps 2-5 epilogue: tcgen05.ld the accumulator, store fp32 (row-major or transposed)
+#include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "ptx.cuh"
 #include "api_internal.cuh"
@@ -83,9 +92,19 @@ struct OperandTile {
   }
 };
 
-template <bool A_MN, bool B_MN, int BN, int STAGES>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_split_tc_kernel(GemmArgs g) {
+// 4-D tensor copy global -> shared (SASS: UTMALDG), completion reported to an mbarrier as tx bytes.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], "
+      "[%2];" ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+// TM: operand tiles by tensor-map TMA (ma / mb), else by 1-D bulk copies from g.a / g.b.
+template <bool A_MN, bool B_MN, int BN, int STAGES, bool TM>
+__global__ void __launch_bounds__(kGemmThreads, 2)
+gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const __grid_constant__ CUtensorMap mb) {
   using S = GemmSmem<BN, STAGES>;
   using TA = OperandTile<A_MN, kGemmBM>;
   using TB = OperandTile<B_MN, BN>;
@@ -125,7 +144,28 @@ gemm_split_tc_kernel(GemmArgs g) {
   const uint32_t tmem_base = *s_tmem;
   pdl_sync();
 
-  if (warp == 0) {
+  if (warp == 0 && TM) {
+    // packed tensor as a 4-D array [set][plane][rows/32][32 rows x 8 elements]; the box of one operand
+    // tile: K-major {256, T/32, KS/8, 2} at {0, tile*T/32, k0/8, 0}; MN-major {256, 1, T/8, 2} at
+    // {0, k0/32, tile*T/8, 0} (ddpb_gemm_split encodes the maps with these boxes)
+    if (lane == 0) {
+      for (int it = 0; it < nst; ++it) {
+        const int stage = it % STAGES;
+        const uint32_t phase = (it / STAGES) & 1;
+        const uint32_t full = bar_full + stage * 8;
+        mbar_wait(bar_empty + stage * 8, phase ^ 1);
+        mbar_arrive_expect_tx(full, S::stage_bytes);
+        const int k0 = (st0 + it) * kGemmKS;
+        const uint32_t sa = s_base + stage * S::stage_bytes;
+        const uint32_t sb = sa + 2 * S::a_set;
+        if (A_MN) tma_load_4d(sa, &ma, full, 0, k0 / 32, m_tile * (kGemmBM / 8), 0);
+        else tma_load_4d(sa, &ma, full, 0, m_tile * (kGemmBM / 32), k0 / 8, 0);
+        if (B_MN) tma_load_4d(sb, &mb, full, 0, k0 / 32, n_tile * (BN / 8), 0);
+        else tma_load_4d(sb, &mb, full, 0, n_tile * (BN / 32), k0 / 8, 0);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 0) {
     constexpr int nA = 2 * TA::copies, nB = 2 * TB::copies;
     for (int it = 0; it < nst; ++it) {
       const int stage = it % STAGES;
@@ -230,24 +270,29 @@ gemm_split_tc_kernel(GemmArgs g) {
 
 // fp32 row-major src[R][K] (leading dimension ld) -> split row planes.  Optional `mask` (same shape and
 // ld as src): elements whose mask value is <= 0 are packed as zero (ReLU backward fused into the pack).
-// Thread = one 8-wide K chunk of two consecutive rows; only the real region is written (the padding
-// of a plane tensor is zero from its allocation and stays zero).
+// Block = 256 rows x 8 chunks (64 K elements); lane = row, so a warp's stores to one plane are 512
+// contiguous bytes, and a thread walks 256 contiguous source bytes (its later loads hit the lines the
+// first ones brought into L1).  Only the real region is written — the padding of a plane tensor is zero
+// from its allocation and stays zero — plus zeros for the rows [R, next multiple of 32): a reduction
+// over rows (MN-major use) runs in stages of 32 rows, and the buffer may hold a larger, earlier batch
+// beyond R.
+constexpr int kPackChunks = 8;
 __global__ void __launch_bounds__(256)
 pack_rows_split_kernel(const float* __restrict__ src, const float* __restrict__ mask, long long ld, int R, int K,
                        uint4* __restrict__ dst, long long rows_pad, long long set_stride, int vec) {
   pdl_sync();
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int r0 = (blockIdx.y * 8 + (threadIdx.x >> 5)) * 2;
-  // rows [R, next multiple of 32) are written as zeros: a reduction over rows (MN-major use) runs in
-  // stages of 32 rows, and the buffer may hold a larger, earlier batch beyond R
+  const int r = blockIdx.y * 256 + threadIdx.x;
   const int Rz = (R + kGemmKS - 1) / kGemmKS * kGemmKS;
-  if (c * 8 >= K || r0 >= Rz) return;
-#pragma unroll
-  for (int rr = 0; rr < 2; ++rr) {
-    const int r = r0 + rr;
+  if (r >= Rz) return;
+  const int c_begin = blockIdx.x * kPackChunks;
+#pragma unroll 4
+  for (int cc = 0; cc < kPackChunks; ++cc) {
+    const int c = c_begin + cc;
+    if (c * 8 >= K) break;
+    const long long o = (long long)c * rows_pad + r;
     if (r >= R) {
-      dst[(long long)c * rows_pad + r] = make_uint4(0u, 0u, 0u, 0u);
-      dst[set_stride + (long long)c * rows_pad + r] = make_uint4(0u, 0u, 0u, 0u);
+      dst[o] = make_uint4(0u, 0u, 0u, 0u);
+      dst[set_stride + o] = make_uint4(0u, 0u, 0u, 0u);
       continue;
     }
     float x[8];
@@ -273,7 +318,6 @@ pack_rows_split_kernel(const float* __restrict__ src, const float* __restrict__ 
     float hi[8], lo[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) split_bf16(x[e], hi[e], lo[e]);
-    const long long o = (long long)c * rows_pad + r;
     dst[o] = make_uint4(pack_bf16x2(hi[0], hi[1]), pack_bf16x2(hi[2], hi[3]), pack_bf16x2(hi[4], hi[5]),
                         pack_bf16x2(hi[6], hi[7]));
     dst[set_stride + o] = make_uint4(pack_bf16x2(lo[0], lo[1]), pack_bf16x2(lo[2], lo[3]),
@@ -383,13 +427,63 @@ relu_maxpool2_bwd_kernel(const float* __restrict__ dout, const uint8_t* __restri
   *reinterpret_cast<float4*>(p + W) = r1;
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime (no link dependency on libcuda); NULL when unavailable or
+// switched off with DDPB_GEMM_TMA=0.
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    const char* e = getenv("DDPB_GEMM_TMA");
+    if (!(e && e[0] == '0')) {
+      void* p = nullptr;
+      cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+      if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+          q == cudaDriverEntryPointSuccess)
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+      else
+        cudaGetLastError();
+    }
+  }
+  return fn;
+}
+
+// Tensor map over a packed tensor for tiles of T elements along M/N read in the given major.
+static int encode_operand_map(EncodeTiledFn enc, CUtensorMap* m, const GemmOperand& op, bool mn, int T) {
+  const cuuint64_t planes = (cuuint64_t)(op.set_stride / op.rows);
+  cuuint64_t dims[4] = {256, (cuuint64_t)op.rows / 32, planes, 2};
+  cuuint64_t strides[3] = {512, (cuuint64_t)op.rows * 16, (cuuint64_t)op.set_stride * 16};
+  cuuint32_t box[4] = {256, mn ? 1u : (cuuint32_t)T / 32, mn ? (cuuint32_t)T / 8 : (cuuint32_t)kGemmKS / 8, 2};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<uint4*>(op.base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : DDPB_ERR_UNSUPPORTED;
+}
+
 template <bool A_MN, bool B_MN, int BN>
 static int launch_gemm(const GemmArgs& g, dim3 grid, cudaStream_t st) {
-  constexpr int STAGES = BN == 256 ? 4 : BN == 128 ? 6 : 8;
+  constexpr int STAGES = BN == 256 ? 2 : BN == 128 ? 3 : 4;  // ~96 KB: two CTAs per SM
   using S = GemmSmem<BN, STAGES>;
-  auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES>;
-  DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
-  DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g));
+  alignas(64) CUtensorMap ma, mb;
+  memset(&ma, 0, sizeof(ma));
+  memset(&mb, 0, sizeof(mb));
+  EncodeTiledFn enc = encode_tiled();
+  if (enc && (encode_operand_map(enc, &ma, g.a, A_MN, kGemmBM) || encode_operand_map(enc, &mb, g.b, B_MN, BN)))
+    enc = nullptr;  // fall back to the 1-D copies
+  if (enc) {
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true>;
+    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
+    DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
+  } else {
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, false>;
+    DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
+    DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
+  }
   return 0;
 }
 
@@ -426,7 +520,7 @@ int ddpb_pack_rows_split(const float* src, const float* mask, long long ld, int 
   const int nchunks = (k + 7) / 8;
   const int vec = (ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
                   (!mask || (reinterpret_cast<uintptr_t>(mask) & 15) == 0);
-  dim3 grid((nchunks + 31) / 32, ((rows + kGemmKS - 1) / kGemmKS * kGemmKS + 15) / 16);
+  dim3 grid((nchunks + kPackChunks - 1) / kPackChunks, ((rows + kGemmKS - 1) / kGemmKS * kGemmKS + 255) / 256);
   DDPB_CUDA_OK(launch_k(pack_rows_split_kernel, grid, dim3(256), 0, (cudaStream_t)stream, src, mask, ld, rows, k,
                         reinterpret_cast<uint4*>(packed), rp, rp * (kp / 8), vec));
   return 0;
