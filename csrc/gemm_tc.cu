@@ -276,17 +276,17 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
 // from its allocation and stays zero — plus zeros for the rows [R, next multiple of 32): a reduction
 // over rows (MN-major use) runs in stages of 32 rows, and the buffer may hold a larger, earlier batch
 // beyond R.
-constexpr int kPackChunks = 8;
+constexpr int kPackChunks = 8;  // chunks per block for large matrices; small ones use 1 (more blocks)
 __global__ void __launch_bounds__(256)
 pack_rows_split_kernel(const float* __restrict__ src, const float* __restrict__ mask, long long ld, int R, int K,
-                       uint4* __restrict__ dst, long long rows_pad, long long set_stride, int vec) {
+                       uint4* __restrict__ dst, long long rows_pad, long long set_stride, int vec, int cpb) {
   pdl_sync();
   const int r = blockIdx.y * 256 + threadIdx.x;
   const int Rz = (R + kGemmKS - 1) / kGemmKS * kGemmKS;
   if (r >= Rz) return;
-  const int c_begin = blockIdx.x * kPackChunks;
+  const int c_begin = blockIdx.x * cpb;
 #pragma unroll 4
-  for (int cc = 0; cc < kPackChunks; ++cc) {
+  for (int cc = 0; cc < cpb; ++cc) {
     const int c = c_begin + cc;
     if (c * 8 >= K) break;
     const long long o = (long long)c * rows_pad + r;
@@ -344,19 +344,40 @@ splitk_reduce_kernel(const float* __restrict__ partial, int nsplit, long long sp
 
 // out[c] = sum_r src[r][c] (mask: only where mask[r][c] > 0) — a linear layer's bias gradient.
 __global__ void __launch_bounds__(256)
-colsum_kernel(const float* __restrict__ src, const float* __restrict__ mask, int R, int C, long long ld,
-              float* __restrict__ out) {
-  // block = 32 columns x 8 row groups; fixed order: each group sums its rows r = g, g+8, ..., then groups 0..7
+colsum_kernel(const float* __restrict__ src, const float* __restrict__ mask, int R_all, int C, long long ld,
+              float* __restrict__ out, int rows_per_split) {
+  // block = 32 columns x 8 row groups over the rows of split blockIdx.y; fixed order: each group sums its
+  // rows r = g, g+8, ..., then groups 0..7.  Split y writes out[y*C + c].
   __shared__ float sm[8][33];
   pdl_sync();
   const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
+  const long long row0 = (long long)blockIdx.y * rows_per_split;
+  const int R = (int)min((long long)rows_per_split, (long long)R_all - row0);
+  src += row0 * ld;
+  if (mask) mask += row0 * ld;
+  out += (long long)blockIdx.y * C;
   float s = 0.f;
-  if (c < C)
-    for (int r = grp; r < R; r += 8) {
-      const float v = src[(long long)r * ld + c];
-      s += (!mask || mask[(long long)r * ld + c] > 0.f) ? v : 0.f;
+  if (c < C) {
+    // four independent chains keep the loads in flight; the order of the additions is fixed
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    int r = grp;
+    for (; r + 24 < R; r += 32) {
+      float v[4], m[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = src[(long long)(r + 8 * u) * ld + c];
+        m[u] = mask ? mask[(long long)(r + 8 * u) * ld + c] : 1.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) a[u] += m[u] > 0.f ? v[u] : 0.f;
     }
+    for (; r < R; r += 8) {
+      const float v = src[(long long)r * ld + c];
+      a[0] += (!mask || mask[(long long)r * ld + c] > 0.f) ? v : 0.f;
+    }
+    s = (a[0] + a[1]) + (a[2] + a[3]);
+  }
   sm[grp][lane] = s;
   __syncthreads();
   if (grp == 0 && c < C) {
@@ -520,9 +541,12 @@ int ddpb_pack_rows_split(const float* src, const float* mask, long long ld, int 
   const int nchunks = (k + 7) / 8;
   const int vec = (ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
                   (!mask || (reinterpret_cast<uintptr_t>(mask) & 15) == 0);
-  dim3 grid((nchunks + kPackChunks - 1) / kPackChunks, ((rows + kGemmKS - 1) / kGemmKS * kGemmKS + 255) / 256);
+  const int row_blocks = ((rows + kGemmKS - 1) / kGemmKS * kGemmKS + 255) / 256;
+  const int cpb = (long long)((nchunks + kPackChunks - 1) / kPackChunks) * row_blocks >= 2 * ddpb_num_sms()
+                      ? kPackChunks : 1;
+  dim3 grid((nchunks + cpb - 1) / cpb, row_blocks);
   DDPB_CUDA_OK(launch_k(pack_rows_split_kernel, grid, dim3(256), 0, (cudaStream_t)stream, src, mask, ld, rows, k,
-                        reinterpret_cast<uint4*>(packed), rp, rp * (kp / 8), vec));
+                        reinterpret_cast<uint4*>(packed), rp, rp * (kp / 8), vec, cpb));
   return 0;
 }
 
@@ -587,10 +611,15 @@ int ddpb_splitk_reduce(const float* partial, int nsplit, long long split_stride,
   return 0;
 }
 
-int ddpb_colsum(const float* src, const float* mask, int rows, int cols, long long ld, float* out, void* stream) {
-  if (rows <= 0 || cols <= 0) return DDPB_ERR_SHAPE;
-  DDPB_CUDA_OK(launch_k(colsum_kernel, dim3((cols + 31) / 32), dim3(256), 0, (cudaStream_t)stream, src, mask, rows,
-                        cols, ld, out));
+// row_splits > 1: out receives row_splits partial sums [row_splits][cols] over consecutive row ranges of
+// ceil(rows / row_splits) rows (sum them with a second call) — for tall matrices.
+int ddpb_colsum(const float* src, const float* mask, int rows, int cols, long long ld, float* out, int row_splits,
+                void* stream) {
+  if (rows <= 0 || cols <= 0 || row_splits < 1 || row_splits > 65535) return DDPB_ERR_SHAPE;
+  const int rps = (rows + row_splits - 1) / row_splits;
+  if ((long long)rps * (row_splits - 1) >= rows) return DDPB_ERR_SHAPE;  // every split must own a row
+  DDPB_CUDA_OK(launch_k(colsum_kernel, dim3((cols + 31) / 32, row_splits), dim3(256), 0, (cudaStream_t)stream, src,
+                        mask, rows, cols, ld, out, rps));
   return 0;
 }
 

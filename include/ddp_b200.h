@@ -317,7 +317,8 @@ int ddpb_broadcast(void* comm, size_t off, long long nbytes, int root, int slot,
  *     b_rows/b_k are the shapes the operands were packed from, a_mn/b_mn = 1 reads an operand
  *     MN-major.  Supported majors: (0,0), (1,0), (1,1).  k_splits > 1 writes that many partial images
  *     split_stride floats apart (sum them, add a bias, apply ReLU with ddpb_splitk_reduce).
- *   colsum: out[c] = sum_r src[r][c] (masked like the pack): the bias gradient. */
+ *   colsum: out[c] = sum_r src[r][c] (masked like the pack): the bias gradient.  row_splits > 1 writes
+ *     that many partial sums [row_splits][cols] over consecutive row ranges (sum them with a second call). */
 int ddpb_gemm_pad(void);
 size_t ddpb_pack_rows_split_bytes(int rows, int k);
 int ddpb_pack_rows_split(const float* src, const float* mask, long long ld, int rows, int k, void* packed,
@@ -328,7 +329,8 @@ int ddpb_gemm_split(const void* a, int a_rows, int a_k, int a_mn, const void* b,
 int ddpb_gemm_split_suggest_splits(int M, int N, int K);
 int ddpb_splitk_reduce(const float* partial, int nsplit, long long split_stride, int rows, int cols, long long ld,
                        const float* bias, int relu, float* out, long long ld_out, void* stream);
-int ddpb_colsum(const float* src, const float* mask, int rows, int cols, long long ld, float* out, void* stream);
+int ddpb_colsum(const float* src, const float* mask, int rows, int cols, long long ld, float* out, int row_splits,
+                void* stream);
 /* ---- fused (bias +) ReLU + 2x2 max pool over NCHW fp32 (what nn.ReLU -> nn.MaxPool2d(2) compute,
  * one pass); `code` [batch][C][H/2][W/2] bytes: index of the winning input (first maximum, row-major)
  * or 4 where the pooled value is <= 0.  H even, W a multiple of 4.  No reference counterpart (its
@@ -337,6 +339,23 @@ int ddpb_relu_maxpool2_fwd(const float* in, const float* bias, float* out, unsig
                            int H, int W, void* stream);
 int ddpb_relu_maxpool2_bwd(const float* dout, const unsigned char* code, float* din, int batch, int C, int H, int W,
                            void* stream);
+
+/* ---- channels-last (NHWC) fp32 CUDA-core kernels for the widened CNN's first convolution and pooling
+ * (csrc/wide_ops.cu).  No reference counterpart (model.py:8-16 has neither a 3-channel input nor a pool).
+ *   small_cin_fwd:   out NHWC = relu(conv3x3_pad1(x NCHW, w[cout][cin][3][3]) + bias); cin 3, cout 64, W 32.
+ *   small_cin_wgrad: dw_db[cout][28] (27 taps in [ci][dy][dx] order, then the bias gradient) from dact /
+ *                    act (NHWC; act = forward output used as ReLU mask, may be NULL) and x; `partial` =
+ *                    scratch of ddpb_conv3x3_small_cin_wgrad_parts() * cout * 28 floats.
+ *   relu_maxpool2_nhwc_*: as ddpb_relu_maxpool2_* on NHWC tensors (C a multiple of 4). */
+int ddpb_conv3x3_small_cin_fwd(const float* x, const float* w, const float* bias, float* out, int cin, int cout,
+                               int batch, int H, int W, void* stream);
+int ddpb_conv3x3_small_cin_wgrad_parts(int batch, int H);
+int ddpb_conv3x3_small_cin_wgrad(const float* dact, const float* act, const float* x, float* partial,
+                                 float* dw_db, int cin, int cout, int batch, int H, int W, void* stream);
+int ddpb_relu_maxpool2_nhwc_fwd(const float* in, const float* bias, float* out, unsigned char* code, int batch,
+                                int C, int H, int W, void* stream);
+int ddpb_relu_maxpool2_nhwc_bwd(const float* dout, const unsigned char* code, float* din, int batch, int C, int H,
+                                int W, void* stream);
 
 /* ---- p -= lr*g with lr read from device memory (single-GPU path; multi-GPU runs fuse the
  * update into the all-reduce).  reference train_ddp.py:41,200. */

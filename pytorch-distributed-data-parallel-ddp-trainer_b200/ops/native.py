@@ -91,9 +91,15 @@ _SIGNATURES = {
     "ddpb_gemm_split": (I, [P, I, I, I, P, I, I, I, I, I, I, P, LL, I, I, LL, P]),
     "ddpb_gemm_split_suggest_splits": (I, [I, I, I]),
     "ddpb_splitk_reduce": (I, [P, I, LL, I, I, LL, P, I, P, LL, P]),
-    "ddpb_colsum": (I, [P, P, I, I, LL, P, P]),
+    "ddpb_colsum": (I, [P, P, I, I, LL, P, I, P]),
     "ddpb_relu_maxpool2_fwd": (I, [P, P, P, P, I, I, I, I, P]),
     "ddpb_relu_maxpool2_bwd": (I, [P, P, P, I, I, I, I, P]),
+    # channels-last kernels of the widened CNN (csrc/wide_ops.cu)
+    "ddpb_conv3x3_small_cin_fwd": (I, [P, P, P, P, I, I, I, I, I, P]),
+    "ddpb_conv3x3_small_cin_wgrad_parts": (I, [I, I]),
+    "ddpb_conv3x3_small_cin_wgrad": (I, [P, P, P, P, P, I, I, I, I, I, P]),
+    "ddpb_relu_maxpool2_nhwc_fwd": (I, [P, P, P, P, I, I, I, I, P]),
+    "ddpb_relu_maxpool2_nhwc_bwd": (I, [P, P, P, I, I, I, I, P]),
 }
 
 #: execution precisions of the step (models/simple_cnn.py): "bf16x3" = the reference's numerics
@@ -539,8 +545,19 @@ def splitk_reduce(partial, nsplit, split_stride, rows, cols, ld, bias, relu, out
 
 
 def colsum(src, mask, out, stream=None):
+    """out[c] = sum_r src[r][c] where mask[r][c] > 0 (mask optional); tall matrices in two fixed-order passes."""
     rows, cols = src.shape
-    check(lib().ddpb_colsum(ptr(src), ptr(mask), rows, cols, src.stride(0), ptr(out), stream_ptr(stream)), "colsum")
+    splits = 1 if rows <= 1024 else min(512, (rows + 255) // 256)
+    if splits == 1:
+        check(lib().ddpb_colsum(ptr(src), ptr(mask), rows, cols, src.stride(0), ptr(out), 1, stream_ptr(stream)),
+              "colsum")
+        return
+    rps = (rows + splits - 1) // splits
+    splits = (rows + rps - 1) // rps
+    part = torch.empty(splits, cols, dtype=torch.float32, device=src.device)
+    check(lib().ddpb_colsum(ptr(src), ptr(mask), rows, cols, src.stride(0), ptr(part), splits, stream_ptr(stream)),
+          "colsum")
+    check(lib().ddpb_colsum(ptr(part), None, splits, cols, cols, ptr(out), 1, stream_ptr(stream)), "colsum")
 
 
 def relu_maxpool2_fwd(x, bias, out, code, stream=None):
@@ -553,3 +570,36 @@ def relu_maxpool2_bwd(dout, code, din, stream=None):
     b, c, h, w = din.shape
     check(lib().ddpb_relu_maxpool2_bwd(ptr(dout), ptr(code), ptr(din), b, c, h, w, stream_ptr(stream)),
           "relu_maxpool2_bwd")
+
+
+# ----------------------------------------------------------------------------- channels-last kernels (widened CNN)
+def conv3x3_small_cin_fwd(x, w, bias, out_nhwc, stream=None):
+    """out_nhwc [b, H, W, cout] = relu(conv3x3(x [b, cin, H, W], w) + bias), fp32 FMA."""
+    b, cin, H, W = x.shape
+    check(lib().ddpb_conv3x3_small_cin_fwd(ptr(x), ptr(w), ptr(bias), ptr(out_nhwc), cin, w.shape[0], b, H, W,
+                                           stream_ptr(stream)), "conv3x3_small_cin_fwd")
+
+
+def conv3x3_small_cin_wgrad(dact_nhwc, act_nhwc, x, cout, stream=None):
+    """(dw [cout, cin, 3, 3], db [cout]) of the convolution above; ReLU' from ``act_nhwc`` (or None)."""
+    b, cin, H, W = x.shape
+    parts = int(lib().ddpb_conv3x3_small_cin_wgrad_parts(b, H))
+    n = cout * 28
+    partial = torch.empty(parts * n, dtype=torch.float32, device=x.device)
+    out = torch.empty(n, dtype=torch.float32, device=x.device)
+    check(lib().ddpb_conv3x3_small_cin_wgrad(ptr(dact_nhwc), ptr(act_nhwc), ptr(x), ptr(partial), ptr(out), cin,
+                                             cout, b, H, W, stream_ptr(stream)), "conv3x3_small_cin_wgrad")
+    out = out.view(cout, 28)
+    return out[:, :27].reshape(cout, cin, 3, 3), out[:, 27].contiguous()
+
+
+def relu_maxpool2_nhwc_fwd(x_nhwc, bias, out, code, stream=None):
+    b, h, w, c = x_nhwc.shape
+    check(lib().ddpb_relu_maxpool2_nhwc_fwd(ptr(x_nhwc), ptr(bias), ptr(out), ptr(code), b, c, h, w,
+                                            stream_ptr(stream)), "relu_maxpool2_nhwc_fwd")
+
+
+def relu_maxpool2_nhwc_bwd(dout, code, din_nhwc, stream=None):
+    b, h, w, c = din_nhwc.shape
+    check(lib().ddpb_relu_maxpool2_nhwc_bwd(ptr(dout), ptr(code), ptr(din_nhwc), b, c, h, w, stream_ptr(stream)),
+          "relu_maxpool2_nhwc_bwd")

@@ -178,6 +178,12 @@ def test_linear_b200_and_wide_cnn_b200_fall_back_to_torch_ops_on_cpu():
     wa = WideCNNB200(hidden=16)
     torch.manual_seed(1)
     wb = WideCNN(hidden=16)
-    assert list(wa.state_dict()) == list(wb.state_dict())
+    sa, sb = wa.state_dict(), wb.state_dict()
+    assert list(sa) == list(sb) and all(torch.equal(sa[k], sb[k]) for k in sa)   # same seed, same values
+    # fc1's weight is STORED with its columns in (h, w, c) order; state_dict converts both ways
+    assert not torch.equal(wa.classifier[0].weight, wb.classifier[0].weight)
     xi = torch.rand(2, 3, 32, 32)
-    assert torch.equal(wa(xi), wb(xi))
+    assert torch.allclose(wa(xi), wb(xi), atol=1e-5)
+    wc = WideCNNB200(hidden=16)
+    wc.load_state_dict(sb)
+    assert torch.equal(wc.classifier[0].weight, wa.classifier[0].weight)
