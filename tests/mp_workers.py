@@ -283,6 +283,47 @@ def scenario_bucketed():
         print("bucketed ok", flush=True)
 
 
+def scenario_bucketed_native():
+    """The widened CNN on the native kernels (models/wide_cnn.py WideCNNB200: tcgen05 linear layers whose
+    weight gradient is written straight into the gradient arena, channels-last conv1 / pooling kernels)
+    under BucketedDataParallel must match plain torch SGD on the torch model over the concatenated batch,
+    and keep the replicas bit-identical."""
+    import torch.nn.functional as F
+    from ddp_b200.models.wide_cnn import WideCNN, WideCNNB200
+    from ddp_b200.parallel.bucketed import BucketedDataParallel
+    rank, world, dev = _init()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(3)
+    m = WideCNNB200(hidden=96, native=True).to(dev)
+    ref = WideCNN(hidden=96).to(dev)
+    ref.load_state_dict(m.state_dict())
+    eng = BucketedDataParallel(m, rank, world, lr=0.05, bucket_mb=0.25)
+    assert len(eng.buckets) >= 3 and len(eng._direct) == 2, (len(eng.buckets), eng._direct)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(17)
+    b = 8
+    xs = torch.rand(4, world, b, 3, 32, 32, generator=g).to(dev)
+    ys = torch.randint(0, 10, (4, world, b), generator=g).to(dev)
+    for it in range(4):
+        eng.step(xs[it, rank], ys[it, rank], F.cross_entropy)
+        opt.zero_grad()
+        F.cross_entropy(ref(xs[it].reshape(-1, 3, 32, 32)), ys[it].reshape(-1)).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    sd, rd = m.state_dict(), ref.state_dict()     # state_dict() brings fc1's columns back to (c, h, w) order
+    for k in rd:
+        d = (sd[k] - rd[k]).abs().max().item()
+        assert d < 2e-4 * max(1.0, rd[k].abs().max().item()), (k, d)
+    gathered = [torch.empty_like(eng.flat_params) for _ in range(world)]
+    dist.all_gather(gathered, eng.flat_params.clone())
+    assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas diverged bitwise"
+    eng.close()
+    dist.barrier()
+    if rank == 0:
+        print("bucketed_native ok", flush=True)
+
+
 def scenario_nvls():
     """VMM + multicast communicator: descriptor exchange, multicast bind, then the in-switch
     (multimem.ld_reduce / multimem.st) all-reduce and fused all-reduce+SGD.  Prints
@@ -397,7 +438,7 @@ def scenario_dead_peer():
 
 
 if __name__ == "__main__":
-    {"dead_peer": scenario_dead_peer, "nvls": scenario_nvls, "bucketed": scenario_bucketed, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
+    {"dead_peer": scenario_dead_peer, "nvls": scenario_nvls, "bucketed": scenario_bucketed, "bucketed_native": scenario_bucketed_native, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
      "dp_equiv": scenario_dp_equiv}[sys.argv[1]]()
     if dist.is_initialized():
         dist.destroy_process_group()
