@@ -19,7 +19,9 @@
 
 namespace ddpb {
 
-int g_pdl = -1;  // -1: take the default from the environment (DDPB_PDL, default on)
+// The setting belongs to the calling host thread (kernels are launched by the thread that asked for
+// them): two engines driven from two threads of one process do not see each other's scoped overrides.
+thread_local int g_pdl = -1;  // -1: take the default from the environment (DDPB_PDL, default on)
 int pdl_enabled() {
   if (g_pdl < 0) {
     const char* e = getenv("DDPB_PDL");

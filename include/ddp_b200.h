@@ -37,7 +37,8 @@ extern "C" {
 #define DDPB_ERR_LIMIT 9003 /* size beyond a documented fixed limit */
 
 const char* ddpb_error_string(int code);
-/* Programmatic dependent launch for the step kernels: 1 on, 0 off, -1 = DDPB_PDL env (default on). */
+/* Programmatic dependent launch for the step kernels: 1 on, 0 off, -1 = DDPB_PDL env (default on).
+ * The setting is per host thread (it applies to the launches that thread makes). */
 void ddpb_set_pdl(int on);
 int ddpb_get_pdl(void);
 int ddpb_num_sms(void);
