@@ -285,6 +285,28 @@ pack_rows_split_kernel(const float* __restrict__ src, const float* __restrict__ 
   const int Rz = (R + kGemmKS - 1) / kGemmKS * kGemmKS;
   if (r >= Rz) return;
   const int c_begin = blockIdx.x * cpb;
+  if (vec && !mask && r < R && cpb == kPackChunks && (c_begin + kPackChunks) * 8 <= K) {
+    // fast path (whole 64-element group inside the matrix): all sixteen loads are issued before the
+    // first conversion, so a thread makes one global round trip instead of eight
+    const float4* p4 = reinterpret_cast<const float4*>(src + (long long)r * ld + c_begin * 8);
+    float4 v[2 * kPackChunks];
+#pragma unroll
+    for (int i = 0; i < 2 * kPackChunks; ++i) v[i] = p4[i];
+#pragma unroll
+    for (int cc = 0; cc < kPackChunks; ++cc) {
+      const float x[8] = {v[2 * cc].x, v[2 * cc].y, v[2 * cc].z, v[2 * cc].w,
+                          v[2 * cc + 1].x, v[2 * cc + 1].y, v[2 * cc + 1].z, v[2 * cc + 1].w};
+      float hi[8], lo[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) split_bf16(x[e], hi[e], lo[e]);
+      const long long o = (long long)(c_begin + cc) * rows_pad + r;
+      dst[o] = make_uint4(pack_bf16x2(hi[0], hi[1]), pack_bf16x2(hi[2], hi[3]), pack_bf16x2(hi[4], hi[5]),
+                          pack_bf16x2(hi[6], hi[7]));
+      dst[set_stride + o] = make_uint4(pack_bf16x2(lo[0], lo[1]), pack_bf16x2(lo[2], lo[3]),
+                                       pack_bf16x2(lo[4], lo[5]), pack_bf16x2(lo[6], lo[7]));
+    }
+    return;
+  }
 #pragma unroll 4
   for (int cc = 0; cc < cpb; ++cc) {
     const int c = c_begin + cc;

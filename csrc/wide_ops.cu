@@ -23,12 +23,24 @@ constexpr int kWideXs = 36;      // padded row length of the staged input tile (
 template <int CIN>
 __device__ __forceinline__ void stage_input_tile(const float* __restrict__ x, float (*xs)[kWideRows + 2][kWideXs],
                                                  int b, int h0, int H, int tid, int nthreads) {
-  for (int i = tid; i < CIN * (kWideRows + 2) * 34; i += nthreads) {
+  // all loads of a thread are issued before the first store (the loop below is fully unrolled): one global
+  // round trip per tile instead of one per element
+  constexpr int N = CIN * (kWideRows + 2) * 34;
+  constexpr int PER = (N + 127) / 128;  // nthreads is 128 at every call site
+  float v[PER];
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const int i = tid + k * nthreads;
     const int col = i % 34, row = (i / 34) % (kWideRows + 2), ci = i / (34 * (kWideRows + 2));
     const int h = h0 - 1 + row, w = col - 1;
-    float v = 0.f;
-    if (h >= 0 && h < H && w >= 0 && w < kWideW) v = x[(((long long)b * CIN + ci) * H + h) * kWideW + w];
-    xs[ci][row][col] = v;
+    v[k] = 0.f;
+    if (i < N && h >= 0 && h < H && w >= 0 && w < kWideW) v[k] = x[(((long long)b * CIN + ci) * H + h) * kWideW + w];
+  }
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    const int i = tid + k * nthreads;
+    const int col = i % 34, row = (i / 34) % (kWideRows + 2), ci = i / (34 * (kWideRows + 2));
+    if (i < N) xs[ci][row][col] = v[k];
   }
 }
 
@@ -132,14 +144,25 @@ conv3x3_small_cin_wgrad_kernel(const float* __restrict__ g, const float* __restr
     __syncthreads();  // the previous tile is consumed
     stage_input_tile<CIN>(x, xs, b, h0, H, tid, 128);  // fills channels [0, CIN) only
     const long long base = (((long long)b * H + h0) * kWideW) * COUT;
-    for (int i = tid; i < kWideRows * kWideW * COUT / 4; i += 128) {
-      float4 gv = *reinterpret_cast<const float4*>(g + base + 4 * i);
-      if (act) {
-        const float4 av = *reinterpret_cast<const float4*>(act + base + 4 * i);
-        gv.x = av.x > 0.f ? gv.x : 0.f; gv.y = av.y > 0.f ? gv.y : 0.f;
-        gv.z = av.z > 0.f ? gv.z : 0.f; gv.w = av.w > 0.f ? gv.w : 0.f;
+    constexpr int kVec = kWideRows * kWideW * COUT / 4 / 128;  // float4 per thread (16)
+#pragma unroll
+    for (int k0 = 0; k0 < kVec; k0 += 8) {  // eight gradient (and mask) loads in flight per thread
+      float4 gv[8], av[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = tid + (k0 + u) * 128;
+        gv[u] = *reinterpret_cast<const float4*>(g + base + 4 * i);
+        if (act) av[u] = *reinterpret_cast<const float4*>(act + base + 4 * i);
       }
-      *reinterpret_cast<float4*>(&gs[0][0] + 4 * i) = gv;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = tid + (k0 + u) * 128;
+        if (act) {
+          gv[u].x = av[u].x > 0.f ? gv[u].x : 0.f; gv[u].y = av[u].y > 0.f ? gv[u].y : 0.f;
+          gv[u].z = av[u].z > 0.f ? gv[u].z : 0.f; gv[u].w = av[u].w > 0.f ? gv[u].w : 0.f;
+        }
+        *reinterpret_cast<float4*>(&gs[0][0] + 4 * i) = gv[u];
+      }
     }
     __syncthreads();
     if (tg < 7) {

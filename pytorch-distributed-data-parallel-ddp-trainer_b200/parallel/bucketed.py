@@ -39,8 +39,16 @@ def plan_buckets(spans, bucket_mb: float):
 
 class BucketedDataParallel:
     def __init__(self, module: torch.nn.Module, rank: int, world_size: int, lr: float = 0.01,
-                 bucket_mb: float = 25.0, algo: int = ALGO_AUTO):
+                 bucket_mb: float = 25.0, algo: int = ALGO_AUTO, use_graph: bool = False):
+        """``use_graph``: after two eager steps with a given input shape, the whole step (forward, backward,
+        bucket exchanges on the side streams) is captured once per (shape, step parity) in a CUDA graph and
+        replayed — the module must then do the same work every step (no data-dependent control flow)."""
         self.module, self.rank, self.world_size, self.lr, self.algo = module, rank, world_size, lr, algo
+        self.use_graph = use_graph
+        self._graphs: dict = {}
+        self._static: dict = {}
+        self._seen: dict = {}
+        self._pool = None
         params = [p for p in module.parameters() if p.requires_grad]
         self.device = params[0].device
         # arena order = reverse registration order, so buckets fill front to back during backward
@@ -137,6 +145,34 @@ class BucketedDataParallel:
     def step(self, x: torch.Tensor, y: torch.Tensor, loss_fn) -> torch.Tensor:
         """forward + backward (+ per-bucket fused all-reduce/SGD from the grad hooks)."""
         self._parity = self.step_count & 1
+        if not self.use_graph:
+            return self._step_eager(x, y, loss_fn)
+        key = (tuple(x.shape), x.dtype, tuple(y.shape), y.dtype, self._parity, loss_fn)
+        seen = self._seen.get(key, 0)
+        self._seen[key] = seen + 1
+        if seen < 2:          # warm-up: lazy initialisation, cuDNN plans, workspace growth
+            return self._step_eager(x, y, loss_fn)
+        skey = key[:4]
+        if skey not in self._static:
+            self._static[skey] = (torch.empty_like(x), torch.empty_like(y))
+        xs, ys = self._static[skey]
+        xs.copy_(x, non_blocking=True)
+        ys.copy_(y, non_blocking=True)
+        entry = self._graphs.get(key)
+        if entry is None:
+            graph = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize(self.device)
+            with torch.cuda.graph(graph, pool=self._pool):
+                loss = self._step_eager(xs, ys, loss_fn, count=False)
+            if self._pool is None:
+                self._pool = graph.pool()
+            entry = self._graphs[key] = (graph, loss)
+        graph, loss = entry
+        graph.replay()
+        self.step_count += 1
+        return loss.clone()
+
+    def _step_eager(self, x: torch.Tensor, y: torch.Tensor, loss_fn, count: bool = True) -> torch.Tensor:
         g = self.flat_grads[self._parity]
         for i, (p, o) in enumerate(self._views):
             v = g[o:o + p.numel()].view(p.shape)
@@ -161,12 +197,15 @@ class BucketedDataParallel:
         for side, ev in zip(self.sides, self._done):
             ev.record(side)
             cur.wait_event(ev)  # parameters are final before the next forward
-        self.step_count += 1
+        if count:
+            self.step_count += 1
         return loss.detach()
 
     def close(self, sync_peers: bool = True) -> None:
         """See B200DataParallel.close: peers must be done reading this rank's buffer before it goes."""
         torch.cuda.synchronize(self.device)
+        self._graphs.clear()
+        self._static.clear()
         if sync_peers and self.world_size > 1 and dist.is_available() and dist.is_initialized():
             dist.barrier()
         self.comm.close()

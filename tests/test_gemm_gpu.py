@@ -263,3 +263,28 @@ def test_wide_cnn_b200_gradients_against_fp64_and_the_torch_model(nat):
         e_ours = float((ga.double() - r.grad).abs().max()) / scale
         e_torch = float((q.grad.double() - r.grad).abs().max()) / scale
         assert e_ours < max(2 * e_torch, 1e-5), (n, e_ours, e_torch)
+
+
+def test_bucketed_engine_graph_replay_matches_eager_steps(nat):
+    """BucketedDataParallel(use_graph=True) on one GPU: the captured step (native model, bucket updates on
+    the side streams) leaves exactly the parameters the eager engine leaves."""
+    from ddp_b200.models.wide_cnn import WideCNNB200
+    from ddp_b200.parallel.bucketed import BucketedDataParallel
+    dev = torch.device("cuda", 0)
+    g = torch.Generator().manual_seed(11)
+    xs = [torch.rand(16, 3, 32, 32, generator=g).to(dev) for _ in range(3)]
+    ys = [torch.randint(0, 10, (16,), generator=g).to(dev) for _ in range(3)]
+    finals = []
+    for use_graph in (False, True):
+        torch.manual_seed(9)
+        m = WideCNNB200(hidden=64, native=True).to(dev)
+        eng = BucketedDataParallel(m, 0, 1, lr=0.05, bucket_mb=1.0, use_graph=use_graph)
+        losses = [float(eng.step(xs[i % 3], ys[i % 3], F.cross_entropy)) for i in range(8)]
+        torch.cuda.synchronize()
+        finals.append((losses, {k: v.clone() for k, v in m.state_dict().items()}))
+        if use_graph:
+            assert len(eng._graphs) == 2          # one per step parity
+        eng.close()
+    (l0, s0), (l1, s1) = finals
+    assert l0 == l1, (l0, l1)
+    assert all(torch.equal(s0[k], s1[k]) for k in s0)

@@ -1,4 +1,5 @@
 """BASELINE.json config 4: widened CNN (~25 M params, 3x32x32 synthetic), DP on N GPUs.
+native_graph = the native arm with the whole step replayed from a CUDA graph (BucketedDataParallel use_graph)
 native = WideCNNB200 (fully connected layers on the tcgen05 GEMM of csrc/gemm_tc.cu, fused ReLU+max-pool;
          convolutions through cuDNN) under BucketedDataParallel, fc1's weight gradient written straight
          into the gradient arena
@@ -69,6 +70,17 @@ def main():
     del eng, mn
     torch.cuda.empty_cache()
 
+    # the same arm with the whole step (forward, backward, bucket exchanges) replayed from a CUDA graph
+    torch.manual_seed(0)
+    mg = WideCNNB200(native=True).to(dev)
+    eng = BucketedDataParallel(mg, rank, world, lr=0.01, bucket_mb=a.bucket_mb, use_graph=True)
+    ms, loss = timed_steps(lambda x, y: eng.step(x, y, F.cross_entropy), xs, ys, a.steps, max(a.warmup, 6), world, dev)
+    out["native_graph_ms_per_step"], out["native_graph_img_s"] = ms, world * a.batch / ms * 1e3
+    out["native_graph_loss"] = loss
+    eng.close()
+    del eng, mg
+    torch.cuda.empty_cache()
+
     torch.manual_seed(0)
     m = WideCNN().to(dev)
     out["params"] = param_count(m)
@@ -96,6 +108,7 @@ def main():
     ms, loss = timed_steps(torch_step, xs, ys, a.steps, a.warmup, world, dev)
     out["torch_ddp_ms_per_step"], out["torch_ddp_img_s"], out["torch_loss"] = ms, world * a.batch / ms * 1e3, loss
     out["native_speedup_vs_torch_ddp"] = out["torch_ddp_ms_per_step"] / out["native_ms_per_step"]
+    out["native_graph_speedup_vs_torch_ddp"] = out["torch_ddp_ms_per_step"] / out["native_graph_ms_per_step"]
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
