@@ -61,7 +61,9 @@ class _NativeLinearFn(torch.autograd.Function):
         x = x.detach().contiguous().float()
         w = weight.detach().contiguous()
         ws.x.pack(x)
-        ws.w.pack(w)                      # the weights may have changed since the last call
+        if not layer._w_packed_valid:     # the weights may have changed since the last call
+            ws.w.pack(w)
+        layer._w_packed_valid = False     # one forward per prepack(): whoever updates the weights renews it
         y = torch.empty(batch, out_f, dtype=torch.float32, device=x.device)
         # y^T[o][b] = sum_k W[o][k] x[b][k]: A = W (K-major), B = x (K-major), stored transposed = y[b][o]
         _gemm(nat, ws, ws.w, False, ws.x, False, out_f, batch, in_f, y, True,
@@ -117,6 +119,21 @@ class LinearB200(nn.Linear):
         self._nat = None
         self._ws: dict = {}
         self._live = None
+        self._w_packed_valid = False
+
+    def prepack(self, stream=None) -> bool:
+        """Pack the CURRENT weights for the next forward now (on ``stream``), instead of at the start of
+        that forward: an engine that has just updated the weights calls this where the pack overlaps other
+        work.  Valid for exactly one forward.  Returns False (and does nothing) before the first native
+        forward, when no workspace exists yet."""
+        if self._nat is None or not self.weight.is_cuda:
+            return False
+        ws = self._ws.get(self.weight.device)
+        if ws is None:
+            return False
+        ws.w.pack(self.weight.detach(), stream=stream)
+        self._w_packed_valid = True
+        return True
 
     def _use_native(self, x: torch.Tensor) -> bool:
         if self._native_wanted is False or not x.is_cuda or x.dim() != 2 or self.weight.dtype != torch.float32:
@@ -143,6 +160,7 @@ class LinearB200(nn.Linear):
     def _apply(self, fn, *a, **kw):  # .to()/.cuda()/.cpu(): workspaces belong to the old device
         self._ws.clear()
         self._live = None
+        self._w_packed_valid = False
         return super()._apply(fn, *a, **kw)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -108,6 +108,9 @@ class BucketedDataParallel:
         self.sync_params()
 
     def sync_params(self, src: int = 0) -> None:
+        for mod in getattr(self, "_direct", {}).values():  # packed weight copies are stale after this
+            if hasattr(mod, "_w_packed_valid"):
+                mod._w_packed_valid = False
         torch.cuda.synchronize(self.device)
         if self.world_size > 1:
             self.comm.broadcast(self.param_off, self.numel * 4, root=src, slot=7)
@@ -141,6 +144,29 @@ class BucketedDataParallel:
         b["launched"] = True
         self.comm.allreduce_sgd(goff + b["start"] * 4, self.param_off + b["start"] * 4, b["n"],
                                 self.lr_dev, self.algo, slot=b_i % 6, stream=side)
+        if self.use_graph:  # an eagerly launched step is host-bound: the extra stream bookkeeping costs more there
+            self._prepack_updated_layers()
+
+    def _prepack_updated_layers(self) -> None:
+        """A layer that keeps a packed copy of its weight (models/linear.py) gets it rebuilt as soon as the
+        last bucket holding a piece of that weight has been launched: on a side stream, under the rest of
+        backward, instead of at the start of the next forward."""
+        for idx, mod in self._direct.items():
+            if idx in self._prepacked or not hasattr(mod, "prepack"):
+                continue
+            bs = self._buckets_of[idx]
+            if not all(self.buckets[b].get("launched") for b in bs):
+                continue
+            self._prepacked.add(idx)
+            home = self.sides[bs[-1] % len(self.sides)]
+            for s_i in sorted({b % len(self.sides) for b in bs}):
+                side = self.sides[s_i]
+                if side is not home:
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                    home.wait_event(ev)
+            with torch.cuda.stream(home):
+                mod.prepack(stream=home)
 
     def step(self, x: torch.Tensor, y: torch.Tensor, loss_fn) -> torch.Tensor:
         """forward + backward (+ per-bucket fused all-reduce/SGD from the grad hooks)."""
@@ -166,8 +192,10 @@ class BucketedDataParallel:
                 loss = self._step_eager(xs, ys, loss_fn, count=False)
             if self._pool is None:
                 self._pool = graph.pool()
-            entry = self._graphs[key] = (graph, loss)
-        graph, loss = entry
+            # the graph holds raw pointers into the layers' workspaces: keep those alive with it
+            keep = [dict(m._ws) for m in self.module.modules() if isinstance(getattr(m, "_ws", None), dict)]
+            entry = self._graphs[key] = (graph, loss, keep)
+        graph, loss = entry[0], entry[1]
         graph.replay()
         self.step_count += 1
         return loss.clone()
@@ -185,6 +213,7 @@ class BucketedDataParallel:
         for b in self.buckets:
             b["pending"] = len(b["members"])
             b["launched"] = False
+        self._prepacked = set()
         loss = loss_fn(self.module(x), y)
         loss.backward()
         # A parameter that got no gradient this step (a branch not taken, a frozen path) never fires its

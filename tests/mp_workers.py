@@ -283,7 +283,12 @@ def scenario_bucketed():
         print("bucketed ok", flush=True)
 
 
-def scenario_bucketed_native():
+def scenario_bucketed_native_graph():
+    """Same as bucketed_native with the step replayed from CUDA graphs (captured per step parity)."""
+    scenario_bucketed_native(use_graph=True, steps=8, tag="bucketed_native_graph")
+
+
+def scenario_bucketed_native(use_graph=False, steps=4, tag="bucketed_native"):
     """The widened CNN on the native kernels (models/wide_cnn.py WideCNNB200: tcgen05 linear layers whose
     weight gradient is written straight into the gradient arena, channels-last conv1 / pooling kernels)
     under BucketedDataParallel must match plain torch SGD on the torch model over the concatenated batch,
@@ -298,14 +303,14 @@ def scenario_bucketed_native():
     m = WideCNNB200(hidden=96, native=True).to(dev)
     ref = WideCNN(hidden=96).to(dev)
     ref.load_state_dict(m.state_dict())
-    eng = BucketedDataParallel(m, rank, world, lr=0.05, bucket_mb=0.25)
+    eng = BucketedDataParallel(m, rank, world, lr=0.05, bucket_mb=0.25, use_graph=use_graph)
     assert len(eng.buckets) >= 3 and len(eng._direct) == 2, (len(eng.buckets), eng._direct)
     opt = torch.optim.SGD(ref.parameters(), lr=0.05)
     g = torch.Generator().manual_seed(17)
     b = 8
-    xs = torch.rand(4, world, b, 3, 32, 32, generator=g).to(dev)
-    ys = torch.randint(0, 10, (4, world, b), generator=g).to(dev)
-    for it in range(4):
+    xs = torch.rand(steps, world, b, 3, 32, 32, generator=g).to(dev)
+    ys = torch.randint(0, 10, (steps, world, b), generator=g).to(dev)
+    for it in range(steps):
         eng.step(xs[it, rank], ys[it, rank], F.cross_entropy)
         opt.zero_grad()
         F.cross_entropy(ref(xs[it].reshape(-1, 3, 32, 32)), ys[it].reshape(-1)).backward()
@@ -318,10 +323,12 @@ def scenario_bucketed_native():
     gathered = [torch.empty_like(eng.flat_params) for _ in range(world)]
     dist.all_gather(gathered, eng.flat_params.clone())
     assert all(torch.equal(t, gathered[0]) for t in gathered), "replicas diverged bitwise"
+    if use_graph:
+        assert len(eng._graphs) == 2, len(eng._graphs)
     eng.close()
     dist.barrier()
     if rank == 0:
-        print("bucketed_native ok", flush=True)
+        print(f"{tag} ok", flush=True)
 
 
 def scenario_nvls():
@@ -438,7 +445,7 @@ def scenario_dead_peer():
 
 
 if __name__ == "__main__":
-    {"dead_peer": scenario_dead_peer, "nvls": scenario_nvls, "bucketed": scenario_bucketed, "bucketed_native": scenario_bucketed_native, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
+    {"dead_peer": scenario_dead_peer, "nvls": scenario_nvls, "bucketed": scenario_bucketed, "bucketed_native": scenario_bucketed_native, "bucketed_native_graph": scenario_bucketed_native_graph, "allreduce": scenario_allreduce, "fused_sgd": scenario_fused_sgd, "stress": scenario_stress,
      "dp_equiv": scenario_dp_equiv}[sys.argv[1]]()
     if dist.is_initialized():
         dist.destroy_process_group()

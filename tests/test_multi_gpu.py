@@ -32,7 +32,7 @@ def _torchrun(world, script_args, cwd=None, env=None, timeout=600):
 
 @pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
 @pytest.mark.parametrize("world", WORLDS or [2])
-@pytest.mark.parametrize("scenario", ["allreduce", "fused_sgd", "stress", "dp_equiv", "bucketed", "bucketed_native"])
+@pytest.mark.parametrize("scenario", ["allreduce", "fused_sgd", "stress", "dp_equiv", "bucketed", "bucketed_native", "bucketed_native_graph"])
 def test_scenario(world, scenario):
     out = _torchrun(world, [os.path.join(ROOT, "tests", "mp_workers.py"), scenario])
     assert f"{scenario} ok" in out
