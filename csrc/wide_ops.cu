@@ -190,11 +190,12 @@ conv3x3_small_cin_wgrad_kernel(const float* __restrict__ g, const float* __restr
   }
 }
 
-// out[i] = sum_p part[p*n + i] for a short vector and many parts: 1024 threads = 32 consecutive outputs x
+// out[i] = sum_p part[p*stride + i], i < n, for a short vector and many parts: 1024 threads = 32 consecutive outputs x
 // 32 part groups; group g adds parts g, g+32, ... (loads independent, all in flight), then the 32 group
 // sums are added in group order.  Fixed order => deterministic.
 __global__ void __launch_bounds__(1024)
-reduce_parts32_kernel(const float* __restrict__ part, int nparts, int n, float* __restrict__ out) {
+reduce_parts32_kernel(const float* __restrict__ part, int nparts, long long stride, int n,
+                      float* __restrict__ out) {
   __shared__ float sm[32][33];
   pdl_sync();
   const int lane = threadIdx.x & 31, pg = threadIdx.x >> 5;
@@ -205,11 +206,11 @@ reduce_parts32_kernel(const float* __restrict__ part, int nparts, int n, float* 
     for (; p + 96 < nparts; p += 128) {
       float v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = part[(long long)(p + 32 * u) * n + idx];
+      for (int u = 0; u < 4; ++u) v[u] = part[(long long)(p + 32 * u) * stride + idx];
 #pragma unroll
       for (int u = 0; u < 4; ++u) s += v[u];
     }
-    for (; p < nparts; p += 32) s += part[(long long)p * n + idx];
+    for (; p < nparts; p += 32) s += part[(long long)p * stride + idx];
   }
   sm[pg][lane] = s;
   __syncthreads();
@@ -281,6 +282,98 @@ relu_maxpool2_nhwc_bwd_kernel(const float* __restrict__ dout, const uint8_t* __r
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Linear layers with a handful of outputs (a classifier head: NOUT <= 16), exact fp32.  The tensor-core
+// GEMM of gemm_tc.cu pads such a layer to a 128-wide tile and needs ten launches per step (three packs,
+// three GEMMs, split-K reduces, a column sum); these are four.
+constexpr int kSmallOutMax = 16;
+
+// y[b][o] = sum_k x[b][k] W[o][k] + bias[o]; one block per batch row, its 256 threads stride over k (a few
+// independent iterations each: the loads of all of them are in flight together), then a fixed-order
+// reduction over lanes and warps.
+__global__ void __launch_bounds__(256)
+small_linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                        float* __restrict__ y, int batch, int K, int nout) {
+  __shared__ float red[8][kSmallOutMax];
+  pdl_sync();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.x;
+  float acc[kSmallOutMax];
+#pragma unroll
+  for (int o = 0; o < kSmallOutMax; ++o) acc[o] = 0.f;
+  const float* xr = x + (long long)b * K;
+#pragma unroll 4
+  for (int k = threadIdx.x; k < K; k += 256) {
+    const float xv = xr[k];
+#pragma unroll
+    for (int o = 0; o < kSmallOutMax; ++o)
+      if (o < nout) acc[o] = fmaf(xv, w[(long long)o * K + k], acc[o]);
+  }
+#pragma unroll
+  for (int o = 0; o < kSmallOutMax; ++o) {
+    float v = acc[o];
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+    if (lane == 0) red[warp][o] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < nout) {
+    float v = 0.f;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v += red[u][threadIdx.x];
+    y[(long long)b * nout + threadIdx.x] = v + (bias ? bias[threadIdx.x] : 0.f);
+  }
+}
+
+// dx[b][k] = sum_o dy[b][o] W[o][k]; thread per (b, k).
+__global__ void __launch_bounds__(256)
+small_linear_dx_kernel(const float* __restrict__ dy, const float* __restrict__ w, float* __restrict__ dx, int batch,
+                       int K, int nout) {
+  pdl_sync();
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  const int b = blockIdx.y;
+  if (k >= K) return;
+  float s = 0.f;
+  for (int o = 0; o < nout; ++o) s = fmaf(dy[(long long)b * nout + o], w[(long long)o * K + k], s);
+  dx[(long long)b * K + k] = s;
+}
+
+// partial[part][o*K + k] = sum over the part's batch rows of dy[b][o] x[b][k]; partial[part][nout*K + o] =
+// sum of dy[b][o] (the bias gradient).  Thread per k; blockIdx.y = part (32 batch rows).
+__global__ void __launch_bounds__(256)
+small_linear_dw_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* __restrict__ partial,
+                       int batch, int K, int nout) {
+  __shared__ float dys[32][kSmallOutMax];
+  pdl_sync();
+  const int k = blockIdx.x * 256 + threadIdx.x;
+  const int b0 = blockIdx.y * 32;
+  const int nb = min(32, batch - b0);
+  for (int i = threadIdx.x; i < 32 * kSmallOutMax; i += 256) {
+    const int bb = i / kSmallOutMax, o = i % kSmallOutMax;
+    dys[bb][o] = (bb < nb && o < nout) ? dy[(long long)(b0 + bb) * nout + o] : 0.f;
+  }
+  __syncthreads();
+  float* dst = partial + (long long)blockIdx.y * ((long long)nout * K + nout);
+  if (k < K) {
+    float acc[kSmallOutMax];
+#pragma unroll
+    for (int o = 0; o < kSmallOutMax; ++o) acc[o] = 0.f;
+    for (int bb = 0; bb < nb; ++bb) {
+      const float xv = x[(long long)(b0 + bb) * K + k];
+#pragma unroll
+      for (int o = 0; o < kSmallOutMax; ++o) acc[o] = fmaf(xv, dys[bb][o], acc[o]);
+    }
+#pragma unroll
+    for (int o = 0; o < kSmallOutMax; ++o)
+      if (o < nout) dst[(long long)o * K + k] = acc[o];
+  }
+  if (blockIdx.x == 0 && threadIdx.x < nout) {
+    float s = 0.f;
+    for (int bb = 0; bb < nb; ++bb) s += dys[bb][threadIdx.x];
+    dst[(long long)nout * K + threadIdx.x] = s;
+  }
+}
+
 }  // namespace ddpb
 
 using namespace ddpb;
@@ -318,7 +411,7 @@ int ddpb_conv3x3_small_cin_wgrad(const float* dact, const float* act, const floa
                         dact, act, x, partial, batch, H));
   const int n = cout * kWgradSlots;
   DDPB_CUDA_OK(launch_k(reduce_parts32_kernel, dim3((n + 31) / 32), dim3(1024), 0, (cudaStream_t)stream,
-                        (const float*)partial, parts, n, dw_db));
+                        (const float*)partial, parts, (long long)n, n, dw_db));
   return 0;
 }
 
@@ -344,6 +437,43 @@ int ddpb_relu_maxpool2_nhwc_bwd(const float* dout, const unsigned char* code, fl
   const long long n4 = (long long)batch * (H / 2) * (W / 2) * (C / 4);
   DDPB_CUDA_OK(launch_k(relu_maxpool2_nhwc_bwd_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0,
                         (cudaStream_t)stream, dout, code, din, n4, C, H, W));
+  return 0;
+}
+
+// ---- linear layers with at most 16 outputs, exact fp32 (x [batch][k], w [nout][k] row-major)
+int ddpb_small_linear_max_out() { return kSmallOutMax; }
+
+int ddpb_small_linear_fwd(const float* x, const float* w, const float* bias, float* y, int batch, int k, int nout,
+                          void* stream) {
+  if (batch <= 0 || k <= 0 || nout <= 0 || nout > kSmallOutMax) return DDPB_ERR_SHAPE;
+  DDPB_CUDA_OK(launch_k(small_linear_fwd_kernel, dim3(batch), dim3(256), 0, (cudaStream_t)stream, x, w, bias, y,
+                        batch, k, nout));
+  return 0;
+}
+
+// Floats of scratch ddpb_small_linear_bwd needs.
+size_t ddpb_small_linear_bwd_scratch_floats(int batch, int k, int nout) {
+  return (size_t)((batch + 31) / 32) * ((size_t)nout * k + nout);
+}
+
+// dx [batch][k] (NULL = skip), dw [nout][k], db [nout] (NULL = skip) from dy [batch][nout], x and w.
+int ddpb_small_linear_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, float* db,
+                          float* scratch, int batch, int k, int nout, void* stream) {
+  if (batch <= 0 || k <= 0 || nout <= 0 || nout > kSmallOutMax) return DDPB_ERR_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dx)
+    DDPB_CUDA_OK(launch_k(small_linear_dx_kernel, dim3((k + 255) / 256, batch), dim3(256), 0, st, dy, w, dx, batch, k,
+                          nout));
+  const int parts = (batch + 31) / 32;
+  if (parts > 65535) return DDPB_ERR_LIMIT;
+  DDPB_CUDA_OK(launch_k(small_linear_dw_kernel, dim3((k + 255) / 256, parts), dim3(256), 0, st, dy, x, scratch, batch,
+                        k, nout));
+  const long long stride = (long long)nout * k + nout;
+  DDPB_CUDA_OK(launch_k(reduce_parts32_kernel, dim3((nout * k + 31) / 32), dim3(1024), 0, st,
+                        (const float*)scratch, parts, stride, nout * k, dw));
+  if (db)
+    DDPB_CUDA_OK(launch_k(reduce_parts32_kernel, dim3(1), dim3(1024), 0, st,
+                          (const float*)(scratch + (long long)nout * k), parts, stride, nout, db));
   return 0;
 }
 

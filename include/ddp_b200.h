@@ -358,6 +358,18 @@ int ddpb_relu_maxpool2_nhwc_fwd(const float* in, const float* bias, float* out, 
 int ddpb_relu_maxpool2_nhwc_bwd(const float* dout, const unsigned char* code, float* din, int batch, int C, int H,
                                 int W, void* stream);
 
+/* ---- linear layers with at most ddpb_small_linear_max_out() (16) outputs — a classifier head of any
+ * input width — in exact fp32 on the CUDA cores: one launch forward, three backward (csrc/wide_ops.cu).
+ * What nn.Linear's cuBLAS calls do for such a layer (reference model.py:16 is the 10-output case the step
+ * engine specialises further).  x [batch][k], w [nout][k], y / dy [batch][nout], all row-major fp32;
+ * scratch = ddpb_small_linear_bwd_scratch_floats() floats; dx and db may be NULL. */
+int ddpb_small_linear_max_out(void);
+int ddpb_small_linear_fwd(const float* x, const float* w, const float* bias, float* y, int batch, int k, int nout,
+                          void* stream);
+size_t ddpb_small_linear_bwd_scratch_floats(int batch, int k, int nout);
+int ddpb_small_linear_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, float* db,
+                          float* scratch, int batch, int k, int nout, void* stream);
+
 /* ---- p -= lr*g with lr read from device memory (single-GPU path; multi-GPU runs fuse the
  * update into the all-reduce).  reference train_ddp.py:41,200. */
 int ddpb_sgd(float* p, const float* grad, const float* lr_dev, long long n, void* stream);

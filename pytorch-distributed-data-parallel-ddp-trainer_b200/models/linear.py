@@ -2,7 +2,8 @@
 kernels of csrc/gemm_tc.cu.
 
 ``LinearB200`` is an ``nn.Linear`` (same parameters, same ``state_dict`` keys, same default
-initialisation) whose CUDA forward/backward are three tcgen05 GEMMs over operands packed once per step
+initialisation) whose CUDA forward/backward are — for layers with more than 16 outputs; a classifier head
+runs on exact-fp32 CUDA-core kernels instead — three tcgen05 GEMMs over operands packed once per step
 as split row planes (x = hi + lo bf16, "bf16x3": above TF32 operand precision, fp32 accumulation) —
 what the reference gets from cuBLAS through ``nn.Linear`` (reference model.py:16, train_ddp.py:199),
 here for shapes beyond the 10-class head the step engine hard-codes: BASELINE.json config 4's
@@ -105,6 +106,38 @@ class _NativeLinearFn(torch.autograd.Function):
         return dx, dw, db, None
 
 
+class _SmallLinearFn(torch.autograd.Function):
+    """A layer with at most 16 outputs (a classifier head): exact fp32 CUDA-core kernels, one launch forward
+    and three backward, no packing (csrc/wide_ops.cu)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, layer):
+        nat = layer._nat
+        x = x.detach().contiguous().float()
+        w = weight.detach().contiguous()
+        y = torch.empty(x.shape[0], w.shape[0], dtype=torch.float32, device=x.device)
+        nat.small_linear_fwd(x, w, None if bias is None else bias.detach(), y)
+        ctx.layer, ctx.has_bias = layer, bias is not None
+        ctx.save_for_backward(x, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        layer, nat = ctx.layer, ctx.layer._nat
+        x, w = ctx.saved_tensors
+        dy = dy.contiguous().float()
+        out_f, in_f = w.shape
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        dst = layer.weight_grad_out
+        if dst is not None and dst.shape == (out_f, in_f) and dst.is_contiguous() and dst.device == dy.device:
+            dw = dst.view(out_f, in_f)
+        else:
+            dw = torch.empty(out_f, in_f, dtype=torch.float32, device=dy.device)
+        db = torch.empty(out_f, dtype=torch.float32, device=dy.device) if ctx.has_bias else None
+        nat.small_linear_bwd(dy, x, w, dx, dw, db)
+        return dx, dw, db, None
+
+
 class LinearB200(nn.Linear):
     """Drop-in ``nn.Linear`` (+ optional fused ReLU) on the tcgen05 GEMM of csrc/gemm_tc.cu."""
 
@@ -126,7 +159,7 @@ class LinearB200(nn.Linear):
         that forward: an engine that has just updated the weights calls this where the pack overlaps other
         work.  Valid for exactly one forward.  Returns False (and does nothing) before the first native
         forward, when no workspace exists yet."""
-        if self._nat is None or not self.weight.is_cuda:
+        if self._nat is None or not self.weight.is_cuda or (self.out_features <= 16 and not self.fused_relu):
             return False
         ws = self._ws.get(self.weight.device)
         if ws is None:
@@ -165,6 +198,8 @@ class LinearB200(nn.Linear):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self._use_native(x):
+            if self.out_features <= 16 and not self.fused_relu:
+                return _SmallLinearFn.apply(x, self.weight, self.bias, self)
             return _NativeLinearFn.apply(x, self.weight, self.bias, self)
         y = F.linear(x, self.weight, self.bias)
         return F.relu(y) if self.fused_relu else y

@@ -100,6 +100,10 @@ _SIGNATURES = {
     "ddpb_conv3x3_small_cin_wgrad": (I, [P, P, P, P, P, I, I, I, I, I, P]),
     "ddpb_relu_maxpool2_nhwc_fwd": (I, [P, P, P, P, I, I, I, I, P]),
     "ddpb_relu_maxpool2_nhwc_bwd": (I, [P, P, P, I, I, I, I, P]),
+    "ddpb_small_linear_max_out": (I, []),
+    "ddpb_small_linear_fwd": (I, [P, P, P, P, I, I, I, P]),
+    "ddpb_small_linear_bwd_scratch_floats": (c_size_t, [I, I, I]),
+    "ddpb_small_linear_bwd": (I, [P, P, P, P, P, P, P, I, I, I, P]),
 }
 
 #: execution precisions of the step (models/simple_cnn.py): "bf16x3" = the reference's numerics
@@ -603,3 +607,23 @@ def relu_maxpool2_nhwc_bwd(dout, code, din_nhwc, stream=None):
     b, h, w, c = din_nhwc.shape
     check(lib().ddpb_relu_maxpool2_nhwc_bwd(ptr(dout), ptr(code), ptr(din_nhwc), b, c, h, w, stream_ptr(stream)),
           "relu_maxpool2_nhwc_bwd")
+
+
+# ----------------------------------------------------------------------------- small-output linear layers (fp32)
+def small_linear_max_out() -> int:
+    return int(lib().ddpb_small_linear_max_out())
+
+
+def small_linear_fwd(x, w, bias, y, stream=None):
+    batch, k = x.shape
+    check(lib().ddpb_small_linear_fwd(ptr(x), ptr(w), ptr(bias), ptr(y), batch, k, w.shape[0], stream_ptr(stream)),
+          "small_linear_fwd")
+
+
+def small_linear_bwd(dy, x, w, dx, dw, db, stream=None):
+    batch, k = x.shape
+    nout = w.shape[0]
+    scr = torch.empty(int(lib().ddpb_small_linear_bwd_scratch_floats(batch, k, nout)), dtype=torch.float32,
+                      device=x.device)
+    check(lib().ddpb_small_linear_bwd(ptr(dy), ptr(x), ptr(w), ptr(dx), ptr(dw), ptr(db), ptr(scr), batch, k, nout,
+                                      stream_ptr(stream)), "small_linear_bwd")

@@ -164,6 +164,28 @@ def test_linear_b200_against_fp64_and_torch(nat, batch, in_f, out_f, relu):
             assert e_ours < 2e-5, (name, b, e_ours, e_torch)
 
 
+def test_small_output_linear_is_exact_fp32(nat):
+    """Layers with at most 16 outputs use the CUDA-core kernels of csrc/wide_ops.cu: fp32-exact results
+    (1e-6 relative to fp64, where the tensor-core path's split operands give 1e-5)."""
+    dev = "cuda"
+    torch.manual_seed(12)
+    for batch, k, nout in ((256, 750, 10), (45, 1000, 16), (1, 33, 1)):
+        x = torch.randn(batch, k, device=dev)
+        w = torch.randn(nout, k, device=dev)
+        bias = torch.randn(nout, device=dev)
+        dy = torch.randn(batch, nout, device=dev)
+        y = torch.full((batch, nout), float("nan"), device=dev)
+        nat.small_linear_fwd(x, w, bias, y)
+        assert _rel(y, x.double() @ w.double().t() + bias.double()) < 2e-6
+        dx = torch.full((batch, k), float("nan"), device=dev)
+        dw = torch.full((nout, k), float("nan"), device=dev)
+        db = torch.full((nout,), float("nan"), device=dev)
+        nat.small_linear_bwd(dy, x, w, dx, dw, db)
+        assert _rel(dx, dy.double() @ w.double()) < 2e-6
+        assert _rel(dw, dy.double().t() @ x.double()) < 2e-6
+        assert _rel(db, dy.double().sum(0)) < 2e-6
+
+
 def test_linear_b200_weight_grad_sink_and_module_protocol(nat):
     """``weight_grad_out``: the backward writes the weight gradient into a caller's buffer and autograd
     adopts it; a second forward before backward is refused; optimizers work on the parameters."""
