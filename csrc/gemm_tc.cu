@@ -62,9 +62,9 @@ struct GemmArgs {
   int transposed;          // 0: out[m*ld + n]   1: out[n*ld + m]
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int MT>
 struct GemmSmem {
-  static constexpr uint32_t a_set = kGemmBM * kGemmKS * 2;  // 8192 B, either major
+  static constexpr uint32_t a_set = MT * kGemmBM * kGemmKS * 2;  // 8192 B per M tile, either major
   static constexpr uint32_t b_set = BN * kGemmKS * 2;
   static constexpr uint32_t stage_bytes = 2 * a_set + 2 * b_set;
   static constexpr uint32_t off_bar = STAGES * stage_bytes;
@@ -102,13 +102,18 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap
 }
 
 // TM: operand tiles by tensor-map TMA (ma / mb), else by 1-D bulk copies from g.a / g.b.
-template <bool A_MN, bool B_MN, int BN, int STAGES, bool TM>
-__global__ void __launch_bounds__(kGemmThreads, 2)
+// MT: M tiles (of 128) per CTA.  MT = 2 multiplies two A tiles by the same B tile (two accumulators, all
+// 512 TMEM columns at BN = 256, one CTA per SM): a third less operand traffic through L2 per FLOP; opt-in,
+// see gemm_tiling().
+template <bool A_MN, bool B_MN, int BN, int STAGES, bool TM, int MT>
+__global__ void __launch_bounds__(kGemmThreads, MT == 1 ? 2 : 1)
 gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const __grid_constant__ CUtensorMap mb) {
-  using S = GemmSmem<BN, STAGES>;
-  using TA = OperandTile<A_MN, kGemmBM>;
+  using S = GemmSmem<BN, STAGES, MT>;
+  using TA = OperandTile<A_MN, MT * kGemmBM>;
   using TB = OperandTile<B_MN, BN>;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t TMEM_COLS = MT * BN < 32 ? 32 : MT * BN;
+  constexpr uint32_t a_sub = A_MN ? (kGemmBM / 8) * kGemmKS * 16 : kGemmBM * 16;  // second M tile inside an A set
+  static_assert(MT == 1 || (MT == 2 && BN * MT <= 512), "two accumulators need 2*BN TMEM columns");
   extern __shared__ __align__(128) uint8_t smem[];
 
   const int tid = threadIdx.x;
@@ -158,8 +163,8 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
         const int k0 = (st0 + it) * kGemmKS;
         const uint32_t sa = s_base + stage * S::stage_bytes;
         const uint32_t sb = sa + 2 * S::a_set;
-        if (A_MN) tma_load_4d(sa, &ma, full, 0, k0 / 32, m_tile * (kGemmBM / 8), 0);
-        else tma_load_4d(sa, &ma, full, 0, m_tile * (kGemmBM / 32), k0 / 8, 0);
+        if (A_MN) tma_load_4d(sa, &ma, full, 0, k0 / 32, m_tile * (MT * kGemmBM / 8), 0);
+        else tma_load_4d(sa, &ma, full, 0, m_tile * (MT * kGemmBM / 32), k0 / 8, 0);
         if (B_MN) tma_load_4d(sb, &mb, full, 0, k0 / 32, n_tile * (BN / 8), 0);
         else tma_load_4d(sb, &mb, full, 0, n_tile * (BN / 32), k0 / 8, 0);
       }
@@ -213,6 +218,15 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
           umma_bf16(tmem_base, a_lo, b_hi, idesc, 1);
           umma_bf16(tmem_base, a_hi, b_lo, idesc, 1);
         }
+        if constexpr (MT == 2) {  // second M tile, same B tile, second accumulator
+          const uint64_t a2_hi = umma_smem_desc(sa + a_sub + kk * TA::kstep, TA::lbo, TA::sbo);
+          const uint64_t a2_lo = umma_smem_desc(sa + S::a_set + a_sub + kk * TA::kstep, TA::lbo, TA::sbo);
+          if (elect_one()) {
+            umma_bf16(tmem_base + BN, a2_hi, b_hi, idesc, (it | kk) != 0);
+            umma_bf16(tmem_base + BN, a2_lo, b_hi, idesc, 1);
+            umma_bf16(tmem_base + BN, a2_hi, b_lo, idesc, 1);
+          }
+        }
       }
       if (elect_one()) umma_commit(bar_empty + stage * 8);
       __syncwarp();
@@ -221,7 +235,6 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
     __syncwarp();
   } else {
     const int q = warp & 3;  // TMEM lane quadrant this warp may read
-    const int m = m_tile * kGemmBM + q * 32 + lane;
     const int n0 = n_tile * BN;
     float* out = g.out + (long long)split * g.split_stride;
     if (nst > 0) {
@@ -231,10 +244,12 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
     const bool vec_ok = !g.transposed && (g.ld & 3) == 0 && (g.split_stride & 3) == 0 &&
                         (reinterpret_cast<uintptr_t>(g.out) & 15) == 0;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
+    for (int cc = 0; cc < MT * BN; cc += 32) {
+      const int mt = cc / BN, c0 = cc - mt * BN;  // accumulator (M tile) and column inside it
+      const int m = (m_tile * MT + mt) * kGemmBM + q * 32 + lane;
       uint32_t v[32];
       if (nst > 0) {
-        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+        tmem_ld32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + cc, v);
         tmem_ld_wait();
       } else {
 #pragma unroll
@@ -508,34 +523,51 @@ static int encode_operand_map(EncodeTiledFn enc, CUtensorMap* m, const GemmOpera
   return r == CUDA_SUCCESS ? 0 : DDPB_ERR_UNSUPPORTED;
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, int MT>
 static int launch_gemm(const GemmArgs& g, dim3 grid, cudaStream_t st) {
-  constexpr int STAGES = BN == 256 ? 2 : BN == 128 ? 3 : 4;  // ~96 KB: two CTAs per SM
-  using S = GemmSmem<BN, STAGES>;
+  // MT = 1: ~96 KB of stages, two CTAs per SM (one's epilogue under the other's main loop);
+  // MT = 2: three 64 KB stages, one CTA per SM
+  constexpr int STAGES = MT == 2 ? 3 : BN == 256 ? 2 : BN == 128 ? 3 : 4;
+  using S = GemmSmem<BN, STAGES, MT>;
   alignas(64) CUtensorMap ma, mb;
   memset(&ma, 0, sizeof(ma));
   memset(&mb, 0, sizeof(mb));
   EncodeTiledFn enc = encode_tiled();
-  if (enc && (encode_operand_map(enc, &ma, g.a, A_MN, kGemmBM) || encode_operand_map(enc, &mb, g.b, B_MN, BN)))
+  if (enc && (encode_operand_map(enc, &ma, g.a, A_MN, MT * kGemmBM) || encode_operand_map(enc, &mb, g.b, B_MN, BN)))
     enc = nullptr;  // fall back to the 1-D copies
   if (enc) {
-    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true>;
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true, MT>;
     DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
   } else {
-    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, false>;
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, false, MT>;
     DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
   }
   return 0;
 }
 
-template <int BN>
+template <int BN, int MT>
 static int launch_gemm_major(int a_mn, int b_mn, const GemmArgs& g, dim3 grid, cudaStream_t st) {
-  if (!a_mn && !b_mn) return launch_gemm<false, false, BN>(g, grid, st);
-  if (a_mn && !b_mn) return launch_gemm<true, false, BN>(g, grid, st);
-  if (a_mn && b_mn) return launch_gemm<true, true, BN>(g, grid, st);
+  if (!a_mn && !b_mn) return launch_gemm<false, false, BN, MT>(g, grid, st);
+  if (a_mn && !b_mn) return launch_gemm<true, false, BN, MT>(g, grid, st);
+  if (a_mn && b_mn) return launch_gemm<true, true, BN, MT>(g, grid, st);
   return DDPB_ERR_SHAPE;  // (K-major A, MN-major B) is not needed by a linear layer
+}
+
+// N tile and M tiles per CTA for an (M, N) output.  One M tile per CTA by default; DDPB_GEMM_MT=2 selects
+// two from 256 rows up at the full N tile.  Measured on B200 for fc 32768->750 at batch 256 (us, one / two M
+// tiles): forward 46.0 / 42.5, data gradient 36.6 / 41.0, weight gradient 65.0 / 64.7 — the third less
+// operand traffic is paid for with the lost overlap of one CTA's epilogue with the other's main loop, so the
+// simpler configuration stays the default.
+static void gemm_tiling(int M, int N, int* bn, int* mt) {
+  *bn = N <= 64 ? 64 : N <= 128 ? 128 : 256;
+  static int mt_max = 0;
+  if (!mt_max) {
+    const char* e = getenv("DDPB_GEMM_MT");
+    mt_max = (e && e[0] == '2') ? 2 : 1;
+  }
+  *mt = (*bn == 256 && M > kGemmBM && mt_max == 2) ? 2 : 1;
 }
 
 }  // namespace ddpb
@@ -602,20 +634,23 @@ int ddpb_gemm_split(const void* a, int a_rows, int a_k, int a_mn, const void* b,
   g.k_stages = (K + kGemmKS - 1) / kGemmKS;
   g.transposed = transposed;
   if (k_splits > g.k_stages) k_splits = g.k_stages;
-  const int bn = N <= 64 ? 64 : N <= 128 ? 128 : 256;
-  dim3 grid((M + kGemmBM - 1) / kGemmBM, (N + bn - 1) / bn, k_splits);
+  int bn, mt;
+  gemm_tiling(M, N, &bn, &mt);
+  dim3 grid((M + mt * kGemmBM - 1) / (mt * kGemmBM), (N + bn - 1) / bn, k_splits);
   if (grid.y > 65535 || grid.z > 65535) return DDPB_ERR_LIMIT;
   cudaStream_t st = (cudaStream_t)stream;
-  if (bn == 64) return launch_gemm_major<64>(a_mn, b_mn, g, grid, st);
-  if (bn == 128) return launch_gemm_major<128>(a_mn, b_mn, g, grid, st);
-  return launch_gemm_major<256>(a_mn, b_mn, g, grid, st);
+  if (bn == 64) return launch_gemm_major<64, 1>(a_mn, b_mn, g, grid, st);
+  if (bn == 128) return launch_gemm_major<128, 1>(a_mn, b_mn, g, grid, st);
+  if (mt == 2) return launch_gemm_major<256, 2>(a_mn, b_mn, g, grid, st);
+  return launch_gemm_major<256, 1>(a_mn, b_mn, g, grid, st);
 }
 
 // The K-split count ddpb_gemm_split would be best called with for an (M, N, K) problem: enough CTAs
 // to fill the GPU once, never fewer than 4 stages of work per split.
 int ddpb_gemm_split_suggest_splits(int M, int N, int K) {
-  const int bn = N <= 64 ? 64 : N <= 128 ? 128 : 256;
-  const long long tiles = (long long)((M + kGemmBM - 1) / kGemmBM) * ((N + bn - 1) / bn);
+  int bn, mt;
+  gemm_tiling(M, N, &bn, &mt);
+  const long long tiles = (long long)((M + mt * kGemmBM - 1) / (mt * kGemmBM)) * ((N + bn - 1) / bn);
   const int stages = (K + kGemmKS - 1) / kGemmKS;
   const int sms = ddpb_num_sms();
   long long s = tiles >= sms ? 1 : sms / tiles;
