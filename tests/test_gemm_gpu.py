@@ -279,11 +279,25 @@ def test_wide_cnn_b200_gradients_against_fp64_and_the_torch_model(nat):
     lo = F.cross_entropy(o(x.double()), y)
     lo.backward()
     assert abs(float(la) - float(lo)) < 1e-4
+    rows = []
     for (n, p), q, r in zip(a.named_parameters(), b.parameters(), o.parameters()):
         ga = a._cols_to_chw(p.grad) if n == "classifier.0.weight" else p.grad
         scale = float(r.grad.abs().max())
         e_ours = float((ga.double() - r.grad).abs().max()) / scale
         e_torch = float((q.grad.double() - r.grad).abs().max()) / scale
+        rows.append((n, e_ours, e_torch))
+    import os
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/precision_wide.md", "w") as f:   # copied to profiles/ as evidence
+        f.write("# Widened CNN (config 4): gradient error against an fp64 oracle, batch 32\n\n"
+                "max |g - g_fp64| / max |g_fp64| per parameter; `ours` = WideCNNB200 (fp32 conv1 kernels, cuDNN TF32 "
+                "conv2, bf16x3 tcgen05 fc1, fp32 head), `torch` = the plain module (cuDNN TF32 convolutions, cuBLAS "
+                "fp32 linear layers).  Written by tests/test_gemm_gpu.py.\n\n"
+                "| parameter | ours | torch | ours / torch |\n|---|---:|---:|---:|\n")
+        for n, eo, et in rows:
+            f.write(f"| `{n}` | {eo:.2e} | {et:.2e} | {eo / max(et, 1e-30):.2f} |\n")
+        f.write(f"\nloss: ours {float(la):.7f}, torch {float(lb):.7f}, fp64 {float(lo):.7f}\n")
+    for n, e_ours, e_torch in rows:
         assert e_ours < max(2 * e_torch, 1e-5), (n, e_ours, e_torch)
 
 
@@ -310,3 +324,35 @@ def test_bucketed_engine_graph_replay_matches_eager_steps(nat):
     (l0, s0), (l1, s1) = finals
     assert l0 == l1, (l0, l1)
     assert all(torch.equal(s0[k], s1[k]) for k in s0)
+
+
+def test_gemm_two_m_tiles_per_cta_option(nat):
+    """DDPB_GEMM_MT=2 (two accumulators per CTA sharing one B tile) is read once per process: run the three
+    operand-major pairs in a child process and compare with fp64 there."""
+    import os
+    import subprocess
+    import sys
+    code = """
+import sys, torch
+sys.path.insert(0, %r)
+from ddp_b200.ops import native as nat
+nat.lib()
+dev = 'cuda'
+torch.manual_seed(0)
+O, B, K = 750, 300, 1000
+w, x, dy = torch.randn(O, K, device=dev), torch.randn(B, K, device=dev), torch.randn(B, O, device=dev)
+pw, px, pdy = nat.PackedMatrix(O, K, dev).pack(w), nat.PackedMatrix(B, K, dev).pack(x), nat.PackedMatrix(B, O, dev).pack(dy)
+rel = lambda a, r: float((a.double() - r).abs().max() / r.abs().max())
+y = torch.full((B, O), float('nan'), device=dev)
+nat.gemm_split(pw, False, px, False, O, B, K, y, O, True)
+dx = torch.full((B, K), float('nan'), device=dev)
+nat.gemm_split(pw, True, pdy, False, K, B, O, dx, K, True)
+dw = torch.full((O, K), float('nan'), device=dev)
+nat.gemm_split(pdy, True, px, True, O, K, B, dw, K, False)
+errs = (rel(y, x.double() @ w.double().t()), rel(dx, dy.double() @ w.double()), rel(dw, dy.double().t() @ x.double()))
+assert max(errs) < 2e-5, errs
+print('mt2 ok', errs)
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, DDPB_GEMM_MT="2")
+    res = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and "mt2 ok" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
