@@ -101,13 +101,44 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap
       : "memory");
 }
 
+// The same copy delivered to the same shared-memory offset (and signalled on the mbarrier at the same offset)
+// of every CTA of the cluster named in cta_mask.  The source is always this GPU's own memory.
+__device__ __forceinline__ void tma_load_4d_multicast(uint32_t dst_smem, const CUtensorMap* map, uint32_t bar, int c0,
+                                                      int c1, int c2, int c3, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%4, %5, %6, %7}], [%2], %3;" ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar),
+      "h"(cta_mask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// tcgen05.commit arriving on the mbarrier at the same offset in every CTA of cta_mask.
+__device__ __forceinline__ void umma_commit_multicast(uint32_t bar, uint16_t cta_mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(cta_mask)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_cta_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // TM: operand tiles by tensor-map TMA (ma / mb), else by 1-D bulk copies from g.a / g.b.
+// CL = 2: the kernel runs as clusters of two CTAs that differ only in their M tile.  Each CTA fetches its own
+// A tile and ONE of the two sets (hi / lo) of the common B tile, multicast into both CTAs' shared memory: the
+// B tile crosses L2 -> SM once per pair.  A stage is free again when BOTH CTAs' MMAs have consumed it
+// (tcgen05.commit multicast onto both "empty" barriers).
 // MT: M tiles (of 128) per CTA.  MT = 2 multiplies two A tiles by the same B tile (two accumulators, all
 // 512 TMEM columns at BN = 256, one CTA per SM): a third less operand traffic through L2 per FLOP; opt-in,
 // see gemm_tiling().
-template <bool A_MN, bool B_MN, int BN, int STAGES, bool TM, int MT>
+template <bool A_MN, bool B_MN, int BN, int STAGES, bool TM, int MT, int CL>
 __global__ void __launch_bounds__(kGemmThreads, MT == 1 ? 2 : 1)
 gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const __grid_constant__ CUtensorMap mb) {
+  static_assert(CL == 1 || (CL == 2 && TM), "the cluster variant needs the tensor-map path");
   using S = GemmSmem<BN, STAGES, MT>;
   using TA = OperandTile<A_MN, MT * kGemmBM>;
   using TB = OperandTile<B_MN, BN>;
@@ -134,7 +165,7 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
   if (tid == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(bar_full + i * 8, 1);
-      mbar_init(bar_empty + i * 8, 1);
+      mbar_init(bar_empty + i * 8, CL);  // one arrival per CTA of the cluster that reads the stage's B tile
     }
     mbar_init(bar_done, 1);
     fence_mbar_init();
@@ -145,8 +176,10 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();  // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
+  const uint32_t crank = CL > 1 ? cluster_cta_rank() : 0;
   pdl_sync();
 
   if (warp == 0 && TM) {
@@ -165,8 +198,15 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
         const uint32_t sb = sa + 2 * S::a_set;
         if (A_MN) tma_load_4d(sa, &ma, full, 0, k0 / 32, m_tile * (MT * kGemmBM / 8), 0);
         else tma_load_4d(sa, &ma, full, 0, m_tile * (MT * kGemmBM / 32), k0 / 8, 0);
-        if (B_MN) tma_load_4d(sb, &mb, full, 0, k0 / 32, n_tile * (BN / 8), 0);
-        else tma_load_4d(sb, &mb, full, 0, n_tile * (BN / 32), k0 / 8, 0);
+        if (CL > 1) {
+          // mb's box holds ONE set here: this CTA fetches set `crank` for the whole cluster
+          const uint32_t dst = sb + crank * S::b_set;
+          if (B_MN) tma_load_4d_multicast(dst, &mb, full, 0, k0 / 32, n_tile * (BN / 8), crank, (1u << CL) - 1);
+          else tma_load_4d_multicast(dst, &mb, full, 0, n_tile * (BN / 32), k0 / 8, crank, (1u << CL) - 1);
+        } else {
+          if (B_MN) tma_load_4d(sb, &mb, full, 0, k0 / 32, n_tile * (BN / 8), 0);
+          else tma_load_4d(sb, &mb, full, 0, n_tile * (BN / 32), k0 / 8, 0);
+        }
       }
     }
     __syncwarp();
@@ -228,7 +268,10 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
           }
         }
       }
-      if (elect_one()) umma_commit(bar_empty + stage * 8);
+      if (elect_one()) {
+        if (CL > 1) umma_commit_multicast(bar_empty + stage * 8, (1u << CL) - 1);
+        else umma_commit(bar_empty + stage * 8);
+      }
       __syncwarp();
     }
     if (elect_one()) umma_commit(bar_done);
@@ -263,17 +306,30 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
             if (n < g.N) out[(long long)n * g.ld + m] = __uint_as_float(v[c]);
           }
         }
+      } else if (vec_ok && n0 + c0 + 32 <= g.N) {
+        // A lane holds 32 columns of ONE row; stored directly, every 16-byte store of a warp would hit 32
+        // different rows and fill half a 32-byte sector each (measured: 197 MB of store traffic for the 98 MB
+        // weight gradient of fc 32768->750).  The 32x32 block goes through shared memory instead (the stage
+        // ring is idle once the accumulator is final) so that eight lanes cover one row's 128 bytes.
+        float* sbuf = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) sbuf[lane * 33 + c] = __uint_as_float(v[c]);
+        __syncwarp();
+        const int m_base = m - lane;  // first row of this warp's quadrant
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int r = i * 4 + (lane >> 3), c4 = (lane & 7) * 4;
+          const float* s = sbuf + r * 33 + c4;
+          if (m_base + r < g.M)
+            *reinterpret_cast<float4*>(out + (long long)(m_base + r) * g.ld + n0 + c0 + c4) =
+                make_float4(s[0], s[1], s[2], s[3]);
+        }
+        __syncwarp();
       } else if (m < g.M) {
         float* row = out + (long long)m * g.ld + n0 + c0;
-        if (vec_ok && n0 + c0 + 32 <= g.N) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(row + 4 * j) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; ++c)
-            if (n0 + c0 + c < g.N) row[c] = __uint_as_float(v[c]);
-        }
+        for (int c = 0; c < 32; ++c)
+          if (n0 + c0 + c < g.N) row[c] = __uint_as_float(v[c]);
       }
     }
   }
@@ -281,6 +337,8 @@ gemm_split_tc_kernel(GemmArgs g, const __grid_constant__ CUtensorMap ma, const _
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+  // neither CTA may exit while the other can still multicast data or barrier arrivals into it
+  if (CL > 1) cluster_sync_all();
 }
 
 // fp32 row-major src[R][K] (leading dimension ld) -> split row planes.  Optional `mask` (same shape and
@@ -516,16 +574,50 @@ static EncodeTiledFn encode_tiled() {
 // 46.2 vs 46.4 us): these GEMMs are bound by L2 throughput — ~300 MB of operand tiles in 46 us — not by the
 // TMA unit.  What would lower the traffic without giving up the second CTA per SM is multicasting the shared
 // B tile across a cluster of CTAs that differ only in their M tile.)
-static int encode_operand_map(EncodeTiledFn enc, CUtensorMap* m, const GemmOperand& op, bool mn, int T) {
+static int encode_operand_map(EncodeTiledFn enc, CUtensorMap* m, const GemmOperand& op, bool mn, int T,
+                              int box_sets = 2) {
   const cuuint64_t planes = (cuuint64_t)(op.set_stride / op.rows);
   cuuint64_t dims[4] = {256, (cuuint64_t)op.rows / 32, planes, 2};
   cuuint64_t strides[3] = {512, (cuuint64_t)op.rows * 16, (cuuint64_t)op.set_stride * 16};
-  cuuint32_t box[4] = {256, mn ? 1u : (cuuint32_t)T / 32, mn ? (cuuint32_t)T / 8 : (cuuint32_t)kGemmKS / 8, 2};
+  cuuint32_t box[4] = {256, mn ? 1u : (cuuint32_t)T / 32, mn ? (cuuint32_t)T / 8 : (cuuint32_t)kGemmKS / 8,
+                       (cuuint32_t)box_sets};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<uint4*>(op.base), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : DDPB_ERR_UNSUPPORTED;
+}
+
+// Launch as clusters of two CTAs along x (plain stream order: no programmatic dependent launch attribute).
+template <typename K>
+static cudaError_t launch_cluster2(K kern, dim3 grid, size_t smem, cudaStream_t st, const GemmArgs& g,
+                                   const CUtensorMap& ma, const CUtensorMap& mb) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, g, ma, mb);
+}
+
+// Clusters of two CTAs sharing the B tile: opt-in with DDPB_GEMM_CLUSTER=1.  Measured on B200, fc 32768->750 at
+// batch 256 (us, independent CTAs / clusters): forward 45.8 / 47.6, data gradient 36.7 / 41.2, weight gradient
+// 65.0 / 72.8 — halving the B traffic does not pay for coupling the two CTAs' pipelines (each waits for the
+// slower one at every stage), so independent CTAs stay the default.
+static bool gemm_cluster_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("DDPB_GEMM_CLUSTER");
+    on = (e && e[0] == '1') ? 1 : 0;
+  }
+  return on == 1;
 }
 
 template <bool A_MN, bool B_MN, int BN, int MT>
@@ -538,14 +630,37 @@ static int launch_gemm(const GemmArgs& g, dim3 grid, cudaStream_t st) {
   memset(&ma, 0, sizeof(ma));
   memset(&mb, 0, sizeof(mb));
   EncodeTiledFn enc = encode_tiled();
+  if constexpr (MT == 1 && BN == 256) {
+    // two or more M tiles: pairs of CTAs share each B tile (the packed rows / planes are padded to 256, so
+    // an odd tile count is rounded up inside the padding)
+    if (enc && gemm_cluster_enabled() && grid.x >= 2 &&
+        !encode_operand_map(enc, &ma, g.a, A_MN, kGemmBM) && !encode_operand_map(enc, &mb, g.b, B_MN, BN, 1)) {
+      auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true, 1, 2>;
+      DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
+      dim3 cgrid((grid.x + 1) / 2 * 2, grid.y, grid.z);
+      DDPB_CUDA_OK(launch_cluster2(kern, cgrid, S::total, st, g, ma, mb));
+      return 0;
+    }
+  }
   if (enc && (encode_operand_map(enc, &ma, g.a, A_MN, MT * kGemmBM) || encode_operand_map(enc, &mb, g.b, B_MN, BN)))
     enc = nullptr;  // fall back to the 1-D copies
+  if constexpr (MT == 1 && BN == 256) {
+    // At most one CTA per SM anyway (a split-K forward pass): spend the whole shared memory on a deeper ring —
+    // with two 48 KB stages a lone CTA keeps only ~96 KB of loads in flight, which bounds it by latency.
+    if (enc && (long long)grid.x * grid.y * grid.z <= ddpb_num_sms()) {
+      using S4 = GemmSmem<BN, 4, MT>;
+      auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, 4, true, MT, 1>;
+      DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S4::total));
+      DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S4::total, st, g, ma, mb));
+      return 0;
+    }
+  }
   if (enc) {
-    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true, MT>;
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, true, MT, 1>;
     DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
   } else {
-    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, false, MT>;
+    auto kern = gemm_split_tc_kernel<A_MN, B_MN, BN, STAGES, false, MT, 1>;
     DDPB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::total));
     DDPB_CUDA_OK(launch_k(kern, grid, dim3(kGemmThreads), S::total, st, g, ma, mb));
   }
