@@ -21,8 +21,12 @@ KEEP_FULL = ("conv3x3_tc_kernel", "conv3x3_wgrad_tc_kernel", "allreduce_sgd_ones
              "linear_bwd_f32_kernelILi10ELb1ELb0ELb1E", "softmax_xent_kernel", "pack_linear_weights_kernel",
              "pack_conv3x3_split_kernel", "allreduce_kernelIfLi8ELi1E",
              # general linear layers (gemm_tc.cu): the three operand-major pairs at N tile 256, tensor-map TMA
-             "gemm_split_tc_kernelILb0ELb0ELi256ELi2ELb1E", "gemm_split_tc_kernelILb1ELb0ELi256ELi2ELb1E",
-             "gemm_split_tc_kernelILb1ELb1ELi256ELi2ELb1E", "pack_rows_split_kernel",
+             # (template arguments: A_MN, B_MN, BN, STAGES, TM, MT, CL)
+             "gemm_split_tc_kernelILb0ELb0ELi256ELi4ELb1ELi1ELi1E", "gemm_split_tc_kernelILb1ELb0ELi256ELi2ELb1ELi1ELi1E",
+             "gemm_split_tc_kernelILb1ELb1ELi256ELi2ELb1ELi1ELi1E",
+             "gemm_split_tc_kernelILb1ELb1ELi256ELi2ELb1ELi1ELi2E",   # cluster of two, multicast B tile (opt-in)
+             "gemm_split_tc_kernelILb1ELb1ELi256ELi3ELb1ELi2ELi1E",   # two M tiles per CTA (opt-in)
+             "small_linear_fwd_kernel", "small_linear_dw_kernel", "pack_rows_split_kernel",
              "conv3x3_small_cin_fwd_kernel", "conv3x3_small_cin_wgrad_kernel", "relu_maxpool2_nhwc_fwd_kernel")
 KEYS = ["UTCHMMA", "UTCBAR", "LDTM", "UBLKCP", "UTMALDG", "LDGSTS", "SYNCS", "HMMA", "FFMA", "LDGMC", "LDG", "STG",
         "LDS", "STS", "SHFL", "ATOM", "RED", "MEMBAR", "CCTL"]
