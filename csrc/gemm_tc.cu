@@ -1,7 +1,6 @@
 // General dense GEMM on the 5th-generation tensor cores for fully connected layers of ANY shape:
-// split-precision ("bf16x3") operands, fp32 accumulation in TMEM, operands fetched by 1-D bulk async
-// copies (TMA) from "row planes" — the same 16-byte-row plane idea as layout.cuh, without the image
-// padding:
+// split-precision ("bf16x3") operands, fp32 accumulation in TMEM, operand tiles fetched by tensor-map TMA
+// from "row planes" — the same 16-byte-row plane idea as layout.cuh, without the image padding:
 //
 //   a matrix X[R][K] (R rows, K contiguous elements each) is stored as two sets (hi, lo; x = hi + lo,
 //   both bf16) of K/8 planes; a plane is R_pad rows of 16 bytes = the 8 consecutive K elements
@@ -27,11 +26,16 @@
 // 16..96 one-dimensional bulk copies per stage and was bound by ~50 ns per copy per SM (weight gradient
 // of fc 32768->750 at batch 256: 195 us); DDPB_GEMM_TMA=0 selects that path for comparison.
 //
-// Warp roles (192 threads, one output tile (x one K split) per CTA, two CTAs per SM so that one's
-// epilogue overlaps the other's main loop):
+// A stage of the ring holds 32 reduction elements of both operands, hi and lo (48 KB at a 256-wide N tile):
+// two stages and two CTAs per SM (one's epilogue under the other's main loop), or four stages when the whole
+// grid is a single wave of CTAs.  Tuning notes with numbers: DESIGN.md §4 and the comments at gemm_tiling(),
+// gemm_cluster_enabled() and encode_operand_map().
+//
+// Warp roles (192 threads, one output tile (x one K split) per CTA):
 //   warp 0    TMA producer (one lane; the 1-D fallback path issues from all 32 lanes)
 //   warp 1    TMEM allocator + MMA issuer (one elected lane issues tcgen05.mma)
-//   warps 2-5 epilogue: tcgen05.ld the accumulator, store fp32 (row-major or transposed)
+//   warps 2-5 epilogue: tcgen05.ld the accumulator, store fp32 (transposed: a column at a time, 128 contiguous
+//             bytes per warp; row-major: through shared memory so that stores fill whole 32-byte sectors)
 #include <cuda.h>
 #include <stdlib.h>
 #include <string.h>
