@@ -88,3 +88,31 @@ def border_rows_are_zero(planes: torch.Tensor, B: int, H: int, W: int) -> bool:
     keep[:GUARD] = False
     keep[GUARD + ntile_rows:] = False
     return bool((planes[:, keep, :].float() == 0).all())
+
+
+# ----------------------------------------------------------------------------- split row planes (csrc/gemm_tc.cu)
+GEMM_PAD = 256  # rows and K elements of a packed matrix are zero-padded to multiples of this
+
+
+def pack_rows_split(x: torch.Tensor, rows_cap: int | None = None) -> torch.Tensor:
+    """Host-side restatement of ``ddpb_pack_rows_split``: a fp32 matrix [R, K] as the operand format of
+    the general tensor-core GEMM — ``[2, Kp/8, Rp, 8]`` bf16 with ``out[0]`` the nearest-bf16 terms,
+    ``out[1]`` the bf16-rounded remainders (x = hi + lo), element (r, k) at ``[set, k // 8, r, k % 8]``
+    and Rp, Kp the sizes rounded up to ``GEMM_PAD`` (padding zero)."""
+    R, K = x.shape
+    rp = -(-(rows_cap if rows_cap is not None else R) // GEMM_PAD) * GEMM_PAD
+    kp = -(-K // GEMM_PAD) * GEMM_PAD
+    hi = x.float().bfloat16()
+    lo = (x.float() - hi.float()).bfloat16()
+    out = torch.zeros(2, kp // 8, rp, 8, dtype=torch.bfloat16, device=x.device)
+    for s, term in enumerate((hi, lo)):
+        full = torch.zeros(rp, kp, dtype=torch.bfloat16, device=x.device)
+        full[:R, :K] = term
+        out[s] = full.view(rp, kp // 8, 8).permute(1, 0, 2)
+    return out
+
+
+def unpack_rows_split(planes: torch.Tensor, R: int, K: int) -> torch.Tensor:
+    """[2, Kp/8, Rp, 8] split row planes -> the fp32 matrix [R, K] they represent (hi + lo)."""
+    both = planes.float().sum(0)                       # [Kp/8, Rp, 8]
+    return both.permute(1, 0, 2).reshape(both.shape[1], -1)[:R, :K].contiguous()

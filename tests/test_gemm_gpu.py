@@ -41,6 +41,12 @@ def test_pack_rows_split_layout_and_padding(nat):
     # the tail of the last real chunk and the rows up to the next multiple of 32 are written as zeros
     assert float(got_hi[:rows, k:752].abs().max()) == 0 and float(got_lo[:rows, k:752].abs().max()) == 0
     assert float(got_hi[rows:64, :752].abs().max()) == 0 and float(got_lo[rows:64, :752].abs().max()) == 0
+    # the host-side restatement of the format (ops/layout.py) agrees on everything the pack defines
+    from ddp_b200.ops.layout import pack_rows_split, unpack_rows_split
+    ref = pack_rows_split(x, rows_cap=100)
+    got = pm.buf.view(2, kp // 8, rp, 8)
+    assert torch.equal(got[:, :94, :64, :], ref[:, :94, :64, :])
+    assert torch.equal(unpack_rows_split(got, rows, k), hi + lo)
     # a mask zeroes where it is <= 0
     m = torch.randn(rows, k, device=dev)
     pm.pack(x, m)

@@ -187,3 +187,17 @@ def test_linear_b200_and_wide_cnn_b200_fall_back_to_torch_ops_on_cpu():
     wc = WideCNNB200(hidden=16)
     wc.load_state_dict(sb)
     assert torch.equal(wc.classifier[0].weight, wa.classifier[0].weight)
+
+
+def test_split_row_planes_reference_roundtrip():
+    """ops/layout.py restates the packed operand format of the general GEMM (csrc/gemm_tc.cu): two bf16
+    terms carry a 16-bit significand, the padding is zero, element (r, k) sits at [set, k//8, r, k%8]."""
+    from ddp_b200.ops.layout import GEMM_PAD, pack_rows_split, unpack_rows_split
+    torch.manual_seed(0)
+    x = torch.randn(37, 750)
+    p = pack_rows_split(x, rows_cap=100)
+    assert p.shape == (2, 768 // 8, GEMM_PAD, 8) and p.dtype == torch.bfloat16
+    assert float(p[0, 750 // 8, 5, 750 % 8 - 1]) == float(x[5, 749].bfloat16())
+    back = unpack_rows_split(p, 37, 750)
+    assert float((back - x).abs().max() / x.abs().max()) < 2 ** -15
+    assert float(p[:, :, 37:, :].float().abs().max()) == 0 and float(p[:, 94:, :, :].float().abs().max()) == 0
