@@ -146,7 +146,10 @@ class LinearB200(nn.Linear):
         super().__init__(in_features, out_features, bias=bias)
         self.fused_relu = fused_relu
         #: optional fp32 [out, in] buffer the native backward writes the weight gradient into (and returns
-        #: as the gradient): a data-parallel engine points it at its flat gradient arena
+        #: as the gradient): a data-parallel engine points it at its flat gradient arena.  The buffer is
+        #: OVERWRITTEN by every backward, so whoever sets it must also reset ``weight.grad`` to None before each
+        #: backward (autograd then adopts the buffer as ``.grad``); it is not compatible with accumulating
+        #: gradients over several backward passes.
         self.weight_grad_out = None
         self._native_wanted = native
         self._nat = None
