@@ -1262,9 +1262,103 @@ int ddpb_linear_bwd(const void* act, const float* dlogits, const float* Wt, void
   return ddpb_reduce_partials(scratch, splits, (long long)nout * C * H * W, dW, stream);
 }
 
+}  // extern "C"
+namespace ddpb {
+// Large-batch linear forward (exact fp32): the kernel above gives every block of IMG images the whole
+// reduction, so at batch 4096 each of 1024 blocks streams the full 2 MB weight from L2 (~2 GB of L2 traffic
+// next to 0.9 GB of activations; measured 385 us).  Here a block owns ONE 256-vector slice of the reduction,
+// keeps that slice of the weight in shared memory (40 KB) and walks the image groups: a warp takes a group of
+// four images, its lanes stride over the slice (8 iterations of 4 activation loads + 10 LDS.128 + 160 FMA),
+// reduces its 40 sums inside the warp and writes partial[slice][img][j] — the layout the loss kernel sums.
+constexpr int kLinBigSlice = 256;   // 16-byte activation vectors (4 channels of one pixel) per slice
+template <int NOUT>
+__global__ void __launch_bounds__(256, 2)
+linear_fwd_f32_big_kernel(const float4* __restrict__ act, const float* __restrict__ W,
+                          float* __restrict__ partial, Geom g, int C) {
+  static_assert(NOUT == 10, "warp reduction over 4 x 10 accumulators");
+  __shared__ float4 ws[NOUT][kLinBigSlice];   // ws[j][v] = W[j][4 channels of vector v]
+  pdl_sync();
+  const int HW = g.H * g.W;
+  const int nvec = (C / 4) * HW;
+  const long long K = (long long)C * HW;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int v0 = blockIdx.x * kLinBigSlice;
+  {
+    const int v = v0 + threadIdx.x;
+    const int chunk = v / HW, pix = v - chunk * HW;
+#pragma unroll
+    for (int j = 0; j < NOUT; ++j) {
+      float4 w4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (v < nvec) {
+        const float* wp = W + j * K + (long long)(chunk * 4) * HW + pix;
+        w4 = make_float4(wp[0], wp[HW], wp[2 * (long long)HW], wp[3 * (long long)HW]);
+      }
+      ws[j][threadIdx.x] = w4;
+    }
+  }
+  // plane row (image 0) of every vector of the slice; -1 beyond the end of the reduction
+  __shared__ int s_row[kLinBigSlice];
+  {
+    const int v = v0 + threadIdx.x;
+    const int chunk = v / HW, pix = v - chunk * HW;
+    const int h = pix / g.W, wc = pix - h * g.W;
+    s_row[threadIdx.x] = v < nvec ? (int)((long long)chunk * g.plane_rows + kGuard + (h + 1) * g.PW + (wc + 1)) : -1;
+  }
+  __syncthreads();
+  const int groups = (g.batch + 3) / 4;
+  for (int grp = blockIdx.y * 8 + warp; grp < groups; grp += gridDim.y * 8) {
+    const int img0 = grp * 4;
+    float acc[4 * NOUT];
+#pragma unroll
+    for (int i = 0; i < 4 * NOUT; ++i) acc[i] = 0.f;
+#pragma unroll 2
+    for (int it = 0; it < kLinBigSlice / 32; ++it) {
+      const int row = s_row[it * 32 + lane];
+      float4 av[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        av[i] = (row >= 0 && img0 + i < g.batch) ? act[row + (long long)(img0 + i) * g.PHW]
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < NOUT; ++j) {
+        const float4 w4 = ws[j][it * 32 + lane];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float s = acc[i * NOUT + j];
+          s = fmaf(w4.x, av[i].x, s);
+          s = fmaf(w4.y, av[i].y, s);
+          s = fmaf(w4.z, av[i].z, s);
+          s = fmaf(w4.w, av[i].w, s);
+          acc[i * NOUT + j] = s;
+        }
+      }
+    }
+    warp_reduce40(acc, lane);
+    if ((lane & 3) == 0) {
+      const int base = warp_reduce40_base(lane);
+#pragma unroll
+      for (int ii = 0; ii < 5; ++ii) {
+        const int tt = base + ii, i = tt / NOUT, j = tt - i * NOUT;
+        if (img0 + i < g.batch) partial[((long long)blockIdx.x * g.batch + img0 + i) * NOUT + j] = acc[ii];
+      }
+    }
+  }
+}
+
+}  // namespace ddpb
+extern "C" {
 // ---- fp32-plane (precision-parity) linear layer.  Scratch sizes: ddpb_linear_fwd_f32_scratch_bytes /
 // ddpb_linear_bwd_scratch_bytes (the partial layout of the backward is the same as the bf16 one).
 static int linear_fwd_f32_img(int batch) { return batch >= 512 ? 4 : 8; }
+// batch >= 512: the sliced kernel with the weight slice in shared memory (DDPB_LINFWD_BIG=0: the old one)
+static bool linear_fwd_f32_big(int batch) {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("DDPB_LINFWD_BIG");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1 && batch >= 512;
+}
 static void linear_fwd_f32_geom(int batch, int nvec, int& S, int& per, int& groups) {
   const int IMG = linear_fwd_f32_img(batch);
   groups = (batch + IMG - 1) / IMG;
@@ -1285,6 +1379,17 @@ int ddpb_linear_fwd_f32(const void* act, const float* Wt, float* partial, int* S
   const Geom g = make_geom(batch, batch_cap, H, W);
   const int nvec = (C / 4) * H * W;
   int S, per, groups;
+  if (linear_fwd_f32_big(batch)) {
+    S = (nvec + kLinBigSlice - 1) / kLinBigSlice;  // == the maxS the scratch is sized for
+    if (S_out) *S_out = S;
+    const int ngroups = (batch + 3) / 4;
+    int by = (2 * ddpb_num_sms() + S - 1) / S;     // about two resident blocks per SM over all slices
+    if (by * 8 > ngroups) by = (ngroups + 7) / 8;
+    if (by < 1) by = 1;
+    return static_cast<int>(launch_k(linear_fwd_f32_big_kernel<10>, dim3(S, by), dim3(256), 0,
+                                     static_cast<cudaStream_t>(stream), static_cast<const float4*>(act), Wt,
+                                     partial, g, C));
+  }
   linear_fwd_f32_geom(batch, nvec, S, per, groups);
   if (S_out) *S_out = S;
   if (linear_fwd_f32_img(batch) == 4)
